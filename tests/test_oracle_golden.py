@@ -1,0 +1,83 @@
+"""The C restatement (oracle/nsim_oracle.c) against the reference's own outputs.
+
+The fixtures were produced by oracle/gen_golden.py from the unmodified reference;
+every frame of every trajectory must match bit for bit (64-bit digest of the full
+canonical record: ninja's 31 doubles + 27 ints and every entity row)."""
+import numpy as np
+import pytest
+
+from oracle import oracle, schema
+
+
+def _check(traj):
+    rec = oracle.run_trajectory(traj["map_data"], traj["hor"], traj["jump"])
+    bad = np.nonzero(rec["hash"] != traj["hash"])[0]
+    assert bad.size == 0, f"{traj['name']}: first differing frame {bad[0]} of {len(traj['hor'])}"
+    assert np.array_equal(rec["nin_f"][:, :4].view(np.int64), traj["pv"].view(np.int64))
+    assert np.array_equal(rec["nin_i"][:, 0], traj["state"])
+    assert np.array_equal(rec["nin_f"][-1].view(np.int64), traj["final_nin_f"].view(np.int64))
+    assert np.array_equal(rec["nin_i"][-1], traj["final_nin_i"])
+    assert np.array_equal(rec["ent_f"][-1].view(np.int64), traj["final_ent_f"].view(np.int64))
+    assert np.array_equal(rec["ent_i"][-1], traj["final_ent_i"])
+    return len(traj["hor"])
+
+
+def test_known_answers(golden_replays):
+    """scripts/validate_replays.py:106-140 requires a win on the last frame."""
+    g = golden_replays
+    assert len(g) == 130
+    finals = g.d["final_nin_i"][:, 0]
+    assert int((finals == 8).sum()) == 128
+    no_exit = {"20251022_151333_train_simple_100001", "20251023_095301_train_complex_100001"}
+    assert {g.names[i] for i in np.nonzero(finals != 8)[0]} == no_exit
+    t = g.traj(0)
+    assert t["name"] == "20251022_142001_train_very_simple_100001"
+    assert len(t["hor"]) == 37
+    assert t["pv"][0, 0] == 828.0 and t["pv"][0, 1] == 540.0
+    assert t["pv"][-1, 0] == 812.0036311681246 and t["pv"][-1, 1] == 542.0 and t["state"][-1] == 8
+    # the win must happen exactly on the last frame, not earlier
+    for i in np.nonzero(finals == 8)[0]:
+        tr = g.traj(int(i))
+        assert tr["state"][-1] == 8 and tr["state"][-2] != 8, tr["name"]
+
+
+def test_oracle_bc_replays_bit_exact(golden_replays):
+    frames = sum(_check(golden_replays.traj(i)) for i in range(len(golden_replays)))
+    assert frames == 31461
+
+
+def test_oracle_generated_bit_exact(golden_generated):
+    frames = sum(_check(golden_generated.traj(i)) for i in range(len(golden_generated)))
+    assert frames == 40800
+
+
+def test_pow_is_libm_not_multiply():
+    """H1: x**2 is libm pow; the oracle must not have folded it to x*x."""
+    import ctypes as C
+    import math
+    L = oracle.lib()
+    L.osim_sq_probe.argtypes = [C.c_double]; L.osim_sq_probe.restype = C.c_double
+    rng = np.random.default_rng(7)
+    xs = rng.uniform(-1100, 1100, 200000)
+    diff = 0
+    for x in xs:
+        x = float(x)
+        assert L.osim_sq_probe(x) == x ** 2
+        diff += (x ** 2) != (x * x)
+    assert diff > 0, "expected pow(x,2) != x*x for some inputs on this libm"
+    assert math.isfinite(diff)
+
+
+def test_reset_and_fast_reset_replay_first_golden(golden_replays):
+    """reset()/fast_reset() bring the env back to the post-load state (nsim.py:62-140)."""
+    t = golden_replays.traj(0)
+    s = oracle.OracleSim()
+    s.load(t["map_data"])
+    first = s.state()
+    s.run(t["hor"], t["jump"])
+    s.fast_reset()
+    again = s.state()
+    for a, b in zip(first, again):
+        assert np.array_equal(np.asarray(a).view(np.int64), np.asarray(b).view(np.int64))
+    nf, ni, _, _ = s.run(t["hor"], t["jump"])
+    assert nf[-1][0] == 812.0036311681246 and ni[-1][0] == 8
