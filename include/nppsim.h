@@ -1,0 +1,121 @@
+/*
+ * nppsim.h -- C ABI of libnppsim.so, the B200 batched N++ physics engine.
+ *
+ * Drop-in boundary for the reference's Simulator hot path (paths are under
+ * /root/reference/nclone/).  The reference has no FFI layer: the seam is the Python
+ * class nsim.Simulator behind the facade nplay_headless.NPlayHeadless, so each entry
+ * point below names the Simulator method it replaces for a whole batch of envs.
+ * The Python binding a maintainer would add is a ctypes stub.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch / C++ types cross this boundary;
+ *   - all buffers are caller-owned (the library never allocates device memory);
+ *   - every function returns 0 on success, <0 for an argument / map error (NPPSIM_E_*),
+ *     >0 for a CUDA runtime error code; nppsim_last_error() describes the last failure
+ *     on the calling thread;
+ *   - launches are asynchronous on the given cudaStream_t (passed as void*); the library
+ *     keeps no global mutable state, so one instance per device / stream is safe.
+ */
+#ifndef NPPSIM_H
+#define NPPSIM_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NPPSIM_VERSION 100
+
+#define NPPSIM_E_ARG      (-1)
+#define NPPSIM_E_MAP      (-2)   /* malformed map_data (the reference raises KeyError/IndexError/ValueError) */
+#define NPPSIM_E_CAPACITY (-3)   /* entity / slot capacity exceeded: an error at load, never truncation */
+#define NPPSIM_E_NOGPU    (-4)
+
+/* Canonical per-env ninja record: NPPSIM_NF doubles + NPPSIM_NI int32, structure-of-arrays
+ * with stride n_envs: field f of env i lives at nin_f[f * n_envs + i].  Field order =
+ * Ninja.__init__ (ninja.py:80-196); names in nclone_b200/fields.py. */
+#define NPPSIM_NF 31
+#define NPPSIM_NI 27
+/* per-env bookkeeping ints (env_i[k * n_envs + i]) */
+#define NPPSIM_ENV_STAMP    0   /* next grid_entity insertion stamp (entities.py:256-264 order) */
+#define NPPSIM_ENV_HOT      1   /* count of toggling mines + touched boost pads */
+#define NPPSIM_ENV_EVENTS   2   /* NPPSIM_EV_* bits accumulated since the caller last cleared them */
+#define NPPSIM_ENV_SWFRAME  3   /* sim.frame at which the exit switch was taken, -1 if not yet */
+#define NPPSIM_ENV_ORDER    4   /* 0: grid lists in creation order (load/reset); 1: entity_dic order (fast_reset) */
+#define NPPSIM_NENV 5
+
+#define NPPSIM_EV_EXIT_SWITCH 1  /* entity_exit_switch.py:128-129 -> gym_env.invalidate_switch_cache() */
+#define NPPSIM_EV_LOCKED_DOOR 2  /* entity_door_locked.py:66-67 */
+#define NPPSIM_EV_WIN         4
+#define NPPSIM_EV_DEATH       8
+
+/* dynamic slot layout: dyn_f[(slot*4 + k) * n_envs + i], dyn_i[(slot*3 + k) * n_envs + i] */
+#define NPPSIM_DYN_F 4          /* xpos, ypos, a0, a1 */
+#define NPPSIM_DYN_I 3          /* cell (cx*25+cy, -1 = not in grid_entity), stamp, aux */
+
+typedef struct {
+    int32_t n_envs;             /* N, also the SoA stride */
+    int32_t ent_cap;            /* rows of ent_flag  (>= max n_ent over the loaded maps) */
+    int32_t dyn_cap;            /* dynamic slots per env (>= max n_dyn over the loaded maps) */
+    int32_t n_maps;
+    double*  nin_f;             /* [NPPSIM_NF][N] */
+    int32_t* nin_i;             /* [NPPSIM_NI][N] */
+    int32_t* env_i;             /* [NPPSIM_NENV][N] */
+    uint8_t* ent_flag;          /* [ent_cap][N]  per-entity byte: active / state / closed bits */
+    double*  dyn_f;             /* [dyn_cap*4][N] */
+    int32_t* dyn_i;             /* [dyn_cap*3][N] */
+    const int32_t*  env_map;    /* [N] index into map_off */
+    const uint8_t*  map_blob;   /* all compiled maps, concatenated (device) */
+    const int64_t*  map_off;    /* [n_maps] byte offset of each map inside map_blob (device) */
+} nppsim_state_t;
+
+int         nppsim_version(void);
+const char* nppsim_last_error(void);
+
+/* ---- host side: Simulator.load's static part (nsim.py:51-56, map_loader.py:18-145) ---------
+ * map_data is the map_loader format as float64 (generators emit non-integer coordinates):
+ * [184:1150] 42x23 tile ids, [1156] exit-door count, [1200] death-ball count,
+ * [1231],[1232] spawn, [1235:] entity records.  Writes one relocatable blob
+ * (nclone_b200/csrc/map_blob.h) to `out`; upload it anywhere 16-byte aligned. */
+int64_t nppsim_map_blob_bound(int32_t map_len);
+int     nppsim_compile_map(const double* map_data, int32_t map_len, uint8_t* out, int64_t out_cap,
+                           int64_t* out_used, int32_t* n_entities, int32_t* n_dyn_slots);
+
+/* ---- device side ------------------------------------------------------------------------
+ * nppsim_reset: Simulator.load()'s dynamic part / reset() (mode 0, nsim.py:62-76) or
+ * fast_reset() (mode 1, nsim.py:78-140) for every env whose mask byte is non-zero
+ * (mask == NULL: all envs).  mask is a device pointer. */
+int nppsim_reset(const nppsim_state_t* st, const uint8_t* mask, int32_t mode, void* stream);
+
+/* nppsim_step: Simulator.tick (nsim.py:221-292) n_ticks times for every env in one launch.
+ *   hor, jump   device int8, hor in {-1,0,1}, jump in {0,1}; input_ticks == 1: one value per
+ *               env held for all ticks ([N]); input_ticks == n_ticks: per-tick rows ([n_ticks][N]).
+ *   tick_limit  optional device int32 [N]: env i runs min(n_ticks, tick_limit[i]) ticks
+ *               (ragged replay batches); NULL = no limit.
+ *   stop_on_terminal  non-zero: an env stops after the tick that leaves it won or dead
+ *               (gym_environment/base_environment.py:605-609 frame-skip early exit).
+ *   frames_executed   optional device int32 [N]: ticks actually run. */
+int nppsim_step(const nppsim_state_t* st, const int8_t* hor, const int8_t* jump, int32_t input_ticks,
+                int32_t n_ticks, const int32_t* tick_limit, int32_t stop_on_terminal,
+                int32_t* frames_executed, void* stream);
+
+/* nppsim_step_actions: same, inputs given as Discrete(6) actions [N] (uint8) held for n_ticks,
+ * decoded with ACTION_TO_INPUTS (action_replayer.py:30-37 == base_environment.py:384-402). */
+int nppsim_step_actions(const nppsim_state_t* st, const uint8_t* actions, int32_t n_ticks,
+                        int32_t stop_on_terminal, int32_t* frames_executed, void* stream);
+
+/* nppsim_step_host: the call a host-resident caller makes (one NppEnvironment.step worth of
+ * physics for the batch): copies `actions_host` [N] to `actions_dev`, runs nppsim_step_actions,
+ * and copies back ninja (xpos, ypos, xspeed, yspeed) [4][N] doubles and the state byte [N]
+ * into host buffers, then synchronises the stream. */
+int nppsim_step_host(const nppsim_state_t* st, const uint8_t* actions_host, uint8_t* actions_dev,
+                     int32_t n_ticks, int32_t stop_on_terminal, double* pos_vel_host, int32_t* state_host,
+                     void* stream);
+
+/* Kernel launch count since library load (bench.py's gpu_launches claim). */
+int64_t nppsim_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,15 @@
+"""nclone_b200: B200-native batched N++ physics (drop-in for nclone's nsim.Simulator.tick path).
+
+Only the hot path lives here: csrc/ (CUDA kernels + C ABI + host map compiler) and the
+host-side mirror of the reference's Simulator / NPlayHeadless interface."""
+from .fields import ACTION_TO_INPUTS  # noqa: F401
+
+
+def __getattr__(name):
+    if name == "BatchedSimulator":
+        from .batched_simulator import BatchedSimulator
+        return BatchedSimulator
+    if name in ("parse_replay", "decode_input_byte"):
+        from . import replay
+        return getattr(replay, name)
+    raise AttributeError(name)

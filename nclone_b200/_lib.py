@@ -1,0 +1,58 @@
+"""ctypes binding of libnppsim.so (include/nppsim.h).  There is no fallback: if the CUDA
+library cannot be built or loaded, importing callers get an exception."""
+import ctypes as C
+import os
+
+from . import build as _build
+
+_lib = None
+
+
+class NppsimState(C.Structure):
+    """nppsim_state_t"""
+    _fields_ = [
+        ("n_envs", C.c_int32), ("ent_cap", C.c_int32), ("dyn_cap", C.c_int32), ("n_maps", C.c_int32),
+        ("nin_f", C.c_void_p), ("nin_i", C.c_void_p), ("env_i", C.c_void_p), ("ent_flag", C.c_void_p),
+        ("dyn_f", C.c_void_p), ("dyn_i", C.c_void_p), ("env_map", C.c_void_p), ("map_blob", C.c_void_p),
+        ("map_off", C.c_void_p),
+    ]
+
+
+EXPORTS = (
+    "nppsim_version", "nppsim_last_error", "nppsim_map_blob_bound", "nppsim_compile_map",
+    "nppsim_reset", "nppsim_step", "nppsim_step_actions", "nppsim_step_host", "nppsim_launch_count",
+)
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = _build.LIB
+    if _build.needs_build():
+        try:
+            _build.build()
+        except Exception:
+            if not os.path.exists(path):
+                raise
+    L = C.CDLL(path)
+    vp, i32, i64 = C.c_void_p, C.c_int32, C.c_int64
+    L.nppsim_version.restype = C.c_int
+    L.nppsim_last_error.restype = C.c_char_p
+    L.nppsim_map_blob_bound.argtypes = [i32]; L.nppsim_map_blob_bound.restype = i64
+    L.nppsim_compile_map.argtypes = [vp, i32, vp, i64, C.POINTER(i64), C.POINTER(i32), C.POINTER(i32)]
+    L.nppsim_compile_map.restype = C.c_int
+    st = C.POINTER(NppsimState)
+    L.nppsim_reset.argtypes = [st, vp, i32, vp]; L.nppsim_reset.restype = C.c_int
+    L.nppsim_step.argtypes = [st, vp, vp, i32, i32, vp, i32, vp, vp]; L.nppsim_step.restype = C.c_int
+    L.nppsim_step_actions.argtypes = [st, vp, i32, i32, vp, vp]; L.nppsim_step_actions.restype = C.c_int
+    L.nppsim_step_host.argtypes = [st, vp, vp, i32, i32, vp, vp, vp]; L.nppsim_step_host.restype = C.c_int
+    L.nppsim_launch_count.restype = i64
+    _lib = L
+    return L
+
+
+def check(rc):
+    if rc != 0:
+        msg = lib().nppsim_last_error()
+        raise RuntimeError(f"nppsim error {rc}: {msg.decode() if msg else '?'}")

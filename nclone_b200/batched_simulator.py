@@ -1,0 +1,331 @@
+"""BatchedSimulator: N independent nclone simulators advanced by one CUDA launch.
+
+Host-side mirror of the reference's ``nsim.Simulator`` (/root/reference/nclone/nsim.py:11-292)
+and of the getters of ``nplay_headless.NPlayHeadless`` (nplay_headless.py:401-455, 546-720),
+batched: every method that takes/returns a scalar there takes/returns an array over envs here.
+PyTorch only owns device memory and streams; all physics runs in libnppsim.so through the
+C ABI of include/nppsim.h.  There is no CPU path: construction fails without a CUDA device.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import fields as FD
+from ._lib import lib, check, NppsimState
+from .map_compile import compile_map, content_key, MapTables
+
+
+class BatchedSimulator:
+    def __init__(self, n_envs, device="cuda:0"):
+        if not torch.cuda.is_available():
+            raise RuntimeError("BatchedSimulator needs a CUDA device (there is no CPU fallback)")
+        self.n_envs = int(n_envs)
+        self.device = torch.device(device)
+        self.L = lib()
+        self.maps = []          # MapTables per distinct level
+        self._keys = {}
+        self._state = None
+        self.env_map_host = None
+
+    # ------------------------------------------------------------------ Simulator.load (nsim.py:51-56)
+    def load_maps(self, map_datas, env_to_map=None):
+        """map_datas: sequence of map_data rows (map_loader format, ints or floats, any length
+        >= 1235); env_to_map: for each env the index into map_datas (default: env i -> map i % M).
+        Identical levels are compiled and stored once.  All envs are reset (mode 'reset')."""
+        N = self.n_envs
+        M = len(map_datas)
+        if env_to_map is None:
+            env_to_map = np.arange(N) % M
+        env_to_map = np.asarray(env_to_map, dtype=np.int64)
+        if env_to_map.shape != (N,) or env_to_map.min() < 0 or env_to_map.max() >= M:
+            raise ValueError("env_to_map must hold one valid map index per env")
+        self.maps, self._keys = [], {}
+        remap = np.zeros(M, dtype=np.int32)
+        blobs = []
+        for m, md in enumerate(map_datas):
+            key = content_key(md)
+            if key not in self._keys:
+                blob = compile_map(md)
+                self._keys[key] = len(blobs)
+                blobs.append(blob)
+                self.maps.append(MapTables(blob))
+            remap[m] = self._keys[key]
+        offs = np.zeros(len(blobs), dtype=np.int64)
+        total = 0
+        for k, b in enumerate(blobs):
+            offs[k] = total
+            total += (len(b) + 255) & ~255
+        host_blob = np.zeros(max(total, 256), dtype=np.uint8)
+        for k, b in enumerate(blobs):
+            host_blob[offs[k]:offs[k] + len(b)] = np.frombuffer(b, dtype=np.uint8)
+        dev = self.device
+        self.map_blob = torch.from_numpy(host_blob).to(dev)
+        self.map_off = torch.from_numpy(offs).to(dev)
+        self.env_map_host = remap[env_to_map].astype(np.int32)
+        self.env_map = torch.from_numpy(self.env_map_host).to(dev)
+        self.ent_cap = max(1, max(t.n_ent for t in self.maps))
+        self.dyn_cap = max(1, max(t.n_dyn for t in self.maps))
+        self.nin_f = torch.zeros((FD.NF, N), dtype=torch.float64, device=dev)
+        self.nin_i = torch.zeros((FD.NI, N), dtype=torch.int32, device=dev)
+        self.env_i = torch.zeros((FD.NENV, N), dtype=torch.int32, device=dev)
+        self.ent_flag = torch.zeros((self.ent_cap, N), dtype=torch.uint8, device=dev)
+        self.dyn_f = torch.zeros((self.dyn_cap * 4, N), dtype=torch.float64, device=dev)
+        self.dyn_i = torch.zeros((self.dyn_cap * 3, N), dtype=torch.int32, device=dev)
+        self.frames_executed = torch.zeros(N, dtype=torch.int32, device=dev)
+        self._actions_dev = torch.zeros(N, dtype=torch.uint8, device=dev)
+        st = NppsimState()
+        st.n_envs, st.ent_cap, st.dyn_cap, st.n_maps = N, self.ent_cap, self.dyn_cap, len(blobs)
+        st.nin_f, st.nin_i, st.env_i = self.nin_f.data_ptr(), self.nin_i.data_ptr(), self.env_i.data_ptr()
+        st.ent_flag, st.dyn_f, st.dyn_i = self.ent_flag.data_ptr(), self.dyn_f.data_ptr(), self.dyn_i.data_ptr()
+        st.env_map, st.map_blob, st.map_off = self.env_map.data_ptr(), self.map_blob.data_ptr(), self.map_off.data_ptr()
+        self._state = st
+        self.reset()
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _need_maps(self):
+        if self._state is None:
+            raise RuntimeError("load_maps() first")
+
+    # ------------------------------------------------------------------ Simulator.reset / fast_reset (nsim.py:62-140)
+    def reset(self, mask=None, mode="reset"):
+        """mode 'reset' = Simulator.load/reset on a fresh Simulator; 'fast' = Simulator.fast_reset."""
+        self._need_maps()
+        m = {"reset": 0, "fast": 1}[mode]
+        ptr = None
+        if mask is not None:
+            mask = torch.as_tensor(mask, device=self.device).to(torch.uint8).contiguous()
+            ptr = C.c_void_p(mask.data_ptr())
+        with torch.cuda.device(self.device):
+            check(self.L.nppsim_reset(C.byref(self._state), ptr, m, self._stream()))
+
+    def fast_reset(self, mask=None):
+        self.reset(mask, mode="fast")
+
+    # ------------------------------------------------------------------ Simulator.tick (nsim.py:221-292)
+    def _dev_i8(self, x):
+        t = torch.as_tensor(x)
+        if t.dtype != torch.int8 or t.device != self.device:
+            t = t.to(device=self.device, dtype=torch.int8)
+        return t.contiguous()
+
+    def tick(self, hor_input, jump_input, n_ticks=1, tick_limit=None, stop_on_terminal=False):
+        """hor_input / jump_input: [N] (held for n_ticks) or [n_ticks, N] (one row per tick)."""
+        self._need_maps()
+        hor, jump = self._dev_i8(hor_input), self._dev_i8(jump_input)
+        if hor.shape != jump.shape:
+            raise ValueError("hor_input and jump_input shapes differ")
+        if hor.dim() == 1:
+            input_ticks = 1
+        else:
+            input_ticks = hor.shape[0]
+            if input_ticks != n_ticks:
+                raise ValueError("per-tick inputs need n_ticks rows")
+        if hor.shape[-1] != self.n_envs:
+            raise ValueError("inputs need one column per env")
+        lim = None
+        if tick_limit is not None:
+            tick_limit = torch.as_tensor(tick_limit).to(device=self.device, dtype=torch.int32).contiguous()
+            lim = C.c_void_p(tick_limit.data_ptr())
+        with torch.cuda.device(self.device):
+            check(self.L.nppsim_step(C.byref(self._state), C.c_void_p(hor.data_ptr()), C.c_void_p(jump.data_ptr()),
+                                     input_ticks, int(n_ticks), lim, int(bool(stop_on_terminal)),
+                                     C.c_void_p(self.frames_executed.data_ptr()), self._stream()))
+        return self.frames_executed
+
+    def step(self, actions, frame_skip=4, stop_on_terminal=True):
+        """Discrete(6) actions [N] (device uint8 tensor preferred) held for frame_skip ticks with the
+        reference's early exit on win/death (gym_environment/base_environment.py:535-609)."""
+        self._need_maps()
+        a = torch.as_tensor(actions)
+        if a.dtype != torch.uint8 or a.device != self.device:
+            a = a.to(device=self.device, dtype=torch.uint8)
+        a = a.contiguous()
+        with torch.cuda.device(self.device):
+            check(self.L.nppsim_step_actions(C.byref(self._state), C.c_void_p(a.data_ptr()), int(frame_skip),
+                                             int(bool(stop_on_terminal)), C.c_void_p(self.frames_executed.data_ptr()),
+                                             self._stream()))
+        return self.frames_executed
+
+    def step_host(self, actions_host, pos_vel_host, state_host, frame_skip=4, stop_on_terminal=True):
+        """Host-buffer entry point (nppsim_step_host): numpy uint8 actions in, pos/vel [4,N] f64 and
+        state [N] i32 out; copies are part of the call and the stream is synchronised on return."""
+        self._need_maps()
+        with torch.cuda.device(self.device):
+            check(self.L.nppsim_step_host(C.byref(self._state), C.c_void_p(actions_host.ctypes.data),
+                                          C.c_void_p(self._actions_dev.data_ptr()), int(frame_skip),
+                                          int(bool(stop_on_terminal)), C.c_void_p(pos_vel_host.ctypes.data),
+                                          C.c_void_p(state_host.ctypes.data), self._stream()))
+
+    # ------------------------------------------------------------------ NPlayHeadless getters, batched
+    def _f(self, name):
+        return self.nin_f[FD.F[name]]
+
+    def _i(self, name):
+        return self.nin_i[FD.I[name]]
+
+    def ninja_position(self):            # nplay_headless.py:415-416
+        return self.nin_f[0], self.nin_f[1]
+
+    def ninja_velocity(self):            # :418-419
+        return self.nin_f[2], self.nin_f[3]
+
+    def ninja_velocity_old(self):        # :421-423
+        return self._f("xspeed_old"), self._f("yspeed_old")
+
+    def ninja_state(self):
+        return self._i("state")
+
+    def ninja_has_won(self):             # :401-402
+        return self._i("state") == 8
+
+    def ninja_has_died(self):            # :404-405
+        s = self._i("state")
+        return (s == 6) | (s == 7)
+
+    def ninja_death_cause(self):         # :407-413 (0 None, 1 "mine", 2 "terminal_impact")
+        return self._i("death_cause")
+
+    def ninja_airborn_old(self):
+        return self._i("airborn_old")
+
+    def ninja_floor_normal(self):
+        return self._f("floor_normalized_x"), self._f("floor_normalized_y")
+
+    def ninja_ceiling_normal(self):
+        return self._f("ceiling_normalized_x"), self._f("ceiling_normalized_y")
+
+    def ninja_last_jump_was_buffered(self):
+        return self._i("last_jump_was_buffered")
+
+    def get_ninja_terminal_impact(self):
+        return self._i("terminal_impact")
+
+    def frame(self):
+        return self._i("frame")
+
+    def events(self, clear=True):
+        """Per-env NPPSIM_EV_* bits raised since the last clear (replaces the reference's
+        sim.gym_env.invalidate_switch_cache() callback, entity_exit_switch.py:128-129)."""
+        ev = self.env_i[FD.ENV_EVENTS].clone()
+        if clear:
+            self.env_i[FD.ENV_EVENTS].zero_()
+        return ev
+
+    def switch_frame(self):
+        return self.env_i[FD.ENV_SWFRAME]
+
+    def _exit_slots(self):
+        """Per env: entity id / dyn slot of the LAST exit switch in entity_dic[3]
+        (nplay_headless.py:546-564 iterates reversed) and of its parent door; -1 if none."""
+        if getattr(self, "_exit_cache", None) is None or self._exit_cache[0] is not self.env_map:
+            sw_id = np.full(len(self.maps), -1); sw_slot = sw_id.copy(); dr_slot = sw_id.copy()
+            for k, t in enumerate(self.maps):
+                ids = np.nonzero(t.ents["kind"] == FD.K_EXIT_SWITCH)[0]
+                if len(ids):
+                    e = t.ents[ids[-1]]
+                    sw_id[k], sw_slot[k] = ids[-1], e["dyn"]
+                    dr_slot[k] = t.ents[e["aux"]]["dyn"]
+            em = self.env_map_host
+            dev = self.device
+            self._exit_cache = (self.env_map, torch.from_numpy(sw_id[em]).to(dev), torch.from_numpy(sw_slot[em]).to(dev),
+                                torch.from_numpy(dr_slot[em]).to(dev))
+        return self._exit_cache[1:]
+
+    def exit_switch_activated(self):     # nplay_headless.py:566-575 (no switch -> True)
+        sw_id, _, _ = self._exit_slots()
+        ar = torch.arange(self.n_envs, device=self.device)
+        fl = self.ent_flag[sw_id.clamp(min=0), ar]
+        return (sw_id < 0) | ((fl & FD.FL_ACTIVE) == 0)
+
+    def _slot_xy(self, slot):
+        ar = torch.arange(self.n_envs, device=self.device)
+        s = slot.clamp(min=0)
+        x = self.dyn_f[s * 4, ar]; y = self.dyn_f[s * 4 + 1, ar]
+        zero = torch.zeros_like(x)
+        return torch.where(slot >= 0, x, zero), torch.where(slot >= 0, y, zero)
+
+    def exit_switch_position(self):      # :577-592 ((0,0) when absent)
+        return self._slot_xy(self._exit_slots()[1])
+
+    def exit_door_position(self):        # :601-616
+        return self._slot_xy(self._exit_slots()[2])
+
+    # ------------------------------------------------------------------ host-side full state (parity tests)
+    def canonical_state(self, env_ids=None):
+        """Host copy of the full canonical record (ninja 31 doubles + 27 ints, and one row per
+        entity in entity_dic order: doubles xpos,ypos,a0,a1; ints type,index,active,cell_x,cell_y,s0,s1,
+        cell_rank) for the given envs -- the record the reference / oracle produce, for bit comparison."""
+        self._need_maps()
+        torch.cuda.synchronize(self.device)
+        ids = np.arange(self.n_envs) if env_ids is None else np.asarray(env_ids)
+        tid = torch.from_numpy(ids).to(self.device)
+        nf = self.nin_f[:, tid].cpu().numpy().T.copy()
+        ni = self.nin_i[:, tid].cpu().numpy().T.astype(np.int64)
+        fl = self.ent_flag[:, tid].cpu().numpy()
+        df = self.dyn_f[:, tid].cpu().numpy()
+        di = self.dyn_i[:, tid].cpu().numpy()
+        order = self.env_i[FD.ENV_ORDER][tid].cpu().numpy()
+        out = []
+        for k, env in enumerate(ids):
+            t = self.maps[self.env_map_host[env]]
+            out.append((nf[k], ni[k]) + _entity_rows(t, fl[:, k], df[:, k], di[:, k], int(order[k])))
+        return out
+
+    def launch_count(self):
+        return int(self.L.nppsim_launch_count())
+
+
+def _entity_rows(t, fl, df, di, order_mode):
+    """Rebuild the reference's per-entity attributes from one env's flag / slot arrays."""
+    E = t.n_ent
+    ef = np.zeros((E, 4)); ei = np.zeros((E, 8), dtype=np.int64)
+    cell = np.zeros(E, dtype=np.int64); stamp = np.zeros(E, dtype=np.int64); in_grid = np.ones(E, dtype=bool)
+    for e in range(E):
+        s = t.ents[e]
+        kind, slot, f = int(s["kind"]), int(s["dyn"]), int(fl[e])
+        x, y, a0, a1, s0, s1 = float(s["x"]), float(s["y"]), 0.0, 0.0, 0, 0
+        c = int(s["cell"]); st = e if order_mode else int(s["load_order"])
+        active = 1 if f & FD.FL_ACTIVE else 0
+        roaming = slot >= 0 and kind != FD.K_DOOR_REGULAR
+        if roaming:
+            x, y = df[slot * 4], df[slot * 4 + 1]
+            c = int(di[slot * 3]); st = int(di[slot * 3 + 1])
+        if kind == FD.K_MINE:
+            s0 = f & FD.FL_MINE
+        elif kind == FD.K_EXIT:
+            s0 = 1 if f & FD.FL_CLOSED else 0
+            if c < 0:
+                in_grid[e] = False
+                c = int(di[slot * 3 + 2])
+        elif kind == FD.K_DOOR_REGULAR:
+            s0 = 1 if f & FD.FL_CLOSED else 0
+            s1 = int(di[slot * 3 + 2]) & 255
+        elif kind in (FD.K_DOOR_LOCKED, FD.K_DOOR_TRAP):
+            s0 = 1 if f & FD.FL_CLOSED else 0
+        elif kind in (FD.K_BOUNCE, FD.K_DEATH_BALL):
+            a0, a1 = df[slot * 4 + 2], df[slot * 4 + 3]
+        elif kind in (FD.K_DRONE_ZAP, FD.K_MINI_DRONE):
+            s0 = (f & FD.FL_ST) >> FD.FL_ST_SHIFT
+            a0, a1 = df[slot * 4 + 2], df[slot * 4 + 3]
+        elif kind == FD.K_THWUMP:
+            s0 = (f & FD.FL_ST) >> FD.FL_ST_SHIFT
+            s0 = -1 if s0 == 3 else s0
+        elif kind == FD.K_BOOST:
+            s0 = 1 if f & FD.FL_TOUCH else 0
+        elif kind == FD.K_SHWUMP:
+            s0 = (f & FD.FL_ST) >> FD.FL_ST_SHIFT
+            s1 = 1 if f & FD.FL_ACTIVATED else 0
+            a0, a1 = df[slot * 4 + 2], df[slot * 4 + 3]
+        cell[e], stamp[e] = c, st
+        ef[e] = (x, y, a0, a1)
+        ei[e, :7] = (int(s["type"]), int(s["index"]), active, c // 25, c % 25, s0, s1)
+    for e in range(E):
+        if not in_grid[e]:
+            ei[e, 7] = -1
+        else:
+            same = in_grid & (cell == cell[e])
+            ei[e, 7] = int(np.count_nonzero(stamp[same] < stamp[e]))
+    return ef, ei

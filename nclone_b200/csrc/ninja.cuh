@@ -1,0 +1,318 @@
+// ninja.cuh -- the ninja's per-frame update.  Reference: /root/reference/nclone/ninja.py.
+#pragma once
+#include "entities.cuh"
+
+DEV void ninja_integrate(Nin& n) {                                       // ninja.py:198-206
+    n.f[F_XSPEED] *= n.f[F_DRAG];
+    n.f[F_YSPEED] *= n.f[F_DRAG];
+    n.f[F_YSPEED] += n.f[F_GRAVITY];
+    n.f[F_XPOS_OLD] = n.f[F_XPOS]; n.f[F_YPOS_OLD] = n.f[F_YPOS];
+    n.f[F_XPOS] += n.f[F_XSPEED]; n.f[F_YPOS] += n.f[F_YSPEED];
+}
+
+// ninja.py:208-222.  The reference caches the gathered entity list for the four substeps; the
+// list cannot change in between (no grid_move / activation happens during ninja physics), so it is
+// enough to remember where it was gathered and whether it holds anything physical at all.
+DEV bool ninja_pre_collision(Nin& n, Ctx& c, double& gx, double& gy) {
+    n.f[F_XSPEED_OLD] = n.f[F_XSPEED]; n.f[F_YSPEED_OLD] = n.f[F_YSPEED];
+    n.i[I_FLOOR_COUNT] = 0; n.i[I_CEILING_COUNT] = 0;                   // wall_count stays 0 forever
+    n.f[F_FLOOR_NX] = 0; n.f[F_FLOOR_NY] = 0; n.f[F_CEIL_NX] = 0; n.f[F_CEIL_NY] = 0;
+    n.i[I_CRUSHABLE] = 0;
+    n.f[F_XCRUSH] = 0; n.f[F_YCRUSH] = 0; n.f[F_CRUSH_LEN] = 0;
+    gx = n.f[F_XPOS]; gy = n.f[F_YPOS];
+    int nphys = 0;
+    gather_entities(c, gx, gy, [&](int id) { if (is_physical_kind(ent_kind(c, id))) nphys++; });
+    return nphys > 0;
+}
+
+__device__ __noinline__ void ninja_collide_vs_objects(Nin& n, Ctx& c, double gx, double gy) {   // ninja.py:224-267
+    gather_entities(c, gx, gy, [&](int id) {
+        if (!is_physical_kind(ent_kind(c, id))) return;
+        EntS e = ld_ent(c, id);
+        double depen_x, depen_y, depen_len;
+        if (!ent_physical_collision(n, c, id, e, depen_x, depen_y, depen_len)) return;
+        double pop_x = depen_x * depen_len, pop_y = depen_y * depen_len;
+        n.f[F_XPOS] += pop_x; n.f[F_YPOS] += pop_y;
+        if (e.kind != NPP_K_BOUNCE) { n.f[F_XCRUSH] += pop_x; n.f[F_YCRUSH] += pop_y; n.f[F_CRUSH_LEN] += depen_len; }
+        if (e.kind == NPP_K_THWUMP) n.i[I_CRUSHABLE] = 1;
+        if (e.kind == NPP_K_BOUNCE || e.kind == NPP_K_THWUMP || e.kind == NPP_K_SHWUMP) { n.f[F_XSPEED] += pop_x; n.f[F_YSPEED] += pop_y; }
+        if (e.kind == NPP_K_ONE_WAY) {
+            double xspeed_new = (n.f[F_XSPEED] * depen_y - n.f[F_YSPEED] * depen_x) * depen_y;
+            // axis-aligned normals are Python ints (physics.py:322-331): -(int 0) is 0, not -0.0
+            double yspeed_new = (n.f[F_XSPEED] * depen_y - n.f[F_YSPEED] * depen_x) * (depen_x == 0 ? 0.0 : -depen_x);
+            n.f[F_XSPEED] = xspeed_new; n.f[F_YSPEED] = yspeed_new;
+        }
+        if (depen_y >= -0.0001) { n.i[I_CEILING_COUNT] += 1; n.f[F_CEIL_NX] += depen_x; n.f[F_CEIL_NY] += depen_y; }
+        else { n.i[I_FLOOR_COUNT] += 1; n.f[F_FLOOR_NX] += depen_x; n.f[F_FLOOR_NY] += depen_y; }
+    });
+}
+
+DEV void ninja_collide_vs_tiles(Nin& n, const Ctx& c) {                  // ninja.py:269-379
+    double dx = n.f[F_XPOS] - n.f[F_XPOS_OLD], dy = n.f[F_YPOS] - n.f[F_YPOS_OLD];
+    double time = sweep_circle_vs_tiles(c, n.f[F_XPOS_OLD], n.f[F_YPOS_OLD], dx, dy, NINJA_RADIUS * 0.5);
+    double xpos = n.f[F_XPOS_OLD] + time * dx;       // recomputed even when time == 1 (not a no-op in fp)
+    double ypos = n.f[F_YPOS_OLD] + time * dy;
+    // segments are gathered once, around the post-sweep position (ninja.py:282-285)
+    const double gx1 = xpos - NINJA_RADIUS, gy1 = ypos - NINJA_RADIUS, gx2 = xpos + NINJA_RADIUS, gy2 = ypos + NINJA_RADIUS;
+    double xspeed = n.f[F_XSPEED], yspeed = n.f[F_YSPEED];
+    for (int it = 0; it < 32; it++) {
+        double a, b;
+        int result = get_single_closest_point(c, gx1, gy1, gx2, gy2, xpos, ypos, NINJA_RADIUS, a, b);
+        if (result == 0) break;
+        dx = xpos - a; dy = ypos - b;
+        if (fabs(dx) <= 0.0000001) {                  // ninja.py:312-318 band-aid
+            dx = 0;
+            if (xpos == 50.51197510492316 || xpos == 49.23232124849253) dx = -0x1p-47;
+            if (xpos == 49.153536108584795) dx = 0x1p-47;
+        }
+        double dist_sq = dx * dx + dy * dy;
+        if (dist_sq < 1e-16) break;
+        double dist = sqrt(dist_sq);
+        double depen_len = NINJA_RADIUS - dist * result;
+        if (depen_len < 0.0000001) break;
+        double inv_dist = 1.0 / dist;
+        double norm_dx = dx * inv_dist, norm_dy = dy * inv_dist;
+        double depen_x = norm_dx * depen_len, depen_y = norm_dy * depen_len;
+        xpos += depen_x; ypos += depen_y;
+        n.f[F_XCRUSH] += depen_x; n.f[F_YCRUSH] += depen_y; n.f[F_CRUSH_LEN] += depen_len;
+        double dot_product = xspeed * dx + yspeed * dy;
+        if (dot_product < 0) {
+            double cross_product = xspeed * dy - yspeed * dx;
+            double inv_dist_sq = inv_dist * inv_dist;
+            xspeed = cross_product * inv_dist_sq * dy;
+            // dx == 0 only via the band-aid's `dx = 0` (a Python int): -(int 0) is 0, not -0.0
+            yspeed = cross_product * inv_dist_sq * (dx == 0 ? 0.0 : -dx);
+        }
+        if (dy >= -0.0001) { n.i[I_CEILING_COUNT] += 1; n.f[F_CEIL_NX] += norm_dx; n.f[F_CEIL_NY] += norm_dy; }
+        else { n.i[I_FLOOR_COUNT] += 1; n.f[F_FLOOR_NX] += norm_dx; n.f[F_FLOOR_NY] += norm_dy; }
+    }
+    n.f[F_XPOS] = xpos; n.f[F_YPOS] = ypos; n.f[F_XSPEED] = xspeed; n.f[F_YSPEED] = yspeed;
+}
+
+DEV void ninja_post_collision(Nin& n, Ctx& c) {                          // ninja.py:381-537
+    double wall_normal = 0;
+    gather_entities(c, n.f[F_XPOS], n.f[F_YPOS], [&](int id) {
+        if (ent_kind(c, id) != NPP_K_BOOST) ent_logical_collision(n, c, id, wall_normal);   // boost pads are not logical-collidable
+    });
+    commit_pending_doors(c);
+    const double rad = NINJA_RADIUS + 0.1;
+    const double xpos = n.f[F_XPOS], ypos = n.f[F_YPOS];
+    query_region(c, xpos - rad, ypos - rad, xpos + rad, ypos + rad, [&](uint32_t s) {
+        bool back; double a, b;
+        seg_closest_point(s, xpos, ypos, back, a, b);
+        double dx = xpos - a, dy = ypos - b;
+        double dist = sqrt(SQ(dx) + SQ(dy));
+        if (fabs(dy) < 0.00001 && 0 < dist && dist <= rad) wall_normal += dx / dist;
+        return true;
+    });
+    n.i[I_AIRBORN_OLD] = n.i[I_AIRBORN];
+    n.i[I_AIRBORN] = 1; n.i[I_WALLED] = 0;
+    if (wall_normal != 0) { n.i[I_WALLED] = 1; n.f[F_WALL_NORMAL] = wall_normal / fabs(wall_normal); }
+    if (n.i[I_FLOOR_COUNT] > 0) {
+        n.i[I_AIRBORN] = 0;
+        double floor_scalar = sqrt(SQ(n.f[F_FLOOR_NX]) + SQ(n.f[F_FLOOR_NY]));
+        if (floor_scalar == 0) { n.f[F_FNX] = 0; n.f[F_FNY] = -1; }
+        else { n.f[F_FNX] = n.f[F_FLOOR_NX] / floor_scalar; n.f[F_FNY] = n.f[F_FLOOR_NY] / floor_scalar; }
+        if (n.i[I_STATE] != 8 && n.i[I_AIRBORN_OLD]) {
+            double impact_vel = -(n.f[F_FNX] * n.f[F_XSPEED_OLD] + n.f[F_FNY] * n.f[F_YSPEED_OLD]);
+            if (impact_vel > MAX_SURVIVABLE_IMPACT - 4.0 / 3 * fabs(n.f[F_FNY])) {
+                n.f[F_XSPEED] = n.f[F_XSPEED_OLD]; n.f[F_YSPEED] = n.f[F_YSPEED_OLD];
+                ninja_kill(n, c, n.f[F_XPOS], n.f[F_YPOS], n.f[F_XSPEED] * 0.5, n.f[F_YSPEED] * 0.5, 2);
+                n.i[I_TERMINAL_IMPACT] = 1;
+            }
+        }
+    }
+    if (n.i[I_AIRBORN]) n.i[I_FRAMES_AIRBORNE] += 1; else n.i[I_FRAMES_AIRBORNE] = 0;
+    if (!n.i[I_AIRBORN]) n.i[I_CONSEC_FLOOR] += 1; else n.i[I_CONSEC_FLOOR] = 0;
+    if (n.i[I_WALLED]) n.i[I_CONSEC_WALL] += 1; else n.i[I_CONSEC_WALL] = 0;
+    if (n.i[I_CEILING_COUNT] > 0) {
+        double ceiling_scalar = sqrt(SQ(n.f[F_CEIL_NX]) + SQ(n.f[F_CEIL_NY]));
+        if (ceiling_scalar == 0) { n.f[F_CNX] = 0; n.f[F_CNY] = 1; }
+        else { n.f[F_CNX] = n.f[F_CEIL_NX] / ceiling_scalar; n.f[F_CNY] = n.f[F_CEIL_NY] / ceiling_scalar; }
+        if (n.i[I_STATE] != 8) {
+            double impact_vel = -(n.f[F_CNX] * n.f[F_XSPEED_OLD] + n.f[F_CNY] * n.f[F_YSPEED_OLD]);
+            if (impact_vel > MAX_SURVIVABLE_IMPACT - 4.0 / 3 * fabs(n.f[F_CNY])) {
+                n.f[F_XSPEED] = n.f[F_XSPEED_OLD]; n.f[F_YSPEED] = n.f[F_YSPEED_OLD];
+                ninja_kill(n, c, n.f[F_XPOS], n.f[F_YPOS], n.f[F_XSPEED] * 0.5, n.f[F_YSPEED] * 0.5, 2);
+                n.i[I_TERMINAL_IMPACT] = 1;
+            }
+        }
+    }
+    if (n.i[I_CRUSHABLE] && n.f[F_CRUSH_LEN] > 0) {
+        if (sqrt(SQ(n.f[F_XCRUSH]) + SQ(n.f[F_YCRUSH])) / n.f[F_CRUSH_LEN] < MIN_SURVIVABLE_CRUSHING)
+            ninja_kill(n, c, n.f[F_XPOS], n.f[F_YPOS], 0, 0, 0);
+    }
+}
+
+DEV void ninja_floor_jump(Nin& n, bool was_buffered) {                   // ninja.py:539-579
+    n.i[I_JUMP_BUFFER] = -1; n.i[I_FLOOR_BUFFER] = -1; n.i[I_LP_BUFFER] = -1;
+    if (was_buffered) n.i[I_LAST_JUMP_BUFFERED] = 1;
+    n.i[I_STATE] = 3;
+    n.f[F_GRAVITY] = GRAVITY_JUMP;
+    double jx, jy;
+    if (n.f[F_FNX] == 0) { jx = 0; jy = -2; }
+    else {
+        double dx = n.f[F_FNX], dy = n.f[F_FNY];
+        if (n.f[F_XSPEED] * dx >= 0) {
+            if (n.f[F_XSPEED] * n.i[I_HOR_INPUT] >= 0) { jx = 2.0 / 3 * dx; jy = 2 * dy; }
+            else { jx = 0; jy = -1.4; }
+        } else {
+            if (n.f[F_XSPEED] * n.i[I_HOR_INPUT] > 0) { jx = 0; jy = -1.4; }
+            else { n.f[F_XSPEED] = 0; jx = 2.0 / 3 * dx; jy = 2 * dy; }
+        }
+    }
+    if (n.f[F_YSPEED] > 0) n.f[F_YSPEED] = 0;
+    n.f[F_XSPEED] += jx; n.f[F_YSPEED] += jy;
+    n.f[F_XPOS] += jx; n.f[F_YPOS] += jy;
+    n.i[I_JUMP_DURATION] = 0;
+}
+DEV void ninja_wall_jump(Nin& n, bool was_buffered) {                    // ninja.py:581-608
+    double jx, jy;
+    if (n.i[I_HOR_INPUT] * n.f[F_WALL_NORMAL] < 0 && n.i[I_STATE] == 5) { jx = 2.0 / 3; jy = -1; }
+    else { jx = 1; jy = -1.4; }
+    if (was_buffered) n.i[I_LAST_JUMP_BUFFERED] = 1;
+    n.i[I_STATE] = 3;
+    n.f[F_GRAVITY] = GRAVITY_JUMP;
+    if (n.f[F_XSPEED] * n.f[F_WALL_NORMAL] < 0) n.f[F_XSPEED] = 0;
+    if (n.f[F_YSPEED] > 0) n.f[F_YSPEED] = 0;
+    n.f[F_XSPEED] += jx * n.f[F_WALL_NORMAL]; n.f[F_YSPEED] += jy;
+    n.f[F_XPOS] += jx * n.f[F_WALL_NORMAL]; n.f[F_YPOS] += jy;
+    n.i[I_JUMP_BUFFER] = -1; n.i[I_WALL_BUFFER] = -1; n.i[I_LP_BUFFER] = -1;
+    n.i[I_JUMP_DURATION] = 0;
+}
+DEV void ninja_lp_jump(Nin& n) {                                         // ninja.py:610-626
+    n.i[I_FLOOR_BUFFER] = -1; n.i[I_WALL_BUFFER] = -1; n.i[I_JUMP_BUFFER] = -1; n.i[I_LP_BUFFER] = -1;
+    double boost_scalar = 2 * fabs(n.f[F_XLP]) + 2;
+    if (boost_scalar == 2) boost_scalar = 1.7;
+    n.f[F_XSPEED] += n.f[F_XLP] * boost_scalar * (2.0 / 3);
+    n.f[F_YSPEED] += n.f[F_YLP] * boost_scalar * (2.0 / 3);
+}
+
+DEV void ninja_think(Nin& n) {                                           // ninja.py:849-1059
+    n.i[I_LAST_JUMP_BUFFERED] = 0;
+    if (n.i[I_STATE] != n.i[I_PREVIOUS_STATE]) { n.i[I_STATE_CHANGE_FRAME] = 0; n.i[I_PREVIOUS_STATE] = n.i[I_STATE]; }
+    else n.i[I_STATE_CHANGE_FRAME] += 1;
+    const int hor_input = n.i[I_HOR_INPUT], jump_input = n.i[I_JUMP_INPUT];
+    bool new_jump_check = jump_input ? (n.i[I_JUMP_INPUT_OLD] == 0) : false;
+    n.i[I_JUMP_INPUT_OLD] = jump_input;
+    int b;
+    b = n.i[I_LP_BUFFER];    b = (-1 < b && b < 3) ? b + 1 : -1; n.i[I_LP_BUFFER] = b;    bool in_lp_buffer = -1 < b && b < 4;
+    b = n.i[I_JUMP_BUFFER];  b = (-1 < b && b < 5) ? b + 1 : -1; n.i[I_JUMP_BUFFER] = b;  bool in_jump_buffer = -1 < b && b < 5;
+    b = n.i[I_WALL_BUFFER];  b = (-1 < b && b < 5) ? b + 1 : -1; n.i[I_WALL_BUFFER] = b;  bool in_wall_buffer = -1 < b && b < 5;
+    b = n.i[I_FLOOR_BUFFER]; b = (-1 < b && b < 5) ? b + 1 : -1; n.i[I_FLOOR_BUFFER] = b; bool in_floor_buffer = -1 < b && b < 5;
+    bool just = false;
+    if (new_jump_check && n.i[I_AIRBORN]) { n.i[I_JUMP_BUFFER] = 0; just = true; }
+    if (n.i[I_WALLED]) n.i[I_WALL_BUFFER] = 0;
+    if (!n.i[I_AIRBORN]) n.i[I_FLOOR_BUFFER] = 0;
+    if (jump_input) {
+        bool has_active;
+        if (just) has_active = true;
+        else { int jb = n.i[I_JUMP_BUFFER]; has_active = (-1 < jb && jb < 5) || in_floor_buffer || in_wall_buffer || in_lp_buffer; }
+        n.i[I_JUMP_USELESS] = (n.i[I_AIRBORN] && n.i[I_STATE] != 3 && !has_active) ? 1 : 0;
+    } else n.i[I_JUMP_USELESS] = 0;
+
+    int state = n.i[I_STATE];
+    if (state == 6 || state == 9) return;
+    if (state == 7) { n.i[I_STATE] = 6; return; }                 // think_awaiting_death :1061-1063
+    if (state == 8) { n.f[F_DRAG] = n.i[I_AIRBORN] ? DRAG_REGULAR : DRAG_SLOW; return; }
+
+    if (!n.i[I_AIRBORN]) {
+        double xspeed_new = n.f[F_XSPEED] + GROUND_ACCEL * hor_input;
+        if (fabs(xspeed_new) < MAX_HOR_SPEED) n.f[F_XSPEED] = xspeed_new;
+        if (state > 2) {
+            if (state == 3) n.f[F_GRAVITY] = GRAVITY_FALL;
+            state = (n.f[F_XSPEED] * hor_input <= 0) ? 2 : 1;
+            n.i[I_STATE] = state;
+        }
+        if (!in_jump_buffer && !new_jump_check) {
+            if (state == 2) {
+                double projection = fabs(n.f[F_YSPEED] * n.f[F_FNX] - n.f[F_XSPEED] * n.f[F_FNY]);
+                if (hor_input * projection * n.f[F_XSPEED] > 0) { n.i[I_STATE] = 1; return; }
+                if (projection < 0.1 && n.f[F_FNX] == 0) { n.i[I_STATE] = 0; return; }
+                if (n.f[F_YSPEED] < 0 && n.f[F_FNX] != 0) {
+                    double speed_scalar = sqrt(SQ(n.f[F_XSPEED]) + SQ(n.f[F_YSPEED]));
+                    double fric_force = fabs(n.f[F_XSPEED] * (1 - FRICTION_GROUND) * n.f[F_FNY]);
+                    double fric_force2 = speed_scalar - fric_force * SQ(n.f[F_FNY]);
+                    n.f[F_XSPEED] = n.f[F_XSPEED] / speed_scalar * fric_force2;
+                    n.f[F_YSPEED] = n.f[F_YSPEED] / speed_scalar * fric_force2;
+                    return;
+                }
+                n.f[F_XSPEED] *= FRICTION_GROUND;
+                return;
+            }
+            if (state == 1) {
+                double projection = fabs(n.f[F_YSPEED] * n.f[F_FNX] - n.f[F_XSPEED] * n.f[F_FNY]);
+                if (hor_input * projection * n.f[F_XSPEED] > 0) {
+                    if (hor_input * n.f[F_FNX] >= 0) return;
+                    if (fabs(xspeed_new) < MAX_HOR_SPEED) {
+                        double boost = GROUND_ACCEL / 2 * hor_input;
+                        double xboost = boost * n.f[F_FNY] * n.f[F_FNY];
+                        double yboost = boost * n.f[F_FNY] * -n.f[F_FNX];
+                        n.f[F_XSPEED] += xboost; n.f[F_YSPEED] += yboost;
+                    }
+                    return;
+                }
+                n.i[I_STATE] = 2;
+            } else {
+                if (hor_input) { n.i[I_STATE] = 1; return; }
+                double projection = fabs(n.f[F_YSPEED] * n.f[F_FNX] - n.f[F_XSPEED] * n.f[F_FNY]);
+                if (projection < 0.1) { n.f[F_XSPEED] *= FRICTION_GROUND_SLOW; return; }
+                n.i[I_STATE] = 2;
+            }
+            return;
+        }
+        ninja_floor_jump(n, false);
+        return;
+    } else {
+        double xspeed_new = n.f[F_XSPEED] + AIR_ACCEL * hor_input;
+        if (fabs(xspeed_new) < MAX_HOR_SPEED) n.f[F_XSPEED] = xspeed_new;
+        if (state < 3) { n.i[I_STATE] = 4; return; }
+        if (state == 3) {
+            n.i[I_JUMP_DURATION] += 1;
+            if (!jump_input || n.i[I_JUMP_DURATION] > MAX_JUMP_DURATION) { n.f[F_GRAVITY] = GRAVITY_FALL; n.i[I_STATE] = 4; return; }
+        }
+        if (in_jump_buffer || new_jump_check) {
+            if (n.i[I_WALLED] || in_wall_buffer) { ninja_wall_jump(n, in_wall_buffer); return; }
+            if (in_floor_buffer) { ninja_floor_jump(n, true); return; }
+            if (in_lp_buffer && new_jump_check) { ninja_lp_jump(n); return; }
+        }
+        if (!n.i[I_WALLED]) { if (state == 5) n.i[I_STATE] = 4; }
+        else {
+            if (state == 5) {
+                if (hor_input * n.f[F_WALL_NORMAL] <= 0) n.f[F_YSPEED] *= FRICTION_WALL;
+                else n.i[I_STATE] = 4;
+            } else {
+                if (n.f[F_YSPEED] > 0 && hor_input * n.f[F_WALL_NORMAL] < 0) {
+                    if (state == 3) n.f[F_GRAVITY] = GRAVITY_FALL;
+                    n.i[I_STATE] = 5;
+                }
+            }
+        }
+    }
+}
+
+// Simulator.tick: nsim.py:221-292 (headless: enable_anim, log_data false)
+DEV void sim_tick(Nin& n, Ctx& c, int hor_input, int jump_input) {
+    n.i[I_FRAME] += 1;
+    n.i[I_HOR_INPUT] = hor_input; n.i[I_JUMP_INPUT] = jump_input;
+    n.f[F_X_AT_ACTION] = n.f[F_XPOS]; n.f[F_Y_AT_ACTION] = n.f[F_YPOS];   // ninja.py:841-847
+    // all move() then all think(): roaming entities in slot (= entity_dic) order, mines and boost
+    // pads by neighbourhood (they are independent of every other entity's update)
+    dyn_move_phase(c);
+    static_update_phase(n, c);
+    dyn_think_phase(n, c);
+    int state = n.i[I_STATE];
+    if (state != 9) {
+        if (state != 6) {        // dead: ragdoll is None when enable_anim=False (ninja.py:122-128)
+            ninja_integrate(n);
+            double gx, gy;
+            bool phys = ninja_pre_collision(n, c, gx, gy);
+            for (int s = 0; s < 4; s++) {
+                if (phys) ninja_collide_vs_objects(n, c, gx, gy);
+                ninja_collide_vs_tiles(n, c);
+            }
+            ninja_post_collision(n, c);
+        }
+        ninja_think(n);
+    }
+}

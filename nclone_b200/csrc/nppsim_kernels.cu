@@ -1,0 +1,238 @@
+// nppsim_kernels.cu -- sm_100a kernels + C ABI launchers (include/nppsim.h).
+// Device code lives in geom.cuh / entities.cuh / ninja.cuh; see geom.cuh for the design notes.
+#include "ninja.cuh"
+
+#include <atomic>
+#include <cstring>
+
+namespace {
+
+thread_local char g_err[256] = "";
+std::atomic<long long> g_launches{0};
+
+int fail(int code, const char* msg) { snprintf(g_err, sizeof(g_err), "%s", msg); return code; }
+int cuda_fail(cudaError_t e, const char* what) {
+    snprintf(g_err, sizeof(g_err), "%s: %s", what, cudaGetErrorString(e));
+    return (int)e > 0 ? (int)e : 1;
+}
+
+// ---- per-thread context ---------------------------------------------------------------------------
+DEV void ctx_init(Ctx& c, const nppsim_state_t& st, int i) {
+    const uint8_t* blob = st.map_blob + __ldg(st.map_off + __ldg(st.env_map + i));
+    const NppMapHeader* h = reinterpret_cast<const NppMapHeader*>(blob);
+    c.cell_hdr = reinterpret_cast<const uint32_t*>(blob + h->off_cell_hdr);
+    c.segs = reinterpret_cast<const uint32_t*>(blob + h->off_segs);
+    c.hedge = reinterpret_cast<const uint32_t*>(blob + h->off_hedge);
+    c.vedge = reinterpret_cast<const uint32_t*>(blob + h->off_vedge);
+    c.ents = reinterpret_cast<const NppStaticEnt*>(blob + h->off_ents);
+    c.ecell_off = reinterpret_cast<const uint16_t*>(blob + h->off_ecell_off);
+    c.dyn_ent = reinterpret_cast<const uint32_t*>(blob + h->off_dyn_ent);
+    c.doors = reinterpret_cast<const NppDoor*>(blob + h->off_doors);
+    c.db_count = h->db_count;
+    c.N = st.n_envs; c.n_ent = h->n_ent; c.n_dyn = h->n_dyn; c.n_doors = h->n_doors;
+    c.flag = st.ent_flag + i; c.dynf = st.dyn_f + i; c.dyni = st.dyn_i + i; c.envi = st.env_i + i;
+    c.order_mode = c.envi[(size_t)NPPSIM_ENV_ORDER * c.N];
+    c.ecell_ids = reinterpret_cast<const uint16_t*>(blob + (c.order_mode ? h->off_ecell_ids_dic : h->off_ecell_ids));
+    c.stamp = c.envi[(size_t)NPPSIM_ENV_STAMP * c.N];
+    c.hot = c.envi[(size_t)NPPSIM_ENV_HOT * c.N];
+    c.sw_frame = c.envi[(size_t)NPPSIM_ENV_SWFRAME * c.N];
+    c.events = 0;
+    c.pending_doors = false;
+}
+DEV void ctx_flush(const Ctx& c) {
+    c.envi[(size_t)NPPSIM_ENV_STAMP * c.N] = c.stamp;
+    c.envi[(size_t)NPPSIM_ENV_HOT * c.N] = c.hot;
+    c.envi[(size_t)NPPSIM_ENV_SWFRAME * c.N] = c.sw_frame;
+    if (c.events) c.envi[(size_t)NPPSIM_ENV_EVENTS * c.N] |= c.events;
+}
+
+// ---- reset -------------------------------------------------------------------------------------------
+// mode 0: state right after Simulator.load / reset (nsim.py:62-76; Ninja.__init__ ninja.py:80-196; entity ctors)
+// mode 1: Simulator.fast_reset (nsim.py:78-140): only classes with reset_state() are restored, every
+//         entity (except exit doors) is re-appended to its cell in entity_dic order.
+__global__ void __launch_bounds__(128) reset_kernel(nppsim_state_t st, const uint8_t* mask, int mode) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= st.n_envs) return;
+    if (mask && !mask[i]) return;
+    const size_t N = st.n_envs;
+    const uint8_t* blob = st.map_blob + st.map_off[st.env_map[i]];
+    const NppMapHeader* h = reinterpret_cast<const NppMapHeader*>(blob);
+    const NppStaticEnt* ents = reinterpret_cast<const NppStaticEnt*>(blob + h->off_ents);
+    double* nf = st.nin_f + i; int32_t* ni = st.nin_i + i; int32_t* envi = st.env_i + i;
+    for (int f = 0; f < NPPSIM_NF; f++) nf[f * N] = 0.0;
+    for (int f = 0; f < NPPSIM_NI; f++) ni[f * N] = 0;
+    nf[F_XPOS * N] = h->spawn_x; nf[F_YPOS * N] = h->spawn_y;
+    nf[F_X_AT_ACTION * N] = h->spawn_x; nf[F_Y_AT_ACTION * N] = h->spawn_y;
+    nf[F_GRAVITY * N] = GRAVITY_FALL; nf[F_DRAG * N] = DRAG_REGULAR; nf[F_FRICTION * N] = FRICTION_GROUND;
+    nf[F_FNY * N] = -1; nf[F_CNY * N] = 1;
+    ni[I_JUMP_BUFFER * N] = -1; ni[I_FLOOR_BUFFER * N] = -1; ni[I_WALL_BUFFER * N] = -1; ni[I_LP_BUFFER * N] = -1;
+    envi[NPPSIM_ENV_STAMP * N] = h->n_ent;
+    envi[NPPSIM_ENV_EVENTS * N] = 0;
+    envi[NPPSIM_ENV_SWFRAME * N] = -1;
+    envi[NPPSIM_ENV_ORDER * N] = mode ? 1 : 0;
+    uint8_t* flag = st.ent_flag + i; double* dynf = st.dyn_f + i; int32_t* dyni = st.dyn_i + i;
+    int hot = 0;   // fast_reset keeps boost pads' is_touching_ninja (no reset_state())
+    for (uint32_t id = 0; id < h->n_ent; id++) {
+        const NppStaticEnt& e = ents[id];
+        int stamp = mode ? (int)id : (int)e.load_order;
+        uint8_t fl = FL_ACTIVE;
+        switch (e.kind) {
+        case NPP_K_MINE: fl |= e.p0; break;
+        case NPP_K_GOLD: break;
+        case NPP_K_BOOST: fl |= FL_IS_BOOST; if (mode) { fl |= flag[id * N] & FL_TOUCH; if (fl & FL_TOUCH) hot++; } break;
+        case NPP_K_DOOR_LOCKED: fl |= FL_CLOSED; break;
+        case NPP_K_DOOR_TRAP: break;                         // starts open (entity_door_trap.py:51-53)
+        case NPP_K_DOOR_REGULAR:
+            if (mode == 0) { fl |= FL_CLOSED; dyni[(e.dyn * 3 + 0) * N] = -1; dyni[(e.dyn * 3 + 1) * N] = stamp; dyni[(e.dyn * 3 + 2) * N] = 256; }
+            else fl |= flag[id * N] & FL_CLOSED;
+            break;
+        case NPP_K_EXIT:
+            dynf[(e.dyn * 4 + 0) * N] = e.x; dynf[(e.dyn * 4 + 1) * N] = e.y; dynf[(e.dyn * 4 + 2) * N] = 0; dynf[(e.dyn * 4 + 3) * N] = 0;
+            dyni[(e.dyn * 3 + 0) * N] = -1; dyni[(e.dyn * 3 + 1) * N] = stamp; dyni[(e.dyn * 3 + 2) * N] = e.cell;
+            break;
+        case NPP_K_EXIT_SWITCH:
+            dynf[(e.dyn * 4 + 0) * N] = e.x; dynf[(e.dyn * 4 + 1) * N] = e.y; dynf[(e.dyn * 4 + 2) * N] = 0; dynf[(e.dyn * 4 + 3) * N] = 0;
+            dyni[(e.dyn * 3 + 0) * N] = e.cell; dyni[(e.dyn * 3 + 1) * N] = stamp; dyni[(e.dyn * 3 + 2) * N] = 0;
+            break;
+        case NPP_K_DRONE_ZAP: case NPP_K_MINI_DRONE: case NPP_K_BOUNCE: case NPP_K_THWUMP: case NPP_K_DEATH_BALL: case NPP_K_SHWUMP:
+            if (mode == 0) {
+                bool drone = (e.kind == NPP_K_DRONE_ZAP || e.kind == NPP_K_MINI_DRONE);
+                if (drone) fl |= (uint8_t)(e.p0 << FL_ST_SHIFT);
+                dynf[(e.dyn * 4 + 0) * N] = e.x; dynf[(e.dyn * 4 + 1) * N] = e.y;
+                dynf[(e.dyn * 4 + 2) * N] = drone ? e.x : 0.0; dynf[(e.dyn * 4 + 3) * N] = drone ? e.y : 0.0;   // xtarget,ytarget | speeds | xdir,ydir
+                dyni[(e.dyn * 3 + 0) * N] = e.cell; dyni[(e.dyn * 3 + 2) * N] = 0;
+            } else {
+                fl = flag[id * N] | FL_ACTIVE;      // no reset_state(): position, speed, state and cell all persist
+            }
+            dyni[(e.dyn * 3 + 1) * N] = stamp;
+            break;
+        default: break;
+        }
+        flag[id * N] = fl;
+    }
+    envi[NPPSIM_ENV_HOT * N] = hot;
+}
+
+// ---- step -----------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) step_kernel(nppsim_state_t st, const int8_t* __restrict__ hor, const int8_t* __restrict__ jump,
+                                                    const uint8_t* __restrict__ actions, int input_ticks, int n_ticks,
+                                                    const int32_t* __restrict__ tick_limit, int stop_on_terminal, int32_t* frames_executed) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= st.n_envs) return;
+    const size_t N = st.n_envs;
+    int limit = n_ticks;
+    if (tick_limit) limit = min(limit, tick_limit[i]);
+    if (limit <= 0) { if (frames_executed) frames_executed[i] = 0; return; }
+    Ctx c; ctx_init(c, st, i);
+    Nin n;
+    const double* nf = st.nin_f + i; const int32_t* ni = st.nin_i + i;
+#pragma unroll
+    for (int f = 0; f < NPPSIM_NF; f++) n.f[f] = nf[f * N];
+#pragma unroll
+    for (int f = 0; f < NPPSIM_NI; f++) n.i[f] = ni[f * N];
+    int h = 0, j = 0;
+    if (actions) {   // ACTION_TO_INPUTS: action_replayer.py:30-37
+        int a = actions[i]; if (a > 5) a = 0;
+        h = (a == 1 || a == 4) ? -1 : ((a == 2 || a == 5) ? 1 : 0);
+        j = a >= 3;
+    }
+    int done = 0;
+    for (int t = 0; t < limit; t++) {
+        if (!actions && (t == 0 || input_ticks > 1)) { h = hor[(size_t)t * N + i]; j = jump[(size_t)t * N + i]; }
+        sim_tick(n, c, h, j);
+        done++;
+        if (stop_on_terminal) { int s = n.i[I_STATE]; if (s == 6 || s == 7 || s == 8) break; }   // base_environment.py:605-609
+    }
+    double* of = st.nin_f + i; int32_t* oi = st.nin_i + i;
+#pragma unroll
+    for (int f = 0; f < NPPSIM_NF; f++) of[f * N] = n.f[f];
+#pragma unroll
+    for (int f = 0; f < NPPSIM_NI; f++) oi[f * N] = n.i[f];
+    ctx_flush(c);
+    if (frames_executed) frames_executed[i] = done;
+}
+
+int check_state(const nppsim_state_t* st) {
+    if (!st) return fail(NPPSIM_E_ARG, "state is NULL");
+    if (st->n_envs <= 0) return fail(NPPSIM_E_ARG, "n_envs must be positive");
+    if (!st->nin_f || !st->nin_i || !st->env_i || !st->env_map || !st->map_blob || !st->map_off)
+        return fail(NPPSIM_E_ARG, "a required state pointer is NULL");
+    if ((st->ent_cap > 0 && !st->ent_flag) || (st->dyn_cap > 0 && (!st->dyn_f || !st->dyn_i)))
+        return fail(NPPSIM_E_ARG, "entity buffers missing for a non-zero capacity");
+    return 0;
+}
+
+int launch_step(const nppsim_state_t* st, const int8_t* hor, const int8_t* jump, const uint8_t* actions, int input_ticks, int n_ticks,
+                const int32_t* tick_limit, int stop_on_terminal, int32_t* frames_executed, void* stream) {
+    int rc = check_state(st);
+    if (rc) return rc;
+    if (n_ticks <= 0) return fail(NPPSIM_E_ARG, "n_ticks must be positive");
+    if (!actions && (!hor || !jump)) return fail(NPPSIM_E_ARG, "inputs are NULL");
+    if (!actions && !(input_ticks == 1 || input_ticks == n_ticks)) return fail(NPPSIM_E_ARG, "input_ticks must be 1 or n_ticks");
+    const int block = 128;
+    const int grid = (st->n_envs + block - 1) / block;
+    step_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(*st, hor, jump, actions, input_ticks, n_ticks, tick_limit, stop_on_terminal, frames_executed);
+    g_launches++;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "step_kernel launch");
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int nppsim_version(void) { return NPPSIM_VERSION; }
+const char* nppsim_compile_error(void);
+const char* nppsim_last_error(void) { return g_err[0] ? g_err : nppsim_compile_error(); }
+int64_t nppsim_launch_count(void) { return (int64_t)g_launches.load(); }
+
+int nppsim_reset(const nppsim_state_t* st, const uint8_t* mask, int32_t mode, void* stream) {
+    g_err[0] = 0;
+    int rc = check_state(st);
+    if (rc) return rc;
+    if (mode != 0 && mode != 1) return fail(NPPSIM_E_ARG, "mode must be 0 (load/reset) or 1 (fast_reset)");
+    const int block = 128;
+    reset_kernel<<<(st->n_envs + block - 1) / block, block, 0, (cudaStream_t)stream>>>(*st, mask, mode);
+    g_launches++;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "reset_kernel launch");
+    return 0;
+}
+
+int nppsim_step(const nppsim_state_t* st, const int8_t* hor, const int8_t* jump, int32_t input_ticks, int32_t n_ticks,
+                const int32_t* tick_limit, int32_t stop_on_terminal, int32_t* frames_executed, void* stream) {
+    g_err[0] = 0;
+    return launch_step(st, hor, jump, nullptr, input_ticks, n_ticks, tick_limit, stop_on_terminal, frames_executed, stream);
+}
+
+int nppsim_step_actions(const nppsim_state_t* st, const uint8_t* actions, int32_t n_ticks, int32_t stop_on_terminal,
+                        int32_t* frames_executed, void* stream) {
+    g_err[0] = 0;
+    if (!actions) return fail(NPPSIM_E_ARG, "actions is NULL");
+    return launch_step(st, nullptr, nullptr, actions, 1, n_ticks, nullptr, stop_on_terminal, frames_executed, stream);
+}
+
+int nppsim_step_host(const nppsim_state_t* st, const uint8_t* actions_host, uint8_t* actions_dev, int32_t n_ticks,
+                     int32_t stop_on_terminal, double* pos_vel_host, int32_t* state_host, void* stream) {
+    g_err[0] = 0;
+    int rc = check_state(st);
+    if (rc) return rc;
+    if (!actions_host || !actions_dev || !pos_vel_host || !state_host) return fail(NPPSIM_E_ARG, "a host/device buffer is NULL");
+    cudaStream_t s = (cudaStream_t)stream;
+    size_t N = (size_t)st->n_envs;
+    cudaError_t e = cudaMemcpyAsync(actions_dev, actions_host, N, cudaMemcpyHostToDevice, s);
+    if (e != cudaSuccess) return cuda_fail(e, "actions H2D");
+    rc = launch_step(st, nullptr, nullptr, actions_dev, 1, n_ticks, nullptr, stop_on_terminal, nullptr, stream);
+    if (rc) return rc;
+    // xpos, ypos, xspeed, yspeed are fields 0..3 -> one contiguous [4][N] block; state is int field 0
+    e = cudaMemcpyAsync(pos_vel_host, st->nin_f, 4 * N * sizeof(double), cudaMemcpyDeviceToHost, s);
+    if (e != cudaSuccess) return cuda_fail(e, "pos/vel D2H");
+    e = cudaMemcpyAsync(state_host, st->nin_i, N * sizeof(int32_t), cudaMemcpyDeviceToHost, s);
+    if (e != cudaSuccess) return cuda_fail(e, "state D2H");
+    e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) return cuda_fail(e, "stream sync");
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,166 @@
+"""CUDA path (through the C ABI of include/nppsim.h) against the reference's own outputs
+(tests/golden, produced by the unmodified reference) and against the oracle.
+Bar: bit-exact -- every double compared by bit pattern, every int by value."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+from oracle import oracle, schema  # noqa: E402  (checker only)
+
+
+def _run_batch_vs_golden(G, idx):
+    """One env per golden trajectory, ragged lengths; one launch per frame, full canonical record
+    of every still-running env hashed and compared against the reference's digest."""
+    import torch
+    from nclone_b200 import BatchedSimulator
+    trajs = [G.traj(i) for i in idx]
+    N = len(trajs)
+    sim = BatchedSimulator(N)
+    sim.load_maps([t["map_data"] for t in trajs], np.arange(N))
+    lens = np.array([len(t["hor"]) for t in trajs])
+    T = int(lens.max())
+    hor = np.zeros((T, N), dtype=np.int8); jump = np.zeros((T, N), dtype=np.int8)
+    for k, t in enumerate(trajs):
+        hor[:lens[k], k] = t["hor"]; jump[:lens[k], k] = t["jump"]
+    hor_d = torch.from_numpy(hor).cuda(); jump_d = torch.from_numpy(jump).cuda()
+    bad = []
+    frames = 0
+    recs = sim.canonical_state()
+    for k in range(N):
+        if schema.state_hash(*recs[k]) != trajs[k]["hash"][0]:
+            bad.append((trajs[k]["name"], 0))
+    alive = np.ones(N, dtype=bool)
+    for f in range(T):
+        limit = (lens > f).astype(np.int32)
+        sim.tick(hor_d[f], jump_d[f], n_ticks=1, tick_limit=limit)
+        ids = np.nonzero((lens > f) & alive)[0]
+        recs = sim.canonical_state(ids)
+        for k, rec in zip(ids, recs):
+            frames += 1
+            if schema.state_hash(*rec) != trajs[k]["hash"][f + 1]:
+                bad.append((trajs[k]["name"], f + 1))
+                alive[k] = False           # report the first differing frame only
+            else:
+                assert rec[0][0] == trajs[k]["pv"][f + 1, 0]
+    return frames, bad, sim, trajs
+
+
+def test_bc_replays_bit_exact(golden_replays):
+    """BASELINE.json config 5: every bc_replays trajectory, every frame, full state."""
+    frames, bad, sim, trajs = _run_batch_vs_golden(golden_replays, range(len(golden_replays)))
+    assert not bad, f"{len(bad)} replays differ; first: {bad[:5]}"
+    assert frames == 31461
+    won = (sim.ninja_state().cpu().numpy() == 8).sum()
+    assert won == 128
+
+
+def test_generated_maps_random_actions_bit_exact(golden_generated):
+    frames, bad, _, _ = _run_batch_vs_golden(golden_generated, range(len(golden_generated)))
+    assert not bad, f"{len(bad)} episodes differ; first: {bad[:5]}"
+    assert frames == 40800
+
+
+def test_first_replay_known_answer(golden_replays):
+    """spawn (828,540); after 37 inputs (812.0036311681246, 542.0), state 8."""
+    import torch
+    from nclone_b200 import BatchedSimulator
+    t = golden_replays.traj(0)
+    sim = BatchedSimulator(1)
+    sim.load_maps([t["map_data"]])
+    x, y = sim.ninja_position()
+    assert (x.item(), y.item()) == (828.0, 540.0)
+    sim.tick(torch.from_numpy(t["hor"][:, None].copy()), torch.from_numpy(t["jump"][:, None].copy()), n_ticks=37)
+    x, y = sim.ninja_position()
+    assert (x.item(), y.item()) == (812.0036311681246, 542.0)
+    assert bool(sim.ninja_has_won().item()) and sim.frame().item() == 37
+    assert bool(sim.exit_switch_activated().item())
+
+
+def test_fused_frame_skip_vs_oracle(golden_replays, golden_generated):
+    """Config-2/3 shape: many envs, Discrete(6) actions held for 4 fused ticks with the env's
+    early exit on win/death; ninja record and frames_executed compared with the oracle."""
+    import torch
+    from nclone_b200 import BatchedSimulator, ACTION_TO_INPUTS
+    maps = [golden_generated.traj(i)["map_data"] for i in range(0, len(golden_generated), 2)]
+    maps += [golden_replays.traj(i)["map_data"] for i in range(0, 130, 5)]
+    M = len(maps)
+    reps = 8
+    N = M * reps
+    rng = np.random.default_rng(5)
+    steps = 60
+    actions = rng.integers(0, 6, size=(steps, N)).astype(np.uint8)
+    sim = BatchedSimulator(N)
+    sim.load_maps(maps, np.arange(N) % M)
+    osims = []
+    for k in range(N):
+        s = oracle.OracleSim(); s.load(maps[k % M]); osims.append(s)
+    done = np.zeros(N, dtype=bool)
+    for st in range(steps):
+        fe = sim.step(torch.from_numpy(actions[st]).cuda(), frame_skip=4, stop_on_terminal=True).cpu().numpy()
+        recs = sim.canonical_state()
+        for k in range(N):
+            h, j = ACTION_TO_INPUTS[actions[st, k]]
+            n = 0
+            for _ in range(4):
+                osims[k].tick(h, j); n += 1
+                if osims[k].state()[1][0] in (6, 7, 8):
+                    break
+            assert fe[k] == n, (k, st)
+            ref = osims[k].state()
+            assert schema.state_hash(*ref) == schema.state_hash(*recs[k]), (k, st, maps and k % M)
+
+
+def test_reset_and_fast_reset(golden_replays):
+    import torch
+    from nclone_b200 import BatchedSimulator
+    idx = [0, 1, 5, 40, 77]
+    trajs = [golden_replays.traj(i) for i in idx]
+    sim = BatchedSimulator(len(idx))
+    sim.load_maps([t["map_data"] for t in trajs])
+    first = sim.canonical_state()
+    rng = np.random.default_rng(0)
+    for _ in range(50):
+        sim.step(torch.from_numpy(rng.integers(0, 6, len(idx)).astype(np.uint8)).cuda(), 4, False)
+    sim.reset()
+    for a, b in zip(first, sim.canonical_state()):
+        assert schema.state_hash(*a) == schema.state_hash(*b)
+    # fast_reset against the oracle's fast_reset after the same history
+    osims = []
+    for t in trajs:
+        s = oracle.OracleSim(); s.load(t["map_data"]); osims.append(s)
+    acts = rng.integers(0, 6, size=(40, len(idx))).astype(np.uint8)
+    from nclone_b200 import ACTION_TO_INPUTS
+    for st in range(40):
+        sim.step(torch.from_numpy(acts[st]).cuda(), 4, False)
+        for k, s in enumerate(osims):
+            h, j = ACTION_TO_INPUTS[acts[st, k]]
+            for _ in range(4):
+                s.tick(h, j)
+    sim.fast_reset()
+    for s in osims:
+        s.fast_reset()
+    for st in range(40):
+        sim.step(torch.from_numpy(acts[st]).cuda(), 4, False)
+        recs = sim.canonical_state()
+        for k, s in enumerate(osims):
+            h, j = ACTION_TO_INPUTS[acts[st, k]]
+            for _ in range(4):
+                s.tick(h, j)
+            assert schema.state_hash(*s.state()) == schema.state_hash(*recs[k]), (k, st)
+
+
+def test_step_host_matches_device_path(golden_replays):
+    import torch
+    from nclone_b200 import BatchedSimulator
+    t = golden_replays.traj(3)
+    N = 64
+    a = np.random.default_rng(1).integers(0, 6, size=(20, N)).astype(np.uint8)
+    s1 = BatchedSimulator(N); s1.load_maps([t["map_data"]])
+    s2 = BatchedSimulator(N); s2.load_maps([t["map_data"]])
+    pv = np.zeros((4, N)); st = np.zeros(N, dtype=np.int32)
+    for k in range(20):
+        s1.step(torch.from_numpy(a[k]).cuda(), 4, True)
+        s2.step_host(a[k], pv, st, 4, True)
+    assert np.array_equal(s1.nin_f[:4].cpu().numpy().view(np.int64), pv.view(np.int64))
+    assert np.array_equal(s1.nin_i[0].cpu().numpy(), st)
