@@ -112,6 +112,12 @@ int nppsim_step_host(const nppsim_state_t* st, const uint8_t* actions_host, uint
                      int32_t n_ticks, int32_t stop_on_terminal, double* pos_vel_host, int32_t* state_host,
                      void* stream);
 
+/* Test hooks.  nppsim_debug_sq: out[i] = the device's SQ(in[i]) -- the reference's `x ** 2`, i.e. glibc
+ * pow(x, 2.0) (ninja.py:412 and ~45 other sites) -- for cross-checking against the host libm.
+ * nppsim_sq_mode: 1 = exact pow emulation (default build), 0 = x*x. */
+int nppsim_debug_sq(const double* in_dev, double* out_dev, int32_t n, void* stream);
+int nppsim_sq_mode(void);
+
 /* Kernel launch count since library load (bench.py's gpu_launches claim). */
 int64_t nppsim_launch_count(void);
 

@@ -152,6 +152,11 @@ __global__ void __launch_bounds__(128) step_kernel(nppsim_state_t st, const int8
     if (frames_executed) frames_executed[i] = done;
 }
 
+__global__ void sq_kernel(const double* in, double* out, int n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = SQ(in[i]);
+}
+
 int check_state(const nppsim_state_t* st) {
     if (!st) return fail(NPPSIM_E_ARG, "state is NULL");
     if (st->n_envs <= 0) return fail(NPPSIM_E_ARG, "n_envs must be positive");
@@ -186,6 +191,17 @@ int nppsim_version(void) { return NPPSIM_VERSION; }
 const char* nppsim_compile_error(void);
 const char* nppsim_last_error(void) { return g_err[0] ? g_err : nppsim_compile_error(); }
 int64_t nppsim_launch_count(void) { return (int64_t)g_launches.load(); }
+int nppsim_sq_mode(void) { return NPP_SQ_MODE; }
+
+int nppsim_debug_sq(const double* in, double* out, int32_t n, void* stream) {
+    g_err[0] = 0;
+    if (!in || !out || n <= 0) return fail(NPPSIM_E_ARG, "bad arguments");
+    sq_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(in, out, n);
+    g_launches++;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "sq_kernel launch");
+    return 0;
+}
 
 int nppsim_reset(const nppsim_state_t* st, const uint8_t* mask, int32_t mode, void* stream) {
     g_err[0] = 0;

@@ -6,7 +6,7 @@
 // NPP_SQ_MODE 1: exact emulation of glibc's pow(x, 2.0) -- see pow2_exact.cuh.
 #pragma once
 #ifndef NPP_SQ_MODE
-#define NPP_SQ_MODE 0
+#define NPP_SQ_MODE 1
 #endif
 #if NPP_SQ_MODE == 0
 DEV double SQ(double x) { return x * x; }
