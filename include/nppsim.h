@@ -42,7 +42,8 @@ extern "C" {
 #define NPPSIM_ENV_EVENTS   2   /* NPPSIM_EV_* bits accumulated since the caller last cleared them */
 #define NPPSIM_ENV_SWFRAME  3   /* sim.frame at which the exit switch was taken, -1 if not yet */
 #define NPPSIM_ENV_ORDER    4   /* 0: grid lists in creation order (load/reset); 1: entity_dic order (fast_reset) */
-#define NPPSIM_NENV 5
+#define NPPSIM_ENV_TICKS   5   /* ticks executed since load_maps (wraps at 2^31), for throughput accounting */
+#define NPPSIM_NENV 6
 
 #define NPPSIM_EV_EXIT_SWITCH 1  /* entity_exit_switch.py:128-129 -> gym_env.invalidate_switch_cache() */
 #define NPPSIM_EV_LOCKED_DOOR 2  /* entity_door_locked.py:66-67 */
@@ -86,6 +87,13 @@ int     nppsim_compile_map(const double* map_data, int32_t map_len, uint8_t* out
  * fast_reset() (mode 1, nsim.py:78-140) for every env whose mask byte is non-zero
  * (mask == NULL: all envs).  mask is a device pointer. */
 int nppsim_reset(const nppsim_state_t* st, const uint8_t* mask, int32_t mode, void* stream);
+
+/* nppsim_reset_terminal: the env wrapper's episode turnover for a whole batch -- reset (mode as above)
+ * exactly those envs whose ninja has won or died (state 6/7/8) or whose sim.frame >= max_frames
+ * (max_frames <= 0: no truncation).  stats, optional device uint64[4], is incremented atomically by
+ * {episodes ended, wins, deaths, truncations}. */
+int nppsim_reset_terminal(const nppsim_state_t* st, int32_t max_frames, int32_t mode,
+                          unsigned long long* stats, void* stream);
 
 /* nppsim_step: Simulator.tick (nsim.py:221-292) n_ticks times for every env in one launch.
  *   hor, jump   device int8, hor in {-1,0,1}, jump in {0,1}; input_ticks == 1: one value per

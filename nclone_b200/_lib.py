@@ -20,7 +20,7 @@ class NppsimState(C.Structure):
 
 EXPORTS = (
     "nppsim_version", "nppsim_last_error", "nppsim_map_blob_bound", "nppsim_compile_map",
-    "nppsim_reset", "nppsim_step", "nppsim_step_actions", "nppsim_step_host", "nppsim_launch_count",
+    "nppsim_reset", "nppsim_reset_terminal", "nppsim_step", "nppsim_step_actions", "nppsim_step_host", "nppsim_launch_count",
     "nppsim_debug_sq", "nppsim_sq_mode",
 )
 
@@ -45,6 +45,7 @@ def lib():
     L.nppsim_compile_map.restype = C.c_int
     st = C.POINTER(NppsimState)
     L.nppsim_reset.argtypes = [st, vp, i32, vp]; L.nppsim_reset.restype = C.c_int
+    L.nppsim_reset_terminal.argtypes = [st, i32, i32, vp, vp]; L.nppsim_reset_terminal.restype = C.c_int
     L.nppsim_step.argtypes = [st, vp, vp, i32, i32, vp, i32, vp, vp]; L.nppsim_step.restype = C.c_int
     L.nppsim_step_actions.argtypes = [st, vp, i32, i32, vp, vp]; L.nppsim_step_actions.restype = C.c_int
     L.nppsim_step_host.argtypes = [st, vp, vp, i32, i32, vp, vp, vp]; L.nppsim_step_host.restype = C.c_int

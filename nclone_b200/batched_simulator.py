@@ -74,6 +74,7 @@ class BatchedSimulator:
         self.dyn_i = torch.zeros((self.dyn_cap * 3, N), dtype=torch.int32, device=dev)
         self.frames_executed = torch.zeros(N, dtype=torch.int32, device=dev)
         self._actions_dev = torch.zeros(N, dtype=torch.uint8, device=dev)
+        self.stats = torch.zeros(4, dtype=torch.int64, device=dev)
         st = NppsimState()
         st.n_envs, st.ent_cap, st.dyn_cap, st.n_maps = N, self.ent_cap, self.dyn_cap, len(blobs)
         st.nin_f, st.nin_i, st.env_i = self.nin_f.data_ptr(), self.nin_i.data_ptr(), self.env_i.data_ptr()
@@ -103,6 +104,17 @@ class BatchedSimulator:
 
     def fast_reset(self, mask=None):
         self.reset(mask, mode="fast")
+
+    def reset_terminal(self, max_frames=0, mode="reset"):
+        """Episode turnover for the batch: reset the envs that won, died or reached max_frames.
+        Episode statistics accumulate in self.stats (device uint64[4]: episodes, wins, deaths, truncations)."""
+        self._need_maps()
+        with torch.cuda.device(self.device):
+            check(self.L.nppsim_reset_terminal(C.byref(self._state), int(max_frames), {"reset": 0, "fast": 1}[mode],
+                                               C.c_void_p(self.stats.data_ptr()), self._stream()))
+
+    def total_ticks(self):
+        return int(self.env_i[FD.ENV_TICKS].to(torch.int64).sum().item())
 
     # ------------------------------------------------------------------ Simulator.tick (nsim.py:221-292)
     def _dev_i8(self, x):

@@ -50,11 +50,21 @@ DEV void ctx_flush(const Ctx& c) {
 // mode 0: state right after Simulator.load / reset (nsim.py:62-76; Ninja.__init__ ninja.py:80-196; entity ctors)
 // mode 1: Simulator.fast_reset (nsim.py:78-140): only classes with reset_state() are restored, every
 //         entity (except exit doors) is re-appended to its cell in entity_dic order.
-__global__ void __launch_bounds__(128) reset_kernel(nppsim_state_t st, const uint8_t* mask, int mode) {
+__global__ void __launch_bounds__(128) reset_kernel(nppsim_state_t st, const uint8_t* mask, int mode, int auto_terminal, int max_frames,
+                                                     unsigned long long* stats) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= st.n_envs) return;
     if (mask && !mask[i]) return;
     const size_t N = st.n_envs;
+    if (auto_terminal) {
+        int s = st.nin_i[I_STATE * N + i], fr = st.nin_i[I_FRAME * N + i];
+        bool term = (s == 6 || s == 7 || s == 8), trunc = (max_frames > 0 && fr >= max_frames);
+        if (!term && !trunc) return;
+        if (stats) {
+            atomicAdd(stats + 0, 1ULL);
+            if (s == 8) atomicAdd(stats + 1, 1ULL); else if (term) atomicAdd(stats + 2, 1ULL); else atomicAdd(stats + 3, 1ULL);
+        }
+    }
     const uint8_t* blob = st.map_blob + st.map_off[st.env_map[i]];
     const NppMapHeader* h = reinterpret_cast<const NppMapHeader*>(blob);
     const NppStaticEnt* ents = reinterpret_cast<const NppStaticEnt*>(blob + h->off_ents);
@@ -149,6 +159,7 @@ __global__ void __launch_bounds__(128) step_kernel(nppsim_state_t st, const int8
 #pragma unroll
     for (int f = 0; f < NPPSIM_NI; f++) oi[f * N] = n.i[f];
     ctx_flush(c);
+    c.envi[(size_t)NPPSIM_ENV_TICKS * N] += done;
     if (frames_executed) frames_executed[i] = done;
 }
 
@@ -209,7 +220,20 @@ int nppsim_reset(const nppsim_state_t* st, const uint8_t* mask, int32_t mode, vo
     if (rc) return rc;
     if (mode != 0 && mode != 1) return fail(NPPSIM_E_ARG, "mode must be 0 (load/reset) or 1 (fast_reset)");
     const int block = 128;
-    reset_kernel<<<(st->n_envs + block - 1) / block, block, 0, (cudaStream_t)stream>>>(*st, mask, mode);
+    reset_kernel<<<(st->n_envs + block - 1) / block, block, 0, (cudaStream_t)stream>>>(*st, mask, mode, 0, 0, nullptr);
+    g_launches++;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "reset_kernel launch");
+    return 0;
+}
+
+int nppsim_reset_terminal(const nppsim_state_t* st, int32_t max_frames, int32_t mode, unsigned long long* stats, void* stream) {
+    g_err[0] = 0;
+    int rc = check_state(st);
+    if (rc) return rc;
+    if (mode != 0 && mode != 1) return fail(NPPSIM_E_ARG, "mode must be 0 (load/reset) or 1 (fast_reset)");
+    const int block = 128;
+    reset_kernel<<<(st->n_envs + block - 1) / block, block, 0, (cudaStream_t)stream>>>(*st, nullptr, mode, 1, max_frames, stats);
     g_launches++;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_fail(e, "reset_kernel launch");

@@ -4,7 +4,9 @@
  * as the reference's one-process-per-env deployment does
  * (/root/reference/nclone/run_multiple_headless.py:128-137).
  */
+#define _POSIX_C_SOURCE 200809L
 #include <pthread.h>
+#include <time.h>
 #include <stdint.h>
 #include <stdlib.h>
 
@@ -12,45 +14,55 @@ typedef struct OSim OSim;
 OSim *osim_create(void);
 void osim_destroy(OSim *);
 int osim_load(OSim *, const double *, int);
+int osim_reset(OSim *);
 void osim_tick(OSim *, int, int);
 void osim_get_state(const OSim *, double *, int64_t *, double *, int64_t *);
 
 typedef struct {
     const double *maps; const int32_t *lens; int stride; int map_lo, map_hi;
     const uint8_t *actions; int n_steps; int frame_skip; int max_frames;
-    long ticks; double checksum;
+    long ticks; double checksum; double loop_seconds;
 } Job;
+
+static double now_s(void) { struct timespec t; clock_gettime(CLOCK_MONOTONIC, &t); return t.tv_sec + 1e-9 * t.tv_nsec; }
 
 static const int ACT_H[6] = {0, -1, 1, 0, -1, 1};
 static const int ACT_J[6] = {0, 0, 0, 1, 1, 1};
 
 /* One env per map in [map_lo, map_hi): n_steps agent steps of frame_skip ticks each, the
-   action of env m at step s is actions[m * n_steps + s]; reload on win/death or at max_frames
+   action of env m at step s is actions[m * n_steps + s]; Simulator.reset() on win/death or at max_frames
    (same policy as bench.py's GPU arm). */
 static void *worker(void *arg) {
     Job *j = (Job *)arg;
     OSim *S = osim_create();
+    long ticks = 0; double checksum = 0, loop_seconds = 0;   /* locals: the Job array is shared cache lines */
     for (int m = j->map_lo; m < j->map_hi; m++) {
         const double *md = j->maps + (size_t)m * j->stride;
         if (osim_load(S, md, j->lens[m])) continue;
         int frames = 0;
+        double t0 = now_s();                 /* level load is not part of the tick path being timed */
         for (int s = 0; s < j->n_steps; s++) {
             int a = j->actions[(size_t)m * j->n_steps + s] % 6;
-            for (int k = 0; k < j->frame_skip; k++) { osim_tick(S, ACT_H[a], ACT_J[a]); j->ticks++; frames++; }
             double nf[31]; int64_t ni[27];
-            osim_get_state(S, nf, ni, NULL, NULL);
-            if (ni[0] >= 6 || frames >= j->max_frames) { osim_load(S, md, j->lens[m]); frames = 0; }
-            j->checksum += nf[0] + nf[1];
+            for (int k = 0; k < j->frame_skip; k++) {
+                osim_tick(S, ACT_H[a], ACT_J[a]); ticks++; frames++;
+                osim_get_state(S, nf, ni, NULL, NULL);
+                if (ni[0] >= 6 && ni[0] <= 8) break;      /* base_environment.py:605-609 early exit */
+            }
+            if ((ni[0] >= 6 && ni[0] <= 8) || frames >= j->max_frames) { osim_reset(S); frames = 0; }   /* Simulator.reset(), as the env does per episode */
+            checksum += nf[0] + nf[1];
         }
+        loop_seconds += now_s() - t0;
     }
     osim_destroy(S);
+    j->ticks = ticks; j->checksum = checksum; j->loop_seconds = loop_seconds;
     return NULL;
 }
 
 /* returns total ticks executed */
 long osim_baseline_run(const double *maps, const int32_t *lens, int n_maps, int stride,
                        const uint8_t *actions, int n_steps, int frame_skip, int max_frames,
-                       int n_threads, double *checksum) {
+                       int n_threads, double *checksum, double *max_loop_seconds) {
     if (n_threads < 1) n_threads = 1;
     if (n_threads > n_maps) n_threads = n_maps;
     pthread_t *th = (pthread_t *)malloc(sizeof(pthread_t) * n_threads);
@@ -62,9 +74,13 @@ long osim_baseline_run(const double *maps, const int32_t *lens, int n_maps, int 
         jobs[t].actions = actions; jobs[t].n_steps = n_steps; jobs[t].frame_skip = frame_skip; jobs[t].max_frames = max_frames;
         pthread_create(&th[t], NULL, worker, &jobs[t]);
     }
-    long total = 0; double cs = 0;
-    for (int t = 0; t < n_threads; t++) { pthread_join(th[t], NULL); total += jobs[t].ticks; cs += jobs[t].checksum; }
+    long total = 0; double cs = 0, mx = 0;
+    for (int t = 0; t < n_threads; t++) {
+        pthread_join(th[t], NULL); total += jobs[t].ticks; cs += jobs[t].checksum;
+        if (jobs[t].loop_seconds > mx) mx = jobs[t].loop_seconds;
+    }
     if (checksum) *checksum = cs;
+    if (max_loop_seconds) *max_loop_seconds = mx;
     free(th); free(jobs);
     return total;
 }

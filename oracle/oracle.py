@@ -50,7 +50,7 @@ def lib():
         L.osim_get_cell_counts.argtypes = [C.c_void_p, i32p, i32p]
         L.osim_get_segments.argtypes = [C.c_void_p, dp]
         L.osim_get_grid_edges.argtypes = [C.c_void_p, i32p, i32p]
-        L.osim_baseline_run.argtypes = [dp, i32p, C.c_int, C.c_int, u8p, C.c_int, C.c_int, C.c_int, C.c_int, dp]
+        L.osim_baseline_run.argtypes = [dp, i32p, C.c_int, C.c_int, u8p, C.c_int, C.c_int, C.c_int, C.c_int, dp, dp]
         L.osim_baseline_run.restype = C.c_long
         _lib = L
     return _lib
@@ -141,10 +141,12 @@ def run_trajectory(map_data, hor, jump):
 
 
 def baseline_run(maps, lens, actions, frame_skip, max_frames, n_threads):
-    """Multi-threaded CPU baseline (baseline_runner.c). maps [M,stride] f64, actions [M,S] u8."""
+    """Multi-threaded CPU baseline (baseline_runner.c). maps [M,stride] f64, actions [M,S] u8.
+    Returns (ticks executed, slowest worker's seconds inside its tick loops)."""
     maps = np.ascontiguousarray(maps, dtype=np.float64); lens = np.ascontiguousarray(lens, dtype=np.int32)
     actions = np.ascontiguousarray(actions, dtype=np.uint8)
-    cs = C.c_double(0)
+    cs = C.c_double(0); secs = C.c_double(0)
     ticks = lib().osim_baseline_run(_p(maps, C.c_double), _p(lens, C.c_int32), maps.shape[0], maps.shape[1],
-                                    _p(actions, C.c_uint8), actions.shape[1], frame_skip, max_frames, n_threads, C.byref(cs))
-    return int(ticks), cs.value
+                                    _p(actions, C.c_uint8), actions.shape[1], frame_skip, max_frames, n_threads,
+                                    C.byref(cs), C.byref(secs))
+    return int(ticks), secs.value
