@@ -188,7 +188,8 @@ def main():
     arr, lens = load_maps(fixture)
     M = len(arr)
     # shard: every rank owns its own env batch (weak scaling); ranks use different level rotations and seeds
-    env_to_map = (np.arange(n_envs) + rank * 977) % M
+    from nclone_b200.sharding import shard_env_to_map, reduce_rollout
+    env_to_map = shard_env_to_map(n_envs, rank, M)
     sim = BatchedSimulator(n_envs, device=dev)
     sim.load_maps([arr[k, :lens[k]] for k in range(M)], env_to_map)
 
@@ -258,18 +259,13 @@ def main():
     clocks = sampler.finish() if rank == 0 else None
 
     # ---- reduce over ranks: max time, summed work ------------------------------------------------------
-    red = torch.tensor([elapsed_ms, e2e_ms], dtype=torch.float64, device=dev)
-    work = torch.tensor([ticks, e2e_ticks], dtype=torch.float64, device=dev)
-    stats = sim.stats.clone()
-    if world > 1:
-        dist.all_reduce(red, op=dist.ReduceOp.MAX)
-        dist.all_reduce(work, op=dist.ReduceOp.SUM)
-        dist.all_reduce(stats, op=dist.ReduceOp.SUM)      # end-of-rollout stats: the only collective (NCCL), not timed
+    # end-of-rollout reduction: the only collective (NCCL), outside the timed regions
+    (elapsed_ms, e2e_ms), (ticks_all, e2e_ticks_all), stats = reduce_rollout(
+        [elapsed_ms, e2e_ms], [ticks, e2e_ticks], sim.stats, dist if world > 1 else None)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
-    elapsed_ms, e2e_ms = red.tolist(); ticks_all, e2e_ticks_all = work.tolist()
     value = ticks_all / (elapsed_ms / 1000.0)
     e2e_value = e2e_ticks_all / (e2e_ms / 1000.0)
 
