@@ -29,8 +29,8 @@ def lib():
     global _lib
     if _lib is not None:
         return _lib
-    path = _build.LIB
-    if _build.needs_build():
+    path = os.environ.get("NPPSIM_LIB") or _build.LIB      # NPPSIM_LIB: A/B testing of kernel builds
+    if path == _build.LIB and _build.needs_build():
         try:
             _build.build()
         except Exception:

@@ -42,7 +42,7 @@ DEV void ninja_kill(Nin& n, Ctx& c, double x, double y, double xs, double ys, in
 }
 
 DEV int cell_index(double x, double y) {
-    return clampi(floordiv(x, 24.0), 0, 43) * NPP_NCY + clampi(floordiv(y, 24.0), 0, 24);
+    return clampi(floordiv24(x), 0, 43) * NPP_NCY + clampi(floordiv24(y), 0, 24);
 }
 // entities.py:256-264 for a roaming entity in dynamic slot `slot`
 DEV void grid_move(Ctx& c, int slot, double x, double y) {
@@ -69,17 +69,19 @@ DEV bool drone_test_dir(Ctx& c, int dir, double xpos, double ypos, double radius
     int ydir = dir == 1 ? 1 : (dir == 3 ? -1 : 0);
     double xtarget = xpos + grid_width * xdir, ytarget = ypos + grid_width * ydir;
     if (!ydir) {
-        int cell_x = floordiv(xpos + xdir * radius, 12.0);
-        int cell_xtarget = floordiv(xtarget + xdir * radius, 12.0);
-        int cell_y1 = floordiv(ypos - radius, 12.0), cell_y2 = floordiv(ypos + radius, 12.0);
+        int cell_x = floordiv12(xpos + xdir * radius);
+        int cell_xtarget = floordiv12(xtarget + xdir * radius);
+        int cell_y1 = floordiv12(ypos - radius), cell_y2 = floordiv12(ypos + radius);
+        #pragma unroll 1
         while (cell_x != cell_xtarget) {
             if (!is_empty_column(c, cell_x, cell_y1, cell_y2, xdir)) return false;
             cell_x += xdir;
         }
     } else {
-        int cell_y = floordiv(ypos + ydir * radius, 12.0);
-        int cell_ytarget = floordiv(ytarget + ydir * radius, 12.0);
-        int cell_x1 = floordiv(xpos - radius, 12.0), cell_x2 = floordiv(xpos + radius, 12.0);
+        int cell_y = floordiv12(ypos + ydir * radius);
+        int cell_ytarget = floordiv12(ytarget + ydir * radius);
+        int cell_x1 = floordiv12(xpos - radius), cell_x2 = floordiv12(xpos + radius);
+        #pragma unroll 1
         while (cell_y != cell_ytarget) {
             if (!is_empty_row(c, cell_x1, cell_x2, cell_y, ydir)) return false;
             cell_y += ydir;
@@ -88,7 +90,9 @@ DEV bool drone_test_dir(Ctx& c, int dir, double xpos, double ypos, double radius
     xt = xtarget; yt = ytarget;
     return true;
 }
-__device__ __noinline__ void drone_move(Ctx& c, int slot, int id, int mode, bool mini) {
+// Rare entity updates are out of line; they take the context BY VALUE (so the caller's copy and the
+// ninja record stay in registers) and return the updated insertion-stamp counter.
+__device__ __noinline__ int drone_move(Ctx c, int slot, int id, int mode, bool mini) {
     const double speed = mini ? 1.3 : 8.0 / 7, radius = mini ? 4.0 : 7.5, grid_width = mini ? 12.0 : 24.0;
     uint8_t fl = FLAG(c, id);
     int dir = (fl & FL_ST) >> FL_ST_SHIFT;
@@ -102,6 +106,7 @@ __device__ __noinline__ void drone_move(Ctx& c, int slot, int id, int mode, bool
         bool can_move = false;
         // DIR_LIST rows (entity_drone_base.py:72): mode -> direction offsets tried in order
         const int dl[4] = {0x2301, 0x2103, 0x2310, 0x2130};     // nibbles, first tried in the low nibble
+        #pragma unroll 1
         for (int k = 0; k < 4; k++) {
             int new_dir = (dir + ((dl[mode] >> (4 * k)) & 15)) & 3;
             if (drone_test_dir(c, new_dir, xpos, ypos, radius, grid_width, xtarget, ytarget)) { dir = new_dir; can_move = true; break; }
@@ -119,14 +124,15 @@ __device__ __noinline__ void drone_move(Ctx& c, int slot, int id, int mode, bool
         DYNF(c, slot, 0) = xpos; DYNF(c, slot, 1) = ypos;
         grid_move(c, slot, xpos, ypos);
     }
+    return c.stamp;
 }
 
 // ---- thwump: entity_thwump.py:109-206 -----------------------------------------------------------------
 DEV int thwump_state(uint8_t fl) { int s = (fl & FL_ST) >> FL_ST_SHIFT; return s == 3 ? -1 : s; }
 DEV void thwump_set_state(Ctx& c, int id, int s) { uint8_t fl = FLAG(c, id); FLAG(c, id) = (fl & ~FL_ST) | ((s & 3) << FL_ST_SHIFT); }
-__device__ __noinline__ void thwump_move(Ctx& c, int slot, int id, int p0) {
+__device__ __noinline__ int thwump_move(Ctx c, int slot, int id, int p0) {
     int state = thwump_state(FLAG(c, id));
-    if (!state) return;
+    if (!state) return c.stamp;
     bool horizontal = p0 & 1; int direction = (p0 & 2) ? -1 : 1;
     double speed = state == 1 ? 20.0 / 7 : 8.0 / 7;
     int speed_dir = direction * state;
@@ -134,38 +140,40 @@ __device__ __noinline__ void thwump_move(Ctx& c, int slot, int id, int p0) {
     EntS e = ld_ent(c, id);                                   // origin = initial position
     if (!horizontal) {
         double ypos_new = ypos + speed * speed_dir;
-        if (state == -1 && (ypos_new - e.y) * (ypos - e.y) < 0) { DYNF(c, slot, 1) = e.y; thwump_set_state(c, id, 0); return; }
-        int cell_y = floordiv(ypos + speed_dir * 11, 12.0), cell_y_new = floordiv(ypos_new + speed_dir * 11, 12.0);
+        if (state == -1 && (ypos_new - e.y) * (ypos - e.y) < 0) { DYNF(c, slot, 1) = e.y; thwump_set_state(c, id, 0); return c.stamp; }
+        int cell_y = floordiv12(ypos + speed_dir * 11), cell_y_new = floordiv12(ypos_new + speed_dir * 11);
         if (cell_y != cell_y_new) {
-            int x1 = floordiv(xpos - 11, 12.0), x2 = floordiv(xpos + 11, 12.0);
-            if (!is_empty_row(c, x1, x2, cell_y, speed_dir)) { thwump_set_state(c, id, -1); return; }
+            int x1 = floordiv12(xpos - 11), x2 = floordiv12(xpos + 11);
+            if (!is_empty_row(c, x1, x2, cell_y, speed_dir)) { thwump_set_state(c, id, -1); return c.stamp; }
         }
         ypos = ypos_new; DYNF(c, slot, 1) = ypos;
     } else {
         double xpos_new = xpos + speed * speed_dir;
-        if (state == -1 && (xpos_new - e.x) * (xpos - e.x) < 0) { DYNF(c, slot, 0) = e.x; thwump_set_state(c, id, 0); return; }
-        int cell_x = floordiv(xpos + speed_dir * 11, 12.0), cell_x_new = floordiv(xpos_new + speed_dir * 11, 12.0);
+        if (state == -1 && (xpos_new - e.x) * (xpos - e.x) < 0) { DYNF(c, slot, 0) = e.x; thwump_set_state(c, id, 0); return c.stamp; }
+        int cell_x = floordiv12(xpos + speed_dir * 11), cell_x_new = floordiv12(xpos_new + speed_dir * 11);
         if (cell_x != cell_x_new) {
-            int y1 = floordiv(ypos - 11, 12.0), y2 = floordiv(ypos + 11, 12.0);
-            if (!is_empty_column(c, cell_x, y1, y2, speed_dir)) { thwump_set_state(c, id, -1); return; }
+            int y1 = floordiv12(ypos - 11), y2 = floordiv12(ypos + 11);
+            if (!is_empty_column(c, cell_x, y1, y2, speed_dir)) { thwump_set_state(c, id, -1); return c.stamp; }
         }
         xpos = xpos_new; DYNF(c, slot, 0) = xpos;
     }
     grid_move(c, slot, xpos, ypos);
+    return c.stamp;
 }
-__device__ __noinline__ void thwump_think(const Nin& n, Ctx& c, int slot, int id, int p0) {
-    if (thwump_state(FLAG(c, id)) || !ninja_valid_target(n)) return;
+__device__ __noinline__ void thwump_think(Ctx c, double ninja_x, double ninja_y, bool ninja_valid, int slot, int id, int p0) {
+    if (thwump_state(FLAG(c, id)) || !ninja_valid) return;
     bool horizontal = p0 & 1; int direction = (p0 & 2) ? -1 : 1;
     double xpos = DYNF(c, slot, 0), ypos = DYNF(c, slot, 1);
     const double activation_range = 2 * (9 + NINJA_RADIUS);
     if (!horizontal) {
-        if (fabs(xpos - n.f[F_XPOS]) < activation_range) {
-            int ninja_ycell = floordiv(n.f[F_YPOS], 12.0);
-            int ty = floordiv(ypos - direction * 11, 12.0);
-            int x1 = floordiv(xpos - 11, 12.0), x2 = floordiv(xpos + 11, 12.0);
+        if (fabs(xpos - ninja_x) < activation_range) {
+            int ninja_ycell = floordiv12(ninja_y);
+            int ty = floordiv12(ypos - direction * 11);
+            int x1 = floordiv12(xpos - 11), x2 = floordiv12(xpos + 11);
             int dy = ninja_ycell - ty;
             if (dy * direction >= 0) {
                 int i;
+                #pragma unroll 1
                 for (i = 0; i < 100; i++) {
                     if (!is_empty_row(c, x1, x2, ty, direction)) { dy = ninja_ycell - ty; break; }
                     ty += direction;
@@ -175,13 +183,14 @@ __device__ __noinline__ void thwump_think(const Nin& n, Ctx& c, int slot, int id
             }
         }
     } else {
-        if (fabs(ypos - n.f[F_YPOS]) < activation_range) {
-            int ninja_xcell = floordiv(n.f[F_XPOS], 12.0);
-            int tx = floordiv(xpos - direction * 11, 12.0);
-            int y1 = floordiv(ypos - 11, 12.0), y2 = floordiv(ypos + 11, 12.0);
+        if (fabs(ypos - ninja_y) < activation_range) {
+            int ninja_xcell = floordiv12(ninja_x);
+            int tx = floordiv12(xpos - direction * 11);
+            int y1 = floordiv12(ypos - 11), y2 = floordiv12(ypos + 11);
             int dx = ninja_xcell - tx;
             if (dx * direction >= 0) {
                 int i;
+                #pragma unroll 1
                 for (i = 0; i < 100; i++) {
                     if (!is_empty_column(c, tx, y1, y2, direction)) { dx = ninja_xcell - tx; break; }
                     tx += direction;
@@ -199,28 +208,28 @@ DEV void shwump_move_if_possible(Ctx& c, int slot, int id, double xdir, double y
     double xpos = DYNF(c, slot, 0), ypos = DYNF(c, slot, 1);
     if (DYNF(c, slot, 3) == 0) {                              // self.ydir == 0
         double xpos_new = xpos + xdir * speed;
-        int cell_x = floordiv(xpos, 12.0), cell_x_new = floordiv(xpos_new, 12.0);
+        int cell_x = floordiv12(xpos), cell_x_new = floordiv12(xpos_new);
         if (cell_x != cell_x_new) {
-            int y1 = floordiv(ypos - 8, 12.0), y2 = floordiv(ypos + 8, 12.0);
+            int y1 = floordiv12(ypos - 8), y2 = floordiv12(ypos + 8);
             if (!is_empty_column(c, cell_x, y1, y2, (int)xdir)) { shwump_set_state(c, id, 3); return; }
         }
         xpos = xpos_new; DYNF(c, slot, 0) = xpos;
     } else {
         double ypos_new = ypos + ydir * speed;
-        int cell_y = floordiv(ypos, 12.0), cell_y_new = floordiv(ypos_new, 12.0);
+        int cell_y = floordiv12(ypos), cell_y_new = floordiv12(ypos_new);
         if (cell_y != cell_y_new) {
-            int x1 = floordiv(xpos - 8, 12.0), x2 = floordiv(xpos + 8, 12.0);
+            int x1 = floordiv12(xpos - 8), x2 = floordiv12(xpos + 8);
             if (!is_empty_row(c, x1, x2, cell_y, (int)ydir)) { shwump_set_state(c, id, 3); return; }
         }
         ypos = ypos_new; DYNF(c, slot, 1) = ypos;
     }
     grid_move(c, slot, xpos, ypos);
 }
-__device__ __noinline__ void shwump_think(Ctx& c, int slot, int id) {
+__device__ __noinline__ int shwump_think(Ctx c, int slot, int id) {
     uint8_t fl = FLAG(c, id);
     int state = (fl & FL_ST) >> FL_ST_SHIFT;
     if (state == 1) {
-        if (fl & FL_ACTIVATED) { FLAG(c, id) = fl & ~FL_ACTIVATED; return; }
+        if (fl & FL_ACTIVATED) { FLAG(c, id) = fl & ~FL_ACTIVATED; return c.stamp; }
         state = 2; shwump_set_state(c, id, 2);
     }
     double xdir = DYNF(c, slot, 2), ydir = DYNF(c, slot, 3);
@@ -233,14 +242,15 @@ __device__ __noinline__ void shwump_think(Ctx& c, int slot, int id) {
         // -xdir of a Python int 0 is 0; the product with speed is only ever added to a position
         shwump_move_if_possible(c, slot, id, xdir == 0 ? 0.0 : -xdir, ydir == 0 ? 0.0 : -ydir, 4);
     }
+    return c.stamp;
 }
 
 // ---- death ball: entity_death_ball.py:74-167 -----------------------------------------------------------
-__device__ __noinline__ void death_ball_think(const Nin& n, Ctx& c, int slot, int id) {
+__device__ __noinline__ int death_ball_think(Ctx c, double ninja_x, double ninja_y, bool ninja_valid, int slot, int id) {
     double xpos = DYNF(c, slot, 0), ypos = DYNF(c, slot, 1), xspeed = DYNF(c, slot, 2), yspeed = DYNF(c, slot, 3);
-    if (!ninja_valid_target(n)) { xspeed *= 0.95; yspeed *= 0.95; }
+    if (!ninja_valid) { xspeed *= 0.95; yspeed *= 0.95; }
     else {
-        double dx = n.f[F_XPOS] - xpos, dy = n.f[F_YPOS] - ypos;
+        double dx = ninja_x - xpos, dy = ninja_y - ypos;
         double dist = sqrt(SQ(dx) + SQ(dy));
         if (dist > 0) { dx /= dist; dy /= dist; }
         xspeed += dx * 0.04; yspeed += dy * 0.04;
@@ -258,6 +268,7 @@ __device__ __noinline__ void death_ball_think(const Nin& n, Ctx& c, int slot, in
     xpos = xpos_old + time * xspeed; ypos = ypos_old + time * yspeed;
     double xnormal = 0, ynormal = 0;
     bool bail = false;
+    #pragma unroll 1
     for (int it = 0; it < 16; it++) {
         double a, b;
         int result = get_single_closest_point(c, xpos - 8, ypos - 8, xpos + 8, ypos + 8, xpos, ypos, 8, a, b);
@@ -285,6 +296,7 @@ __device__ __noinline__ void death_ball_think(const Nin& n, Ctx& c, int slot, in
         int index = (int)(__ldg(reinterpret_cast<const uint32_t*>(c.ents + id) + 6) >> 16);
         if ((double)(index + 1) < c.db_count) {
             // entity_dic[25][index+1:]: the later death balls (slots are in entity_dic order)
+            #pragma unroll 1
             for (int t = slot + 1; t < c.n_dyn; t++) {
                 if (((__ldg(c.dyn_ent + t) >> 16) & 255) != NPP_K_DEATH_BALL) continue;
                 double dx = xpos - DYNF(c, t, 0), dy = ypos - DYNF(c, t, 1);
@@ -299,14 +311,16 @@ __device__ __noinline__ void death_ball_think(const Nin& n, Ctx& c, int slot, in
     }
     DYNF(c, slot, 0) = xpos; DYNF(c, slot, 1) = ypos; DYNF(c, slot, 2) = xspeed; DYNF(c, slot, 3) = yspeed;
     if (!bail) grid_move(c, slot, xpos, ypos);
+    return c.stamp;
 }
 
 // ---- move / think for the dynamic slots (entity_dic order; nsim.py:235-251) --------------------------------
 DEV void dyn_move_phase(Ctx& c) {
+    #pragma unroll 1
     for (int s = 0; s < c.n_dyn; s++) {
         uint32_t de = __ldg(c.dyn_ent + s);
         int kind = (de >> 16) & 255, id = de & 0xffff, p = de >> 24;
-        if (kind == NPP_K_DRONE_ZAP || kind == NPP_K_MINI_DRONE) drone_move(c, s, id, p, kind == NPP_K_MINI_DRONE);
+        if (kind == NPP_K_DRONE_ZAP || kind == NPP_K_MINI_DRONE) c.stamp = drone_move(c, s, id, p, kind == NPP_K_MINI_DRONE);
         else if (kind == NPP_K_BOUNCE) {                         // entity_bounce_block.py:107-125
             EntS e = ld_ent(c, id);
             double xpos = DYNF(c, s, 0), ypos = DYNF(c, s, 1), xspeed = DYNF(c, s, 2), yspeed = DYNF(c, s, 3);
@@ -316,10 +330,11 @@ DEV void dyn_move_phase(Ctx& c) {
             xpos += xforce; ypos += yforce; xspeed += xforce; yspeed += yforce;
             DYNF(c, s, 0) = xpos; DYNF(c, s, 1) = ypos; DYNF(c, s, 2) = xspeed; DYNF(c, s, 3) = yspeed;
             grid_move(c, s, xpos, ypos);
-        } else if (kind == NPP_K_THWUMP) thwump_move(c, s, id, p);
+        } else if (kind == NPP_K_THWUMP) c.stamp = thwump_move(c, s, id, p);
     }
 }
 DEV void dyn_think_phase(const Nin& n, Ctx& c) {
+    #pragma unroll 1
     for (int s = 0; s < c.n_dyn; s++) {
         uint32_t de = __ldg(c.dyn_ent + s);
         int kind = (de >> 16) & 255, id = de & 0xffff, p = de >> 24;
@@ -329,9 +344,9 @@ DEV void dyn_think_phase(const Nin& n, Ctx& c) {
                 DYNI(c, s, 2) = aux;
                 if ((aux & 255) > 5) regular_door_change_state(c, id, s, true);
             }
-        } else if (kind == NPP_K_THWUMP) thwump_think(n, c, s, id, p);
-        else if (kind == NPP_K_DEATH_BALL) death_ball_think(n, c, s, id);
-        else if (kind == NPP_K_SHWUMP) shwump_think(c, s, id);
+        } else if (kind == NPP_K_THWUMP) thwump_think(c, n.f[F_XPOS], n.f[F_YPOS], ninja_valid_target(n), s, id, p);
+        else if (kind == NPP_K_DEATH_BALL) c.stamp = death_ball_think(c, n.f[F_XPOS], n.f[F_YPOS], ninja_valid_target(n), s, id);
+        else if (kind == NPP_K_SHWUMP) c.stamp = shwump_think(c, s, id);
     }
 }
 
@@ -372,6 +387,7 @@ DEV void static_update_phase(Nin& n, Ctx& c) {
     // pass B first: hot entities anywhere on the map (they may be leaving contact)
     if (c.hot > 0) {
         int seen = 0, want = c.hot;
+        #pragma unroll 1
         for (int id = 0; id < c.n_ent && seen < want; id++) {
             uint8_t fl = FLAG(c, id);
             if ((fl & FL_MINE) == 2) { seen++; mine_think(n, c, id, valid); }
@@ -382,10 +398,12 @@ DEV void static_update_phase(Nin& n, Ctx& c) {
     double x = n.f[F_XPOS], y = n.f[F_YPOS];
     bool interior = (x >= 24.0 && x < 1032.0 && y >= 24.0 && y < 576.0);
     if (interior) {
-        int cx = floordiv(x, 24.0), cy = floordiv(y, 24.0);      // 1..42, 1..23: the 3x3 block needs no clamping
+        int cx = floordiv24(x), cy = floordiv24(y);      // 1..42, 1..23: the 3x3 block needs no clamping
         int nboost = 0;
+        #pragma unroll 1
         for (int xc = cx - 1; xc <= cx + 1; xc++) {
             int a = __ldg(c.ecell_off + xc * NPP_NCY + cy - 1), b = __ldg(c.ecell_off + xc * NPP_NCY + cy + 2);
+            #pragma unroll 1
             for (int k = a; k < b; k++) {
                 int id = __ldg(c.ecell_ids + k);
                 uint8_t fl = FLAG(c, id);
@@ -395,10 +413,13 @@ DEV void static_update_phase(Nin& n, Ctx& c) {
         }
         // boost pads change the ninja's velocity, so they run in entity_dic (= id) order
         int last = -1;
+        #pragma unroll 1
         for (int r = 0; r < nboost; r++) {
             int best = 0x7fffffff;
+            #pragma unroll 1
             for (int xc = cx - 1; xc <= cx + 1; xc++) {
                 int a = __ldg(c.ecell_off + xc * NPP_NCY + cy - 1), b = __ldg(c.ecell_off + xc * NPP_NCY + cy + 2);
+                #pragma unroll 1
                 for (int k = a; k < b; k++) {
                     int id = __ldg(c.ecell_ids + k);
                     if (id > last && id < best && (FLAG(c, id) & (FL_IS_BOOST | FL_TOUCH)) == FL_IS_BOOST) best = id;
@@ -409,6 +430,7 @@ DEV void static_update_phase(Nin& n, Ctx& c) {
         }
     } else {
         // ninja in the border ring or outside the map: test everything (exact, never taken in practice)
+        #pragma unroll 1
         for (int id = 0; id < c.n_ent; id++) {
             int kind = ent_kind(c, id);
             uint8_t fl = FLAG(c, id);
@@ -422,25 +444,31 @@ DEV void static_update_phase(Nin& n, Ctx& c) {
 // f(id) is called for every active entity of the nine cells, x-major over cells, list order inside a cell.
 template <class F>
 DEV void gather_entities(Ctx& c, double xpos, double ypos, F&& f) {
-    int cx = clampi(floordiv(xpos, 24.0), 0, 43), cy = clampi(floordiv(ypos, 24.0), 0, 24);
+    int cx = clampi(floordiv24(xpos), 0, 43), cy = clampi(floordiv24(ypos), 0, 24);
     int x0 = max(cx - 1, 0), x1 = min(cx + 1, 43), y0 = max(cy - 1, 0), y1 = min(cy + 1, 24);
     int nroam = 0;
+    #pragma unroll 1
     for (int s = 0; s < c.n_dyn; s++) {
         int cell = DYNI(c, s, 0);
         if (cell >= 0) { int ex = cell / NPP_NCY, ey = cell - ex * NPP_NCY; if (ex >= x0 && ex <= x1 && ey >= y0 && ey <= y1) nroam++; }
     }
     if (nroam == 0) {
+        #pragma unroll 1
         for (int xc = x0; xc <= x1; xc++) {
             int a = __ldg(c.ecell_off + xc * NPP_NCY + y0), b = __ldg(c.ecell_off + xc * NPP_NCY + y1 + 1);
+            #pragma unroll 1
             for (int k = a; k < b; k++) { int id = __ldg(c.ecell_ids + k); if (FLAG(c, id) & FL_ACTIVE) f(id); }
         }
         return;
     }
+    #pragma unroll 1
     for (int xc = x0; xc <= x1; xc++)
+        #pragma unroll 1
         for (int yc = y0; yc <= y1; yc++) {
             int cell = xc * NPP_NCY + yc;
             int ka = __ldg(c.ecell_off + cell), kb = __ldg(c.ecell_off + cell + 1);
             int last = -1;
+            #pragma unroll 1
             for (;;) {
                 int sid = -1, sst = 0x7fffffff;
                 if (ka < kb) {
@@ -448,6 +476,7 @@ DEV void gather_entities(Ctx& c, double xpos, double ypos, F&& f) {
                     sst = c.order_mode ? sid : (int)(__ldg(reinterpret_cast<const uint32_t*>(c.ents + sid) + 7) & 0xffff);
                 }
                 int rid = -1, rst = 0x7fffffff;
+                #pragma unroll 1
                 for (int s = 0; s < c.n_dyn; s++)
                     if (DYNI(c, s, 0) == cell) { int st = DYNI(c, s, 1); if (st > last && st < rst) { rst = st; rid = __ldg(c.dyn_ent + s) & 0xffff; } }
                 if (sid < 0 && rid < 0) break;
@@ -461,6 +490,7 @@ DEV void gather_entities(Ctx& c, double xpos, double ypos, F&& f) {
 // pass that took the switch never sees them (the reference gathers its list before looping).
 DEV void commit_pending_doors(Ctx& c) {
     if (!c.pending_doors) return;
+    #pragma unroll 1
     for (int s = 0; s < c.n_dyn; s++) { int cell = DYNI(c, s, 0); if (cell <= -2) DYNI(c, s, 0) = -(cell + 2); }
     c.pending_doors = false;
 }

@@ -1,6 +1,7 @@
 // ninja.cuh -- the ninja's per-frame update.  Reference: /root/reference/nclone/ninja.py.
 #pragma once
 #include "entities.cuh"
+#include "pool.cuh"
 
 DEV void ninja_integrate(Nin& n) {                                       // ninja.py:198-206
     n.f[F_XSPEED] *= n.f[F_DRAG];
@@ -25,7 +26,7 @@ DEV bool ninja_pre_collision(Nin& n, Ctx& c, double& gx, double& gy) {
     return nphys > 0;
 }
 
-__device__ __noinline__ void ninja_collide_vs_objects(Nin& n, Ctx& c, double gx, double gy) {   // ninja.py:224-267
+DEV void ninja_collide_vs_objects(Nin& n, Ctx& c, double gx, double gy) {   // ninja.py:224-267
     gather_entities(c, gx, gy, [&](int id) {
         if (!is_physical_kind(ent_kind(c, id))) return;
         EntS e = ld_ent(c, id);
@@ -47,18 +48,22 @@ __device__ __noinline__ void ninja_collide_vs_objects(Nin& n, Ctx& c, double gx,
     });
 }
 
-DEV void ninja_collide_vs_tiles(Nin& n, const Ctx& c) {                  // ninja.py:269-379
+// ninja.py:269-379, warp-synchronous: every lane of the warp calls this; `alive` lanes collide.
+DEV void ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) {
     double dx = n.f[F_XPOS] - n.f[F_XPOS_OLD], dy = n.f[F_YPOS] - n.f[F_YPOS_OLD];
-    double time = sweep_circle_vs_tiles(c, n.f[F_XPOS_OLD], n.f[F_YPOS_OLD], dx, dy, NINJA_RADIUS * 0.5);
+    double time = pooled_sweep(wp, c, alive, n.f[F_XPOS_OLD], n.f[F_YPOS_OLD], dx, dy);
     double xpos = n.f[F_XPOS_OLD] + time * dx;       // recomputed even when time == 1 (not a no-op in fp)
     double ypos = n.f[F_YPOS_OLD] + time * dy;
     // segments are gathered once, around the post-sweep position (ninja.py:282-285)
     const double gx1 = xpos - NINJA_RADIUS, gy1 = ypos - NINJA_RADIUS, gx2 = xpos + NINJA_RADIUS, gy2 = ypos + NINJA_RADIUS;
     double xspeed = n.f[F_XSPEED], yspeed = n.f[F_YSPEED];
-    for (int it = 0; it < 32; it++) {
-        double a, b;
-        int result = get_single_closest_point(c, gx1, gy1, gx2, gy2, xpos, ypos, NINJA_RADIUS, a, b);
-        if (result == 0) break;
+    bool need = alive;
+    #pragma unroll 1
+    for (int it = 0; it < 32 && __any_sync(FULL_MASK, need); it++) {
+        double a = 0, b = 0;
+        int result = pooled_closest_point(wp, c, need, gx1, gy1, gx2, gy2, xpos, ypos, a, b);
+        if (!need) continue;
+        if (result == 0) { need = false; continue; }
         dx = xpos - a; dy = ypos - b;
         if (fabs(dx) <= 0.0000001) {                  // ninja.py:312-318 band-aid
             dx = 0;
@@ -66,10 +71,10 @@ DEV void ninja_collide_vs_tiles(Nin& n, const Ctx& c) {                  // ninj
             if (xpos == 49.153536108584795) dx = 0x1p-47;
         }
         double dist_sq = dx * dx + dy * dy;
-        if (dist_sq < 1e-16) break;
+        if (dist_sq < 1e-16) { need = false; continue; }
         double dist = sqrt(dist_sq);
         double depen_len = NINJA_RADIUS - dist * result;
-        if (depen_len < 0.0000001) break;
+        if (depen_len < 0.0000001) { need = false; continue; }
         double inv_dist = 1.0 / dist;
         double norm_dx = dx * inv_dist, norm_dy = dy * inv_dist;
         double depen_x = norm_dx * depen_len, depen_y = norm_dy * depen_len;
@@ -86,17 +91,13 @@ DEV void ninja_collide_vs_tiles(Nin& n, const Ctx& c) {                  // ninj
         if (dy >= -0.0001) { n.i[I_CEILING_COUNT] += 1; n.f[F_CEIL_NX] += norm_dx; n.f[F_CEIL_NY] += norm_dy; }
         else { n.i[I_FLOOR_COUNT] += 1; n.f[F_FLOOR_NX] += norm_dx; n.f[F_FLOOR_NY] += norm_dy; }
     }
-    n.f[F_XPOS] = xpos; n.f[F_YPOS] = ypos; n.f[F_XSPEED] = xspeed; n.f[F_YSPEED] = yspeed;
+    if (alive) { n.f[F_XPOS] = xpos; n.f[F_YPOS] = ypos; n.f[F_XSPEED] = xspeed; n.f[F_YSPEED] = yspeed; }
 }
 
-DEV void ninja_post_collision(Nin& n, Ctx& c) {                          // ninja.py:381-537
-    double wall_normal = 0;
-    gather_entities(c, n.f[F_XPOS], n.f[F_YPOS], [&](int id) {
-        if (ent_kind(c, id) != NPP_K_BOOST) ent_logical_collision(n, c, id, wall_normal);   // boost pads are not logical-collidable
-    });
-    commit_pending_doors(c);
+// literal per-thread wall test (ninja.py:422-441) with exact squares: fallback of the pooled version
+__device__ __noinline__ double wall_terms_exact(const uint32_t* cell_hdr, const uint32_t* segs, double xpos, double ypos, double wall_normal) {
+    Ctx c; c.cell_hdr = cell_hdr; c.segs = segs;
     const double rad = NINJA_RADIUS + 0.1;
-    const double xpos = n.f[F_XPOS], ypos = n.f[F_YPOS];
     query_region(c, xpos - rad, ypos - rad, xpos + rad, ypos + rad, [&](uint32_t s) {
         bool back; double a, b;
         seg_closest_point(s, xpos, ypos, back, a, b);
@@ -105,6 +106,30 @@ DEV void ninja_post_collision(Nin& n, Ctx& c) {                          // ninj
         if (fabs(dy) < 0.00001 && 0 < dist && dist <= rad) wall_normal += dx / dist;
         return true;
     });
+    return wall_normal;
+}
+
+// ninja.py:381-537, warp-synchronous
+DEV void ninja_post_collision(Nin& n, Ctx& c, WarpPool& wp, bool alive) {
+    double wall_normal = 0;
+    int ent_pos = 0, ent_neg = 0; bool ent_other = false;
+    if (alive) {
+        gather_entities(c, n.f[F_XPOS], n.f[F_YPOS], [&](int id) {
+            if (ent_kind(c, id) == NPP_K_BOOST) return;            // boost pads are not logical-collidable
+            double before = wall_normal;
+            ent_logical_collision(n, c, id, wall_normal);
+            double d = wall_normal - before;                        // entity terms are exactly +-1 (or absent)
+            if (wall_normal != before) { if (d == 1.0) ent_pos++; else if (d == -1.0) ent_neg++; else ent_other = true; }
+        });
+        commit_pending_doors(c);
+    }
+    int npos, nneg; bool uncertain;
+    pooled_wall_test(wp, c, alive, n.f[F_XPOS], n.f[F_YPOS], npos, nneg, uncertain);
+    if (!alive) return;
+    // only the sign of the total is used (ninja.py:447-449); every term is +-1 or +-(1 - 1e-10)
+    int bal = (ent_pos + npos) - (ent_neg + nneg);
+    if (uncertain || ent_other || (bal == 0 && (npos + nneg) > 0)) wall_normal = wall_terms_exact(c.cell_hdr, c.segs, n.f[F_XPOS], n.f[F_YPOS], wall_normal);
+    else wall_normal = (double)bal;
     n.i[I_AIRBORN_OLD] = n.i[I_AIRBORN];
     n.i[I_AIRBORN] = 1; n.i[I_WALLED] = 0;
     if (wall_normal != 0) { n.i[I_WALLED] = 1; n.f[F_WALL_NORMAL] = wall_normal / fabs(wall_normal); }
@@ -291,28 +316,32 @@ DEV void ninja_think(Nin& n) {                                           // ninj
     }
 }
 
-// Simulator.tick: nsim.py:221-292 (headless: enable_anim, log_data false)
-DEV void sim_tick(Nin& n, Ctx& c, int hor_input, int jump_input) {
-    n.i[I_FRAME] += 1;
-    n.i[I_HOR_INPUT] = hor_input; n.i[I_JUMP_INPUT] = jump_input;
-    n.f[F_X_AT_ACTION] = n.f[F_XPOS]; n.f[F_Y_AT_ACTION] = n.f[F_YPOS];   // ninja.py:841-847
-    // all move() then all think(): roaming entities in slot (= entity_dic) order, mines and boost
-    // pads by neighbourhood (they are independent of every other entity's update)
-    dyn_move_phase(c);
-    static_update_phase(n, c);
-    dyn_think_phase(n, c);
-    int state = n.i[I_STATE];
-    if (state != 9) {
-        if (state != 6) {        // dead: ragdoll is None when enable_anim=False (ninja.py:122-128)
+// Simulator.tick: nsim.py:221-292 (headless: enable_anim, log_data false).  Warp-synchronous: all 32
+// lanes call it together; `run` lanes advance their env by one frame.
+DEV void sim_tick(Nin& n, Ctx& c, WarpPool& wp, bool run, int hor_input, int jump_input) {
+    bool alive = false, phys = false;
+    double gx = 0, gy = 0;
+    if (run) {
+        n.i[I_FRAME] += 1;
+        n.i[I_HOR_INPUT] = hor_input; n.i[I_JUMP_INPUT] = jump_input;
+        n.f[F_X_AT_ACTION] = n.f[F_XPOS]; n.f[F_Y_AT_ACTION] = n.f[F_YPOS];   // ninja.py:841-847
+        // all move() then all think(): roaming entities in slot (= entity_dic) order, mines and boost
+        // pads by neighbourhood (they are independent of every other entity's update)
+        dyn_move_phase(c);
+        static_update_phase(n, c);
+        dyn_think_phase(n, c);
+        int state = n.i[I_STATE];
+        alive = (state != 9 && state != 6);      // dead: ragdoll is None when enable_anim=False (ninja.py:122-128)
+        if (alive) {
             ninja_integrate(n);
-            double gx, gy;
-            bool phys = ninja_pre_collision(n, c, gx, gy);
-            for (int s = 0; s < 4; s++) {
-                if (phys) ninja_collide_vs_objects(n, c, gx, gy);
-                ninja_collide_vs_tiles(n, c);
-            }
-            ninja_post_collision(n, c);
+            phys = ninja_pre_collision(n, c, gx, gy);
         }
-        ninja_think(n);
     }
+    #pragma unroll 1
+    for (int s = 0; s < 4; s++) {
+        if (phys) ninja_collide_vs_objects(n, c, gx, gy);
+        ninja_collide_vs_tiles(n, c, wp, alive);
+    }
+    ninja_post_collision(n, c, wp, alive);
+    if (run && n.i[I_STATE] != 9) ninja_think(n);
 }

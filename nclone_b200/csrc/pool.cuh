@@ -1,0 +1,298 @@
+// pool.cuh -- warp-pooled tile-segment queries.
+//
+// Why: segment queries are sparse (mean 1.65 segments per query, median 0).  With one
+// thread per env and a per-thread loop over "my" segments, a warp executed the per-segment maths with
+// 1-3 of 32 lanes active (profiles/r01_a: 4.9 lanes on average).  Here the 32 envs of a warp put
+// their (owner lane, segment) pairs into a shared-memory queue and all 32 lanes sweep that queue, so
+// the expensive fp64 work runs on dense lanes; each owner then folds its own items in reference order.
+//
+// Exactness: SQ() (glibc pow emulation) is expensive, so the comparison-only sites use x*x plus a
+// guard band: a decision is taken from the cheap value only when it is provably the same for any
+// squares within 1 ulp of it; otherwise the literal reference expression with exact SQ() is evaluated.
+#pragma once
+#include "geom.cuh"
+
+#define POOL_CAP 256                 // 32 lanes x at most 8 segments per cell per round
+#define FULL_MASK 0xffffffffu
+
+struct WarpPool {
+    double par[5][32];               // per-owner query parameters
+    double res[POOL_CAP];            // per-item result (time of impact | adjusted distance^2 | wall term)
+    double ra[POOL_CAP], rb[POOL_CAP];   // per-item closest point
+    uint32_t seg[POOL_CAP];
+    uint8_t own[POOL_CAP], aux[POOL_CAP];
+};
+
+// ---- per-lane iterator over the cells of a query box (SpatialSegmentIndex.query_region order) ----------
+struct CellIter { int cx1, cy0, cy1, xc, yc; double min_x, min_y, max_x, max_y; bool more; };
+DEV void cell_iter_init(CellIter& it, bool active, double x1, double y1, double x2, double y2) {
+    it.min_x = (x2 < x1) ? x2 : x1; it.min_y = (y2 < y1) ? y2 : y1;
+    it.max_x = (x2 > x1) ? x2 : x1; it.max_y = (y2 > y1) ? y2 : y1;
+    it.xc = clampi(floordiv24(it.min_x), 0, 43); it.cx1 = clampi(floordiv24(it.max_x), 0, 43);
+    it.cy0 = clampi(floordiv24(it.min_y), 0, 24); it.cy1 = clampi(floordiv24(it.max_y), 0, 24);
+    it.yc = it.cy0;
+    it.more = active;
+}
+// next cell that is present in cell_data and whose AABB meets the query; returns its segment count (0 = exhausted)
+DEV int cell_iter_next(CellIter& it, const Ctx& c, int& cell) {
+    #pragma unroll 1
+    while (it.xc <= it.cx1) {
+        int xc = it.xc, yc = it.yc;
+        if (++it.yc > it.cy1) { it.yc = it.cy0; it.xc++; }
+        int ci = xc * NPP_NCY + yc;
+        uint32_t hdr = __ldg(c.cell_hdr + ci);
+        int cnt = hdr & 15;
+        if (!cnt) continue;
+        double bx0 = 12.0 * (double)(int)((hdr >> 4) & 127), by0 = 12.0 * (double)(int)((hdr >> 11) & 63);
+        double bx1 = 12.0 * (double)(int)((hdr >> 17) & 127), by1 = 12.0 * (double)(int)((hdr >> 24) & 63);
+        if (it.max_x < bx0 || it.min_x > bx1 || it.max_y < by0 || it.min_y > by1) continue;
+        cell = ci;
+        return cnt;
+    }
+    it.more = false;
+    return 0;
+}
+
+// All 32 lanes must call this together.  item(j, seg, owner) fills wp.res/ra/rb/aux[j];
+// fold(off, cnt) lets an owner consume its items [off, off+cnt) in order and returns false to stop early.
+template <class ItemF, class FoldF>
+DEV void pooled_query(WarpPool& wp, const Ctx& c, bool active, double x1, double y1, double x2, double y2, ItemF&& item, FoldF&& fold) {
+    const int lane = threadIdx.x & 31;
+    CellIter it;
+    cell_iter_init(it, active, x1, y1, x2, y2);
+    #pragma unroll 1
+    while (__any_sync(FULL_MASK, it.more)) {
+        int cell = 0, cnt = 0;
+        if (it.more) cnt = cell_iter_next(it, c, cell);
+        int incl = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { int v = __shfl_up_sync(FULL_MASK, incl, d); if (lane >= d) incl += v; }
+        const int off = incl - cnt;
+        const int total = __shfl_sync(FULL_MASK, incl, 31);
+        if (total == 0) continue;
+        #pragma unroll 1
+        for (int k = 0; k < cnt; k++) { wp.seg[off + k] = __ldg(c.segs + cell * NPP_SEGS_PER_CELL + k); wp.own[off + k] = (uint8_t)lane; }
+        __syncwarp();
+        #pragma unroll 1
+        for (int j = lane; j < total; j += 32) item(j, wp.seg[j], (int)wp.own[j]);
+        __syncwarp();
+        if (cnt > 0 && !fold(off, cnt)) it.more = false;
+        __syncwarp();
+    }
+}
+
+// ---- time of impact, guarded ------------------------------------------------------------------------
+// literal physics.py:247-261 (out of line: reached only when the guarded version cannot decide)
+__device__ __noinline__ double toi_circle_exact(double dx, double dy, double dot_prod, double vx, double vy, double rr) {
+    double vel_sq = SQ(vx) + SQ(vy);
+    double dist_sq = SQ(dx) + SQ(dy);
+    if (dist_sq - rr > 0) {
+        double radicand = SQ(dot_prod) - vel_sq * (dist_sq - rr);
+        if (vel_sq > 0.0001 && dot_prod < 0 && radicand >= 0) return (-dot_prod - sqrt(radicand)) / vel_sq;
+        return 1;
+    }
+    return 0;
+}
+// Same value as the reference's get_time_of_intersection_circle_vs_circle whenever that value is < 1
+// or == 0; otherwise some value >= 1 (callers only ever test `== 0` and `< shortest` with
+// shortest <= 1: physics.py:119-126, entities.py:96).  vel_a = vx*vx + vy*vy (cheap squares).
+DEV double toi_circle_guarded(double xpos, double ypos, double vx, double vy, double vel_a, double a, double b, double rr) {
+    const double dx = xpos - a, dy = ypos - b;
+    const double dot_prod = dx * vx + dy * vy;
+    const double m = dx * dx + dy * dy;                 // within 3 ulp of dx**2 + dy**2
+    const double diff = m - rr;
+    const double g = 1e-13 * (m + rr);
+    if (diff > g) {                                       // certainly outside the circle
+        if (!(dot_prod < 0)) return 1;
+        if (vel_a < 0.0001 * (1 - 1e-12)) return 1;       // vel_sq > 0.0001 certainly false
+        if (vel_a > 0.0001 * (1 + 1e-12)) {
+            const double d2 = dot_prod * dot_prod;
+            const double R = d2 - vel_a * diff;
+            const double E = 1e-13 * (d2 + vel_a * (m + rr));
+            if (R < -E) return 1;                         // radicand certainly negative
+            if (R > E) {
+                const double t_lo = (-dot_prod - sqrt(R + E)) / vel_a;   // below the true root
+                if (t_lo > 1.000000001) return 1;         // certainly later than this frame
+            }
+        }
+    } else if (diff < -g) {
+        return 0;                                         // certainly inside
+    }
+    return toi_circle_exact(dx, dy, dot_prod, vx, vy, rr);
+}
+// physics.py:264-285; the segment's end points are integers, so wx**2 + wy**2 is exact as a product
+DEV double toi_lineseg_int(double xpos, double ypos, double dx, double dy, double a1, double b1, double a2, double b2, double radius) {
+    double wx = a2 - a1, wy = b2 - b1;
+    double seg_len = sqrt(wx * wx + wy * wy);
+    double nx = wx / seg_len, ny = wy / seg_len;
+    double normal_proj = (xpos - a1) * ny - (ypos - b1) * nx;
+    double hor_proj = (xpos - a1) * nx + (ypos - b1) * ny;
+    if (fabs(normal_proj) >= radius) {
+        double dir = dx * ny - dy * nx;
+        if (dir * normal_proj < 0) {
+            double q = (fabs(normal_proj) - radius) / fabs(dir);
+            double t = (1 < q) ? 1 : q;
+            double hor_proj2 = hor_proj + t * (dx * nx + dy * ny);
+            if (0 <= hor_proj2 && hor_proj2 <= seg_len) return t;
+        }
+    } else {
+        if (0 <= hor_proj && hor_proj <= seg_len) return 0;
+    }
+    return 1;
+}
+// physics.py:288-314
+__device__ __noinline__ double toi_arc_exact(double xpos, double ypos, double vx, double vy, double a, double b, double hor, double ver, double radius_circle) {
+    double dx = xpos - a, dy = ypos - b;
+    double dist_sq = SQ(dx) + SQ(dy);
+    double vel_sq = SQ(vx) + SQ(vy);
+    double dot_prod = dx * vx + dy * vy;
+    double radius1 = 24.0 + radius_circle, radius2 = 24.0 - radius_circle;
+    double rr1 = radius1 * radius1, rr2 = radius2 * radius2;             // small integers or x.5 halves: exact
+    double t = 1;
+    if (dist_sq > rr1) {
+        double radicand = SQ(dot_prod) - vel_sq * (dist_sq - rr1);
+        if (vel_sq > 0.0001 && dot_prod < 0 && radicand >= 0) t = (-dot_prod - sqrt(radicand)) / vel_sq;
+    } else if (dist_sq < rr2) {
+        double radicand = SQ(dot_prod) - vel_sq * (dist_sq - rr2);
+        if (vel_sq > 0.0001) { double q = (-dot_prod + sqrt(radicand)) / vel_sq; t = (1 < q) ? 1 : q; }
+    } else {
+        t = 0;
+    }
+    if ((dx + t * vx) * hor > 0 && (dy + t * vy) * ver > 0) return t;
+    return 1;
+}
+// entities.py:82-96,180-203 for the ninja's sweep radius (an exactly representable square)
+DEV double seg_toi_guarded(uint32_t s, double xpos, double ypos, double dx, double dy, double vel_a, double radius, double rr) {
+    if (!(s & NPP_SEG_ARC)) {
+        SegLin l = dec_lin(s);
+        double t1 = toi_circle_guarded(xpos, ypos, dx, dy, vel_a, l.x1, l.y1, rr);
+        double t2 = toi_circle_guarded(xpos, ypos, dx, dy, vel_a, l.x2, l.y2, rr);
+        double t3 = toi_lineseg_int(xpos, ypos, dx, dy, l.x1, l.y1, l.x2, l.y2, radius);
+        return min3(t1, t2, t3);
+    } else {
+        SegArc a = dec_arc(s);
+        double t1 = toi_circle_guarded(xpos, ypos, dx, dy, vel_a, a.cx + 24.0 * a.hor, a.cy, rr);
+        double t2 = toi_circle_guarded(xpos, ypos, dx, dy, vel_a, a.cx, a.cy + 24.0 * a.ver, rr);
+        double t3 = toi_arc_exact(xpos, ypos, dx, dy, a.cx, a.cy, a.hor, a.ver, radius);
+        return min3(t1, t2, t3);
+    }
+}
+
+// ---- pooled sweep_circle_vs_tiles (physics.py:104-128), ninja radius 5 -----------------------------------
+// The reference returns 0 as soon as a segment reports exactly 0, else the minimum; the owner's fold
+// walks its items in list order with the same early exit.
+DEV double pooled_sweep(WarpPool& wp, const Ctx& c, bool active, double xpos_old, double ypos_old, double dx, double dy) {
+    const int lane = threadIdx.x & 31;
+    const double radius = NINJA_RADIUS * 0.5;
+    double xpos_new = xpos_old + dx, ypos_new = ypos_old + dy;
+    double width = radius + 1;
+    double x1 = (xpos_old < xpos_new ? xpos_old : xpos_new) - width;
+    double y1 = (ypos_old < ypos_new ? ypos_old : ypos_new) - width;
+    double x2 = (xpos_old > xpos_new ? xpos_old : xpos_new) + width;
+    double y2 = (ypos_old > ypos_new ? ypos_old : ypos_new) + width;
+    wp.par[0][lane] = xpos_old; wp.par[1][lane] = ypos_old; wp.par[2][lane] = dx; wp.par[3][lane] = dy; wp.par[4][lane] = dx * dx + dy * dy;
+    __syncwarp();
+    double shortest = 1;
+    pooled_query(wp, c, active, x1, y1, x2, y2,
+        [&](int j, uint32_t s, int o) {
+            wp.res[j] = seg_toi_guarded(s, wp.par[0][o], wp.par[1][o], wp.par[2][o], wp.par[3][o], wp.par[4][o], radius, radius * radius);
+        },
+        [&](int off, int cnt) {
+            #pragma unroll 1
+            for (int k = 0; k < cnt; k++) {
+                double t = wp.res[off + k];
+                if (t == 0) { shortest = 0; return false; }
+                if (t < shortest) shortest = t;
+            }
+            return true;
+        });
+    return shortest;
+}
+
+// literal per-thread get_single_closest_point with exact squares (out of line, rare)
+__device__ __noinline__ int closest_point_exact(const uint32_t* cell_hdr, const uint32_t* segs, double gx1, double gy1, double gx2, double gy2,
+                                                double xpos, double ypos, double& pa, double& pb) {
+    Ctx c; c.cell_hdr = cell_hdr; c.segs = segs;
+    return get_single_closest_point(c, gx1, gy1, gx2, gy2, xpos, ypos, NINJA_RADIUS, pa, pb);
+}
+
+// ---- pooled get_single_closest_point (physics.py:131-180), radius 10 -----------------------------------------
+// Items carry the cheap adjusted squared distance; the owner's strict-< scan accepts a comparison only
+// when it cannot flip under 1-ulp changes of the squares (or both items are the same point and side);
+// otherwise it re-runs the literal per-thread version with exact SQ().
+DEV int pooled_closest_point(WarpPool& wp, const Ctx& c, bool active, double gx1, double gy1, double gx2, double gy2,
+                             double xpos, double ypos, double& pa, double& pb) {
+    const int lane = threadIdx.x & 31;
+    wp.par[0][lane] = xpos; wp.par[1][lane] = ypos;
+    __syncwarp();
+    double best = __longlong_as_double(0x7ff0000000000000LL), ba = 0, bb = 0;
+    int result = 0;
+    bool uncertain = false;
+    pooled_query(wp, c, active, gx1, gy1, gx2, gy2,
+        [&](int j, uint32_t s, int o) {
+            const double x = wp.par[0][o], y = wp.par[1][o];
+            double sx0, sy0, sx1, sy1;
+            seg_bounds(s, sx0, sy0, sx1, sy1);
+            if (sx1 < x - NINJA_RADIUS || sx0 > x + NINJA_RADIUS || sy1 < y - NINJA_RADIUS || sy0 > y + NINJA_RADIUS) { wp.aux[j] = 2; return; }
+            bool back; double a, b;
+            seg_closest_point(s, x, y, back, a, b);
+            double ex = x - a, ey = y - b;
+            double d2 = ex * ex + ey * ey;
+            if (!back) d2 -= 0.1;
+            wp.res[j] = d2; wp.ra[j] = a; wp.rb[j] = b; wp.aux[j] = back ? 1 : 0;
+        },
+        [&](int off, int cnt) {
+            #pragma unroll 1
+            for (int k = 0; k < cnt; k++) {
+                int ax = wp.aux[off + k];
+                if (ax == 2) continue;                                   // AABB-rejected
+                double d2 = wp.res[off + k], a = wp.ra[off + k], b = wp.rb[off + k];
+                int r = ax ? -1 : 1;
+                const double G = 1e-10;                                  // >> 3 ulp of any d2 here (<= 800)
+                if (d2 < best - G) { best = d2; ba = a; bb = b; result = r; }
+                else if (d2 > best + G) { }
+                else if (a == ba && b == bb && r == result) { }          // identical inputs: exact values tie, first wins
+                else uncertain = true;
+            }
+            return true;
+        });
+    if (uncertain) return closest_point_exact(c.cell_hdr, c.segs, gx1, gy1, gx2, gy2, xpos, ypos, pa, pb);
+    pa = ba; pb = bb;
+    return result;
+}
+
+// ---- pooled wall test of post_collision (ninja.py:422-441) ----------------------------------------------------
+// Each qualifying segment adds dx/dist = +-(1 - eps), eps < 1e-12, and only the sign of the total is
+// used (ninja.py:447-449).  Returns the counts of positive / negative terms; `uncertain` when a
+// `dist <= rad` test is within the guard band.
+DEV void pooled_wall_test(WarpPool& wp, const Ctx& c, bool active, double xpos, double ypos, int& npos, int& nneg, bool& uncertain) {
+    const int lane = threadIdx.x & 31;
+    const double rad = NINJA_RADIUS + 0.1;
+    wp.par[0][lane] = xpos; wp.par[1][lane] = ypos;
+    __syncwarp();
+    npos = 0; nneg = 0; uncertain = false;
+    pooled_query(wp, c, active, xpos - rad, ypos - rad, xpos + rad, ypos + rad,
+        [&](int j, uint32_t s, int o) {
+            const double x = wp.par[0][o], y = wp.par[1][o];
+            bool back; double a, b;
+            seg_closest_point(s, x, y, back, a, b);
+            double dx = x - a, dy = y - b;
+            int code = 0;                                                // 0 none, 1 positive, 2 negative, 3 uncertain
+            if (fabs(dy) < 0.00001) {
+                double dist = sqrt(dx * dx + dy * dy);
+                if (dist > 0) {                                          // dist == 0 iff dx == dy == 0, exact either way
+                    if (dist <= rad - 1e-9) code = (dx > 1.0) ? 1 : ((dx < -1.0) ? 2 : 3);   // |dx| > 1: the term is +-(1 - 1e-10)
+                    else if (dist < rad + 1e-9) code = 3;
+                }
+            }
+            wp.aux[j] = (uint8_t)code;
+        },
+        [&](int off, int cnt) {
+            #pragma unroll 1
+            for (int k = 0; k < cnt; k++) {
+                int code = wp.aux[off + k];
+                if (code == 1) npos++; else if (code == 2) nneg++; else if (code == 3) uncertain = true;
+            }
+            return true;
+        });
+}

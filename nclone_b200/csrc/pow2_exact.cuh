@@ -93,20 +93,34 @@ POW2_SLOW double pow2_table_path(double x) {
 }
 
 // Python `x ** 2` for a float x.
+#ifdef __CUDACC__
+POW2_FN double pow2_exact(double x) {
+    const double hi = x * x;
+    const double lo = __fma_rn(x, x, -hi);                     // exact: x*x == hi + lo
+    const int hw = __double2hiint(hi);
+    const int eb = hw & 0x7ff00000;
+    // outside [2^-200, 2^200] (incl. 0, inf, nan) the table path's preconditions are not checked: x*x
+    if ((unsigned)(eb - 0x33700000) > (unsigned)(0x4c800000 - 0x33700000)) return hi;
+    const double thr = __hiloint2double(eb - 0x03500000, 0) * 0.96875;      // (1 - 2/64) * ulp/2, exact
+    if (fabs(lo) < thr && ((hw & 0x000fffff) | __double2loint(hi)) != 0) return hi;
+    if (hi == 1.0 && lo == 0) return hi;                       // |x| == 1: log is exactly 0 (special-cased in glibc)
+    return pow2_table_path(x);
+}
+#else
 POW2_FN double pow2_exact(double x) {
     const double hi = x * x;
     const double lo = POW2_FMA(x, x, -hi);                    // exact: x*x == hi + lo
     const uint64_t hb = POW2_AS_U64(hi);
     const uint64_t eb = hb & 0x7ff0000000000000ULL;
-    // outside [2^-200, 2^200] (incl. 0, inf, nan) the table path's preconditions are not checked: x*x
     if (eb - 0x3370000000000000ULL > 0x4c80000000000000ULL - 0x3370000000000000ULL) return hi;
     const double half_ulp = POW2_AS_F64(eb - 0x0350000000000000ULL);          // 2^(e-53)
-    const double thr = half_ulp * 0.96875;                     // (1 - 2/64) * ulp/2, exact
+    const double thr = half_ulp * 0.96875;
     const double alo = lo < 0 ? -lo : lo;
     if (alo < thr && (hb & 0x000fffffffffffffULL) != 0) return hi;
-    if (hi == 1.0 && lo == 0) return hi;                        // |x| == 1: log is exactly 0 (special-cased in glibc)
+    if (hi == 1.0 && lo == 0) return hi;
     return pow2_table_path(x);
 }
+#endif
 
 #ifdef __CUDACC__
 DEV double SQ(double x) { return pow2_exact(x); }
