@@ -49,7 +49,10 @@ DEV void ninja_collide_vs_objects(Nin& n, Ctx& c, double gx, double gy) {   // n
 }
 
 // ninja.py:269-379, warp-synchronous: every lane of the warp calls this; `alive` lanes collide.
-DEV void ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) {
+// Returns true when the substep changed nothing (position bit-identical, no depenetration push).
+DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) {
+    const double xin = n.f[F_XPOS], yin = n.f[F_YPOS];
+    bool pushed = false;
     double dx = n.f[F_XPOS] - n.f[F_XPOS_OLD], dy = n.f[F_YPOS] - n.f[F_YPOS_OLD];
     double time = pooled_sweep(wp, c, alive, n.f[F_XPOS_OLD], n.f[F_YPOS_OLD], dx, dy);
     double xpos = n.f[F_XPOS_OLD] + time * dx;       // recomputed even when time == 1 (not a no-op in fp)
@@ -78,6 +81,7 @@ DEV void ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
         double inv_dist = 1.0 / dist;
         double norm_dx = dx * inv_dist, norm_dy = dy * inv_dist;
         double depen_x = norm_dx * depen_len, depen_y = norm_dy * depen_len;
+        pushed = true;
         xpos += depen_x; ypos += depen_y;
         n.f[F_XCRUSH] += depen_x; n.f[F_YCRUSH] += depen_y; n.f[F_CRUSH_LEN] += depen_len;
         double dot_product = xspeed * dx + yspeed * dy;
@@ -92,6 +96,7 @@ DEV void ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
         else { n.i[I_FLOOR_COUNT] += 1; n.f[F_FLOOR_NX] += norm_dx; n.f[F_FLOOR_NY] += norm_dy; }
     }
     if (alive) { n.f[F_XPOS] = xpos; n.f[F_YPOS] = ypos; n.f[F_XSPEED] = xspeed; n.f[F_YSPEED] = yspeed; }
+    return !pushed && __double_as_longlong(xpos) == __double_as_longlong(xin) && __double_as_longlong(ypos) == __double_as_longlong(yin);
 }
 
 // literal per-thread wall test (ninja.py:422-441) with exact squares: fallback of the pooled version
@@ -337,10 +342,15 @@ DEV void sim_tick(Nin& n, Ctx& c, WarpPool& wp, bool run, int hor_input, int jum
             phys = ninja_pre_collision(n, c, gx, gy);
         }
     }
+    // The four substeps (nsim.py:263-267).  A substep without entity pushes that leaves the position
+    // bit-identical and performs no depenetration is a pure function of unchanged inputs, so the remaining
+    // substeps would repeat it verbatim: they are skipped (typical: free flight, or resting after substep 2).
+    bool sub = alive;
     #pragma unroll 1
-    for (int s = 0; s < 4; s++) {
-        if (phys) ninja_collide_vs_objects(n, c, gx, gy);
-        ninja_collide_vs_tiles(n, c, wp, alive);
+    for (int s = 0; s < 4 && __any_sync(FULL_MASK, sub); s++) {
+        if (sub && phys) ninja_collide_vs_objects(n, c, gx, gy);
+        bool idle = ninja_collide_vs_tiles(n, c, wp, sub);
+        if (idle && !phys) sub = false;
     }
     ninja_post_collision(n, c, wp, alive);
     if (run && n.i[I_STATE] != 9) ninja_think(n);

@@ -164,3 +164,70 @@ def test_step_host_matches_device_path(golden_replays):
         s2.step_host(a[k], pv, st, 4, True)
     assert np.array_equal(s1.nin_f[:4].cpu().numpy().view(np.int64), pv.view(np.int64))
     assert np.array_equal(s1.nin_i[0].cpu().numpy(), st)
+
+
+def _oracle_rollout(maps, env_to_map, actions, frame_skip, max_frames, check_every):
+    """Oracle side of test_large_random_rollout: list of (step, nin_f[N,31], nin_i[N,27]) checkpoints.
+    Same policy as bench.py: early exit on win/death inside the frame-skip, Simulator.reset() on
+    terminal / max_frames after the step."""
+    from oracle import oracle as orc
+    N = len(env_to_map)
+    sims = []
+    for k in range(N):
+        s = orc.OracleSim(); s.load(maps[env_to_map[k]]); sims.append(s)
+    L = orc.lib()
+    out = []
+    nf = np.zeros((N, 31)); ni = np.zeros((N, 27), dtype=np.int64)
+    import ctypes as C
+    for st in range(actions.shape[0]):
+        for k, s in enumerate(sims):
+            h, j = ((0, 0), (-1, 0), (1, 0), (0, 1), (-1, 1), (1, 1))[actions[st, k]]
+            for _ in range(frame_skip):
+                L.osim_tick(s.h, h, j)
+                L.osim_get_state(s.h, nf[k].ctypes.data_as(C.POINTER(C.c_double)), ni[k].ctypes.data_as(C.POINTER(C.c_int64)), None, None)
+                if ni[k, 0] in (6, 7, 8):
+                    break
+        if (st + 1) % check_every == 0:
+            out.append((st, nf.copy(), ni.copy()))
+        for k, s in enumerate(sims):
+            if ni[k, 0] in (6, 7, 8) or ni[k, 26] >= max_frames:
+                s.load(maps[env_to_map[k]])           # fresh-Simulator semantics, as nppsim_reset mode 0
+    return out
+
+
+def test_large_random_rollout_vs_oracle(golden_replays):
+    """Guard-band / pooling safety net: 2,048 envs over the benchmark's generated levels and 512 over
+    entity-rich replay levels, 240 agent steps (frame-skip 4, auto-reset): the ninja record of every env
+    is compared bit-for-bit with the oracle every 20 steps, and full entity state at the end."""
+    import torch
+    from nclone_b200 import BatchedSimulator
+    import bench
+    arr, lens = bench.load_maps("simplest_with_mines")
+    maps = [arr[k, :lens[k]] for k in range(0, 2048)]
+    arr2, lens2 = bench.load_maps("locked_doors")
+    maps += [arr2[k, :lens2[k]] for k in range(0, 256)]
+    maps += [golden_replays.traj(i)["map_data"] for i in range(0, 130)]
+    M = len(maps)
+    N = 2048 + 256 + 130 * 2
+    env_to_map = np.concatenate([np.arange(2048), 2048 + np.arange(256), 2304 + np.arange(260) % 130])
+    rng = np.random.default_rng(11)
+    steps, every = 240, 20
+    actions = rng.integers(0, 6, size=(steps, N)).astype(np.uint8)
+    # long holds make the ninja run / wall-slide / fall far: repeat each action for a few agent steps
+    hold = rng.integers(1, 6, size=(steps, N))
+    for st in range(1, steps):
+        keep = (st % hold[st]) != 0
+        actions[st, keep] = actions[st - 1, keep]
+    sim = BatchedSimulator(N)
+    sim.load_maps(maps, env_to_map)
+    ref = _oracle_rollout(maps, env_to_map, actions, 4, 2000, every)
+    ci = 0
+    for st in range(steps):
+        sim.step(torch.from_numpy(actions[st]).cuda(), 4, True)
+        if (st + 1) % every == 0:
+            _, nf, ni = ref[ci]; ci += 1
+            gf = sim.nin_f.cpu().numpy().T; gi = sim.nin_i.cpu().numpy().T.astype(np.int64)
+            badf = np.nonzero((gf.view(np.int64) != nf.view(np.int64)).any(1))[0]
+            badi = np.nonzero((gi != ni).any(1))[0]
+            assert badf.size == 0 and badi.size == 0, (st, badf[:5], badi[:5], env_to_map[badf[:5]])
+        sim.reset_terminal(2000)
