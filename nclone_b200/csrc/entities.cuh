@@ -33,8 +33,8 @@ DEV void ninja_win(Nin& n, Ctx& c) {                                   // ninja.
 }
 DEV void ninja_kill(Nin& n, Ctx& c, double x, double y, double xs, double ys, int cause) {   // ninja.py:1253-1270
     if (n.i[I_STATE] < 6) {
-        n.f[F_DEATH_X] = x; n.f[F_DEATH_Y] = y; n.f[F_DEATH_XS] = xs; n.f[F_DEATH_YS] = ys;
-        n.i[I_DEATH_CAUSE] = cause;
+        GF(c, F_DEATH_X) = x; GF(c, F_DEATH_Y) = y; GF(c, F_DEATH_XS) = xs; GF(c, F_DEATH_YS) = ys;
+        GI(c, I_DEATH_CAUSE) = cause;
         if (n.i[I_STATE] == 3) n.f[F_GRAVITY] = GRAVITY_FALL;
         n.i[I_STATE] = 7;
         c.events |= NPPSIM_EV_DEATH;
@@ -558,7 +558,7 @@ DEV void ent_logical_collision(Nin& n, Ctx& c, int id, double& wall_normal) {
         }
         break; }
     case NPP_K_GOLD:                                            // entity_gold.py:63-72
-        if (n.i[I_STATE] != 8 && overlap_circle_vs_circle(e.x, e.y, 6, px, py, NINJA_RADIUS)) { n.i[I_GOLD] += 1; FLAG(c, id) &= ~FL_ACTIVE; }
+        if (n.i[I_STATE] != 8 && overlap_circle_vs_circle(e.x, e.y, 6, px, py, NINJA_RADIUS)) { GI(c, I_GOLD) += 1; FLAG(c, id) &= ~FL_ACTIVE; }
         break;
     case NPP_K_EXIT:                                            // entity_exit.py:66-74
         if (overlap_circle_vs_circle(DYNF(c, e.dyn, 0), DYNF(c, e.dyn, 1), 12, px, py, NINJA_RADIUS)) ninja_win(n, c);
@@ -584,7 +584,7 @@ DEV void ent_logical_collision(Nin& n, Ctx& c, int id, double& wall_normal) {
         break;
     case NPP_K_DOOR_LOCKED:                                     // entity_door_locked.py:54-67
         if (overlap_circle_vs_circle(e.x, e.y, 5, px, py, NINJA_RADIUS)) {
-            n.i[I_DOORS_OPENED] += 1; door_set_closed(c, id, false); FLAG(c, id) &= ~FL_ACTIVE; c.events |= NPPSIM_EV_LOCKED_DOOR;
+            GI(c, I_DOORS_OPENED) += 1; door_set_closed(c, id, false); FLAG(c, id) &= ~FL_ACTIVE; c.events |= NPPSIM_EV_LOCKED_DOOR;
         }
         break;
     case NPP_K_DOOR_TRAP:                                       // entity_door_trap.py:60-67
@@ -602,7 +602,7 @@ DEV void ent_logical_collision(Nin& n, Ctx& c, int id, double& wall_normal) {
                 n.f[F_XSPEED] = xboost; n.f[F_YSPEED] = yboost;
                 n.i[I_FLOOR_COUNT] = 0; n.i[I_FLOOR_BUFFER] = -1;
                 double boost_scalar = sqrt(SQ(xboost) + SQ(yboost));
-                n.f[F_XLP] = xboost / boost_scalar; n.f[F_YLP] = yboost / boost_scalar;
+                GF(c, F_XLP) = xboost / boost_scalar; GF(c, F_YLP) = yboost / boost_scalar;
                 n.i[I_LP_BUFFER] = 0;
                 if (n.i[I_STATE] == 3) n.f[F_GRAVITY] = GRAVITY_FALL;
                 n.i[I_STATE] = 4;

@@ -3,6 +3,18 @@
 #include "entities.cuh"
 #include "pool.cuh"
 
+// NPP_PROFILE: per-warp cycle counters per phase (debug builds only; tools/phase_profile.py)
+#ifdef NPP_PROFILE
+__device__ unsigned long long g_phase_cycles[16];
+__device__ unsigned long long g_warp_cycles[1 << 16];      // per warp: kernel duration of the last launch
+__device__ unsigned long long g_warp_phase[1 << 16][4];   // per warp: cycles in entities / sweep / closest / post of the last launch
+#define PH_BEGIN long long _ph_t = clock64();
+#define PH_MARK(k) { long long _t2 = clock64(); if ((threadIdx.x & 31) == (__ffs(__activemask()) - 1)) { atomicAdd(&g_phase_cycles[k], (unsigned long long)(_t2 - _ph_t)); int _w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; int _b = (k) <= 3 ? 0 : ((k) == 5 ? 1 : ((k) == 6 ? 2 : (((k) == 9 || (k) == 10) ? 3 : -1))); if (_b >= 0 && _w < (1 << 16)) g_warp_phase[_w][_b] += (unsigned long long)(_t2 - _ph_t); } _ph_t = _t2; }
+#else
+#define PH_BEGIN
+#define PH_MARK(k)
+#endif
+
 DEV void ninja_integrate(Nin& n) {                                       // ninja.py:198-206
     n.f[F_XSPEED] *= n.f[F_DRAG];
     n.f[F_YSPEED] *= n.f[F_DRAG];
@@ -54,18 +66,24 @@ DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
     const double xin = n.f[F_XPOS], yin = n.f[F_YPOS];
     bool pushed = false;
     double dx = n.f[F_XPOS] - n.f[F_XPOS_OLD], dy = n.f[F_YPOS] - n.f[F_YPOS_OLD];
+    PH_BEGIN
     double time = pooled_sweep(wp, c, alive, n.f[F_XPOS_OLD], n.f[F_YPOS_OLD], dx, dy);
+    PH_MARK(5)
     double xpos = n.f[F_XPOS_OLD] + time * dx;       // recomputed even when time == 1 (not a no-op in fp)
     double ypos = n.f[F_YPOS_OLD] + time * dy;
     // segments are gathered once, around the post-sweep position (ninja.py:282-285)
     const double gx1 = xpos - NINJA_RADIUS, gy1 = ypos - NINJA_RADIUS, gx2 = xpos + NINJA_RADIUS, gy2 = ypos + NINJA_RADIUS;
     double xspeed = n.f[F_XSPEED], yspeed = n.f[F_YSPEED];
+    // iteration 0 is pooled over the warp (and caches each lane's gathered list); iterations 1..31 run
+    // per lane on the cached list
+    double a0 = 0, b0 = 0; int nseg = 0;
+    int result0 = pooled_closest_point(wp, c, alive, gx1, gy1, gx2, gy2, xpos, ypos, a0, b0, nseg);
     bool need = alive;
     #pragma unroll 1
-    for (int it = 0; it < 32 && __any_sync(FULL_MASK, need); it++) {
-        double a = 0, b = 0;
-        int result = pooled_closest_point(wp, c, need, gx1, gy1, gx2, gy2, xpos, ypos, a, b);
-        if (!need) continue;
+    for (int it = 0; it < 32 && need; it++) {
+        double a = a0, b = b0;
+        int result = result0;
+        if (it > 0) result = cached_closest_point(wp, c, nseg, gx1, gy1, gx2, gy2, xpos, ypos, a, b);
         if (result == 0) { need = false; continue; }
         dx = xpos - a; dy = ypos - b;
         if (fabs(dx) <= 0.0000001) {                  // ninja.py:312-318 band-aid
@@ -95,6 +113,7 @@ DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
         if (dy >= -0.0001) { n.i[I_CEILING_COUNT] += 1; n.f[F_CEIL_NX] += norm_dx; n.f[F_CEIL_NY] += norm_dy; }
         else { n.i[I_FLOOR_COUNT] += 1; n.f[F_FLOOR_NX] += norm_dx; n.f[F_FLOOR_NY] += norm_dy; }
     }
+    PH_MARK(6)
     if (alive) { n.f[F_XPOS] = xpos; n.f[F_YPOS] = ypos; n.f[F_XSPEED] = xspeed; n.f[F_YSPEED] = yspeed; }
     return !pushed && __double_as_longlong(xpos) == __double_as_longlong(xin) && __double_as_longlong(ypos) == __double_as_longlong(yin);
 }
@@ -116,25 +135,21 @@ __device__ __noinline__ double wall_terms_exact(const uint32_t* cell_hdr, const 
 
 // ninja.py:381-537, warp-synchronous
 DEV void ninja_post_collision(Nin& n, Ctx& c, WarpPool& wp, bool alive) {
+    PH_BEGIN
     double wall_normal = 0;
-    int ent_pos = 0, ent_neg = 0; bool ent_other = false;
     if (alive) {
         gather_entities(c, n.f[F_XPOS], n.f[F_YPOS], [&](int id) {
-            if (ent_kind(c, id) == NPP_K_BOOST) return;            // boost pads are not logical-collidable
-            double before = wall_normal;
-            ent_logical_collision(n, c, id, wall_normal);
-            double d = wall_normal - before;                        // entity terms are exactly +-1 (or absent)
-            if (wall_normal != before) { if (d == 1.0) ent_pos++; else if (d == -1.0) ent_neg++; else ent_other = true; }
+            if (ent_kind(c, id) != NPP_K_BOOST) ent_logical_collision(n, c, id, wall_normal);   // boost pads are not logical-collidable
         });
         commit_pending_doors(c);
     }
-    int npos, nneg; bool uncertain;
-    pooled_wall_test(wp, c, alive, n.f[F_XPOS], n.f[F_YPOS], npos, nneg, uncertain);
+    PH_MARK(9)
+    const double wall_entities = wall_normal;
+    bool uncertain;
+    pooled_wall_test(wp, c, alive, n.f[F_XPOS], n.f[F_YPOS], wall_normal, uncertain);
+    PH_MARK(10)
     if (!alive) return;
-    // only the sign of the total is used (ninja.py:447-449); every term is +-1 or +-(1 - 1e-10)
-    int bal = (ent_pos + npos) - (ent_neg + nneg);
-    if (uncertain || ent_other || (bal == 0 && (npos + nneg) > 0)) wall_normal = wall_terms_exact(c.cell_hdr, c.segs, n.f[F_XPOS], n.f[F_YPOS], wall_normal);
-    else wall_normal = (double)bal;
+    if (uncertain) wall_normal = wall_terms_exact(c.cell_hdr, c.segs, n.f[F_XPOS], n.f[F_YPOS], wall_entities);
     n.i[I_AIRBORN_OLD] = n.i[I_AIRBORN];
     n.i[I_AIRBORN] = 1; n.i[I_WALLED] = 0;
     if (wall_normal != 0) { n.i[I_WALLED] = 1; n.f[F_WALL_NORMAL] = wall_normal / fabs(wall_normal); }
@@ -148,7 +163,7 @@ DEV void ninja_post_collision(Nin& n, Ctx& c, WarpPool& wp, bool alive) {
             if (impact_vel > MAX_SURVIVABLE_IMPACT - 4.0 / 3 * fabs(n.f[F_FNY])) {
                 n.f[F_XSPEED] = n.f[F_XSPEED_OLD]; n.f[F_YSPEED] = n.f[F_YSPEED_OLD];
                 ninja_kill(n, c, n.f[F_XPOS], n.f[F_YPOS], n.f[F_XSPEED] * 0.5, n.f[F_YSPEED] * 0.5, 2);
-                n.i[I_TERMINAL_IMPACT] = 1;
+                GI(c, I_TERMINAL_IMPACT) = 1;
             }
         }
     }
@@ -157,14 +172,16 @@ DEV void ninja_post_collision(Nin& n, Ctx& c, WarpPool& wp, bool alive) {
     if (n.i[I_WALLED]) n.i[I_CONSEC_WALL] += 1; else n.i[I_CONSEC_WALL] = 0;
     if (n.i[I_CEILING_COUNT] > 0) {
         double ceiling_scalar = sqrt(SQ(n.f[F_CEIL_NX]) + SQ(n.f[F_CEIL_NY]));
-        if (ceiling_scalar == 0) { n.f[F_CNX] = 0; n.f[F_CNY] = 1; }
-        else { n.f[F_CNX] = n.f[F_CEIL_NX] / ceiling_scalar; n.f[F_CNY] = n.f[F_CEIL_NY] / ceiling_scalar; }
+        double cnx, cny;
+        if (ceiling_scalar == 0) { cnx = 0; cny = 1; }
+        else { cnx = n.f[F_CEIL_NX] / ceiling_scalar; cny = n.f[F_CEIL_NY] / ceiling_scalar; }
+        GF(c, F_CNX) = cnx; GF(c, F_CNY) = cny;
         if (n.i[I_STATE] != 8) {
-            double impact_vel = -(n.f[F_CNX] * n.f[F_XSPEED_OLD] + n.f[F_CNY] * n.f[F_YSPEED_OLD]);
-            if (impact_vel > MAX_SURVIVABLE_IMPACT - 4.0 / 3 * fabs(n.f[F_CNY])) {
+            double impact_vel = -(cnx * n.f[F_XSPEED_OLD] + cny * n.f[F_YSPEED_OLD]);
+            if (impact_vel > MAX_SURVIVABLE_IMPACT - 4.0 / 3 * fabs(cny)) {
                 n.f[F_XSPEED] = n.f[F_XSPEED_OLD]; n.f[F_YSPEED] = n.f[F_YSPEED_OLD];
                 ninja_kill(n, c, n.f[F_XPOS], n.f[F_YPOS], n.f[F_XSPEED] * 0.5, n.f[F_YSPEED] * 0.5, 2);
-                n.i[I_TERMINAL_IMPACT] = 1;
+                GI(c, I_TERMINAL_IMPACT) = 1;
             }
         }
     }
@@ -174,9 +191,9 @@ DEV void ninja_post_collision(Nin& n, Ctx& c, WarpPool& wp, bool alive) {
     }
 }
 
-DEV void ninja_floor_jump(Nin& n, bool was_buffered) {                   // ninja.py:539-579
+DEV void ninja_floor_jump(Nin& n, bool was_buffered, int hor_input, int& ljb) {                   // ninja.py:539-579
     n.i[I_JUMP_BUFFER] = -1; n.i[I_FLOOR_BUFFER] = -1; n.i[I_LP_BUFFER] = -1;
-    if (was_buffered) n.i[I_LAST_JUMP_BUFFERED] = 1;
+    if (was_buffered) ljb = 1;
     n.i[I_STATE] = 3;
     n.f[F_GRAVITY] = GRAVITY_JUMP;
     double jx, jy;
@@ -184,10 +201,10 @@ DEV void ninja_floor_jump(Nin& n, bool was_buffered) {                   // ninj
     else {
         double dx = n.f[F_FNX], dy = n.f[F_FNY];
         if (n.f[F_XSPEED] * dx >= 0) {
-            if (n.f[F_XSPEED] * n.i[I_HOR_INPUT] >= 0) { jx = 2.0 / 3 * dx; jy = 2 * dy; }
+            if (n.f[F_XSPEED] * hor_input >= 0) { jx = 2.0 / 3 * dx; jy = 2 * dy; }
             else { jx = 0; jy = -1.4; }
         } else {
-            if (n.f[F_XSPEED] * n.i[I_HOR_INPUT] > 0) { jx = 0; jy = -1.4; }
+            if (n.f[F_XSPEED] * hor_input > 0) { jx = 0; jy = -1.4; }
             else { n.f[F_XSPEED] = 0; jx = 2.0 / 3 * dx; jy = 2 * dy; }
         }
     }
@@ -196,11 +213,11 @@ DEV void ninja_floor_jump(Nin& n, bool was_buffered) {                   // ninj
     n.f[F_XPOS] += jx; n.f[F_YPOS] += jy;
     n.i[I_JUMP_DURATION] = 0;
 }
-DEV void ninja_wall_jump(Nin& n, bool was_buffered) {                    // ninja.py:581-608
+DEV void ninja_wall_jump(Nin& n, bool was_buffered, int hor_input, int& ljb) {                    // ninja.py:581-608
     double jx, jy;
-    if (n.i[I_HOR_INPUT] * n.f[F_WALL_NORMAL] < 0 && n.i[I_STATE] == 5) { jx = 2.0 / 3; jy = -1; }
+    if (hor_input * n.f[F_WALL_NORMAL] < 0 && n.i[I_STATE] == 5) { jx = 2.0 / 3; jy = -1; }
     else { jx = 1; jy = -1.4; }
-    if (was_buffered) n.i[I_LAST_JUMP_BUFFERED] = 1;
+    if (was_buffered) ljb = 1;
     n.i[I_STATE] = 3;
     n.f[F_GRAVITY] = GRAVITY_JUMP;
     if (n.f[F_XSPEED] * n.f[F_WALL_NORMAL] < 0) n.f[F_XSPEED] = 0;
@@ -210,19 +227,18 @@ DEV void ninja_wall_jump(Nin& n, bool was_buffered) {                    // ninj
     n.i[I_JUMP_BUFFER] = -1; n.i[I_WALL_BUFFER] = -1; n.i[I_LP_BUFFER] = -1;
     n.i[I_JUMP_DURATION] = 0;
 }
-DEV void ninja_lp_jump(Nin& n) {                                         // ninja.py:610-626
+DEV void ninja_lp_jump(Nin& n, const Ctx& c) {                                         // ninja.py:610-626
     n.i[I_FLOOR_BUFFER] = -1; n.i[I_WALL_BUFFER] = -1; n.i[I_JUMP_BUFFER] = -1; n.i[I_LP_BUFFER] = -1;
-    double boost_scalar = 2 * fabs(n.f[F_XLP]) + 2;
+    const double xlp = GF(c, F_XLP), ylp = GF(c, F_YLP);
+    double boost_scalar = 2 * fabs(xlp) + 2;
     if (boost_scalar == 2) boost_scalar = 1.7;
-    n.f[F_XSPEED] += n.f[F_XLP] * boost_scalar * (2.0 / 3);
-    n.f[F_YSPEED] += n.f[F_YLP] * boost_scalar * (2.0 / 3);
+    n.f[F_XSPEED] += xlp * boost_scalar * (2.0 / 3);
+    n.f[F_YSPEED] += ylp * boost_scalar * (2.0 / 3);
 }
 
-DEV void ninja_think(Nin& n) {                                           // ninja.py:849-1059
-    n.i[I_LAST_JUMP_BUFFERED] = 0;
+DEV void ninja_think_body(Nin& n, const Ctx& c, const int hor_input, const int jump_input, int& ljb) {   // ninja.py:849-1059
     if (n.i[I_STATE] != n.i[I_PREVIOUS_STATE]) { n.i[I_STATE_CHANGE_FRAME] = 0; n.i[I_PREVIOUS_STATE] = n.i[I_STATE]; }
     else n.i[I_STATE_CHANGE_FRAME] += 1;
-    const int hor_input = n.i[I_HOR_INPUT], jump_input = n.i[I_JUMP_INPUT];
     bool new_jump_check = jump_input ? (n.i[I_JUMP_INPUT_OLD] == 0) : false;
     n.i[I_JUMP_INPUT_OLD] = jump_input;
     int b;
@@ -238,8 +254,8 @@ DEV void ninja_think(Nin& n) {                                           // ninj
         bool has_active;
         if (just) has_active = true;
         else { int jb = n.i[I_JUMP_BUFFER]; has_active = (-1 < jb && jb < 5) || in_floor_buffer || in_wall_buffer || in_lp_buffer; }
-        n.i[I_JUMP_USELESS] = (n.i[I_AIRBORN] && n.i[I_STATE] != 3 && !has_active) ? 1 : 0;
-    } else n.i[I_JUMP_USELESS] = 0;
+        GI(c, I_JUMP_USELESS) = (n.i[I_AIRBORN] && n.i[I_STATE] != 3 && !has_active) ? 1 : 0;
+    } else GI(c, I_JUMP_USELESS) = 0;
 
     int state = n.i[I_STATE];
     if (state == 6 || state == 9) return;
@@ -291,7 +307,7 @@ DEV void ninja_think(Nin& n) {                                           // ninj
             }
             return;
         }
-        ninja_floor_jump(n, false);
+        ninja_floor_jump(n, false, hor_input, ljb);
         return;
     } else {
         double xspeed_new = n.f[F_XSPEED] + AIR_ACCEL * hor_input;
@@ -302,9 +318,9 @@ DEV void ninja_think(Nin& n) {                                           // ninj
             if (!jump_input || n.i[I_JUMP_DURATION] > MAX_JUMP_DURATION) { n.f[F_GRAVITY] = GRAVITY_FALL; n.i[I_STATE] = 4; return; }
         }
         if (in_jump_buffer || new_jump_check) {
-            if (n.i[I_WALLED] || in_wall_buffer) { ninja_wall_jump(n, in_wall_buffer); return; }
-            if (in_floor_buffer) { ninja_floor_jump(n, true); return; }
-            if (in_lp_buffer && new_jump_check) { ninja_lp_jump(n); return; }
+            if (n.i[I_WALLED] || in_wall_buffer) { ninja_wall_jump(n, in_wall_buffer, hor_input, ljb); return; }
+            if (in_floor_buffer) { ninja_floor_jump(n, true, hor_input, ljb); return; }
+            if (in_lp_buffer && new_jump_check) { ninja_lp_jump(n, c); return; }
         }
         if (!n.i[I_WALLED]) { if (state == 5) n.i[I_STATE] = 4; }
         else {
@@ -321,20 +337,30 @@ DEV void ninja_think(Nin& n) {                                           // ninj
     }
 }
 
+DEV void ninja_think(Nin& n, const Ctx& c, int hor_input, int jump_input) {
+    int ljb = 0;                                   // last_jump_was_buffered = False at the start of each frame
+    ninja_think_body(n, c, hor_input, jump_input, ljb);
+    GI(c, I_LAST_JUMP_BUFFERED) = ljb;
+}
+
 // Simulator.tick: nsim.py:221-292 (headless: enable_anim, log_data false).  Warp-synchronous: all 32
 // lanes call it together; `run` lanes advance their env by one frame.
 DEV void sim_tick(Nin& n, Ctx& c, WarpPool& wp, bool run, int hor_input, int jump_input) {
     bool alive = false, phys = false;
     double gx = 0, gy = 0;
+    PH_BEGIN
     if (run) {
         n.i[I_FRAME] += 1;
-        n.i[I_HOR_INPUT] = hor_input; n.i[I_JUMP_INPUT] = jump_input;
-        n.f[F_X_AT_ACTION] = n.f[F_XPOS]; n.f[F_Y_AT_ACTION] = n.f[F_YPOS];   // ninja.py:841-847
+        GI(c, I_HOR_INPUT) = hor_input; GI(c, I_JUMP_INPUT) = jump_input;
+        GF(c, F_X_AT_ACTION) = n.f[F_XPOS]; GF(c, F_Y_AT_ACTION) = n.f[F_YPOS];   // ninja.py:841-847
         // all move() then all think(): roaming entities in slot (= entity_dic) order, mines and boost
         // pads by neighbourhood (they are independent of every other entity's update)
         dyn_move_phase(c);
+        PH_MARK(0)
         static_update_phase(n, c);
+        PH_MARK(1)
         dyn_think_phase(n, c);
+        PH_MARK(2)
         int state = n.i[I_STATE];
         alive = (state != 9 && state != 6);      // dead: ragdoll is None when enable_anim=False (ninja.py:122-128)
         if (alive) {
@@ -342,6 +368,7 @@ DEV void sim_tick(Nin& n, Ctx& c, WarpPool& wp, bool run, int hor_input, int jum
             phys = ninja_pre_collision(n, c, gx, gy);
         }
     }
+    PH_MARK(3)
     // The four substeps (nsim.py:263-267).  A substep without entity pushes that leaves the position
     // bit-identical and performs no depenetration is a pure function of unchanged inputs, so the remaining
     // substeps would repeat it verbatim: they are skipped (typical: free flight, or resting after substep 2).
@@ -352,6 +379,9 @@ DEV void sim_tick(Nin& n, Ctx& c, WarpPool& wp, bool run, int hor_input, int jum
         bool idle = ninja_collide_vs_tiles(n, c, wp, sub);
         if (idle && !phys) sub = false;
     }
+    PH_MARK(4)
     ninja_post_collision(n, c, wp, alive);
-    if (run && n.i[I_STATE] != 9) ninja_think(n);
+    PH_MARK(7)
+    if (run && n.i[I_STATE] != 9) ninja_think(n, c, hor_input, jump_input);
+    PH_MARK(8)
 }

@@ -31,6 +31,7 @@ DEV void ctx_init(Ctx& c, const nppsim_state_t& st, int i) {
     c.db_count = h->db_count;
     c.N = st.n_envs; c.n_ent = h->n_ent; c.n_dyn = h->n_dyn; c.n_doors = h->n_doors;
     c.flag = st.ent_flag + i; c.dynf = st.dyn_f + i; c.dyni = st.dyn_i + i; c.envi = st.env_i + i;
+    c.gf = st.nin_f + i; c.gi = st.nin_i + i;
     c.order_mode = c.envi[(size_t)NPPSIM_ENV_ORDER * c.N];
     c.ecell_ids = reinterpret_cast<const uint16_t*>(blob + (c.order_mode ? h->off_ecell_ids_dic : h->off_ecell_ids));
     c.stamp = c.envi[(size_t)NPPSIM_ENV_STAMP * c.N];
@@ -126,6 +127,16 @@ __global__ void __launch_bounds__(128) reset_kernel(nppsim_state_t st, const uin
     envi[NPPSIM_ENV_HOT * N] = hot;
 }
 
+// Fields of the ninja record that live in registers for the launch; the rest is written through (GF/GI).
+__host__ __device__ constexpr bool hot_f(int f) {
+    return !(f == F_FRICTION || f == F_CNX || f == F_CNY || f == F_XLP || f == F_YLP || f == F_DEATH_X || f == F_DEATH_Y ||
+             f == F_DEATH_XS || f == F_DEATH_YS || f == F_X_AT_ACTION || f == F_Y_AT_ACTION);
+}
+__host__ __device__ constexpr bool hot_i(int f) {
+    return !(f == I_JUMP_USELESS || f == I_LAST_JUMP_BUFFERED || f == I_GOLD || f == I_DOORS_OPENED || f == I_TERMINAL_IMPACT ||
+             f == I_DEATH_CAUSE || f == I_HOR_INPUT || f == I_JUMP_INPUT);
+}
+
 // ---- step -----------------------------------------------------------------------------------------------
 // The register budget is left to ptxas (168/thread): capping it to fit more blocks per SM spills the
 // ninja record and costs more than the extra residency gains (measured: 128 regs -> -20 %).
@@ -143,13 +154,16 @@ __global__ void __launch_bounds__(STEP_BLOCK, STEP_BLOCKS_PER_SM) step_kernel(np
     int limit = n_ticks;
     if (tick_limit) limit = min(limit, tick_limit[i]);
     if (!valid) limit = 0;
+#ifdef NPP_PROFILE
+    long long _k0 = clock64();
+#endif
     Ctx c; ctx_init(c, st, i);
     Nin n;
     const double* nf = st.nin_f + i; const int32_t* ni = st.nin_i + i;
 #pragma unroll
-    for (int f = 0; f < NPPSIM_NF; f++) n.f[f] = nf[f * N];
+    for (int f = 0; f < NPPSIM_NF; f++) if (hot_f(f)) n.f[f] = nf[f * N];
 #pragma unroll
-    for (int f = 0; f < NPPSIM_NI; f++) n.i[f] = ni[f * N];
+    for (int f = 0; f < NPPSIM_NI; f++) if (hot_i(f)) n.i[f] = ni[f * N];
     int h = 0, j = 0;
     if (actions) {   // ACTION_TO_INPUTS: action_replayer.py:30-37
         int a = actions[i]; if (a > 5) a = 0;
@@ -173,13 +187,16 @@ __global__ void __launch_bounds__(STEP_BLOCK, STEP_BLOCKS_PER_SM) step_kernel(np
     if (done > 0) {
         double* of = st.nin_f + i; int32_t* oi = st.nin_i + i;
 #pragma unroll
-        for (int f = 0; f < NPPSIM_NF; f++) of[f * N] = n.f[f];
+        for (int f = 0; f < NPPSIM_NF; f++) if (hot_f(f)) of[f * N] = n.f[f];
 #pragma unroll
-        for (int f = 0; f < NPPSIM_NI; f++) oi[f * N] = n.i[f];
+        for (int f = 0; f < NPPSIM_NI; f++) if (hot_i(f)) oi[f * N] = n.i[f];
         ctx_flush(c);
         c.envi[(size_t)NPPSIM_ENV_TICKS * N] += done;
     }
     if (frames_executed) frames_executed[i] = done;
+#ifdef NPP_PROFILE
+    if ((threadIdx.x & 31) == 0) { unsigned long long d = (unsigned long long)(clock64() - _k0); atomicAdd(&g_phase_cycles[15], d); int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; if (w < (1 << 16)) g_warp_cycles[w] = d; }
+#endif
 }
 
 __global__ void sq_kernel(const double* in, double* out, int n) {
@@ -222,6 +239,21 @@ const char* nppsim_compile_error(void);
 const char* nppsim_last_error(void) { return g_err[0] ? g_err : nppsim_compile_error(); }
 int64_t nppsim_launch_count(void) { return (int64_t)g_launches.load(); }
 int nppsim_sq_mode(void) { return NPP_SQ_MODE; }
+#ifdef NPP_PROFILE
+int nppsim_debug_warp_cycles(unsigned long long* out, unsigned long long* phases, int n, int reset) {
+    cudaDeviceSynchronize();
+    if (out) cudaMemcpyFromSymbol(out, g_warp_cycles, sizeof(unsigned long long) * n);
+    if (phases) cudaMemcpyFromSymbol(phases, g_warp_phase, sizeof(unsigned long long) * n * 4);
+    if (reset) cudaMemset((void*)0, 0, 0);
+    return 0;
+}
+int nppsim_debug_phase_cycles(unsigned long long* out16, int reset) {
+    cudaDeviceSynchronize();
+    if (out16) cudaMemcpyFromSymbol(out16, g_phase_cycles, sizeof(unsigned long long) * 16);
+    if (reset) { unsigned long long z[16] = {0}; cudaMemcpyToSymbol(g_phase_cycles, z, sizeof(z)); }
+    return 0;
+}
+#endif
 
 int nppsim_debug_sq(const double* in, double* out, int32_t n, void* stream) {
     g_err[0] = 0;

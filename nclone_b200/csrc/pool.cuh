@@ -14,6 +14,7 @@
 
 #define POOL_CAP 256                 // 32 lanes x at most 8 segments per cell per round
 #define FULL_MASK 0xffffffffu
+#define POOL_LCAP 24                 // larger gathers fall back to the out-of-line exact walk
 
 struct WarpPool {
     double par[5][32];               // per-owner query parameters
@@ -21,6 +22,7 @@ struct WarpPool {
     double ra[POOL_CAP], rb[POOL_CAP];   // per-item closest point
     uint32_t seg[POOL_CAP];
     uint8_t own[POOL_CAP], aux[POOL_CAP];
+    uint32_t lseg[32][POOL_LCAP];   // per-lane copy of the segments gathered for the current substep (ninja.py:282-285)
 };
 
 // ---- per-lane iterator over the cells of a query box (SpatialSegmentIndex.query_region order) ----------
@@ -220,39 +222,56 @@ __device__ __noinline__ int closest_point_exact(const uint32_t* cell_hdr, const 
 // Items carry the cheap adjusted squared distance; the owner's strict-< scan accepts a comparison only
 // when it cannot flip under 1-ulp changes of the squares (or both items are the same point and side);
 // otherwise it re-runs the literal per-thread version with exact SQ().
+// One candidate of get_single_closest_point's strict-< scan (physics.py:155-179).  d2 was computed
+// with cheap squares; `ix` says it may differ from the reference's value by an ulp.  Between two exact
+// values the reference's own comparison is used; otherwise the comparison is accepted only outside a guard band.
+DEV void closest_fold(double d2, double a, double b, int r, bool ix, double& best, double& ba, double& bb, int& result, bool& bix, bool& uncertain) {
+    if (!ix && !bix) { if (d2 < best) { best = d2; ba = a; bb = b; result = r; } return; }
+    const double G = 1e-10;                                  // >> 3 ulp of any d2 here (<= 1000)
+    if (d2 < best - G) { best = d2; ba = a; bb = b; result = r; bix = ix; }
+    else if (d2 > best + G) { }
+    else if (a == ba && b == bb && r == result) { }          // identical inputs: exact values tie, first wins
+    else uncertain = true;
+}
+// closest point + adjusted squared distance of one segment; false when the AABB test rejects it
+DEV bool closest_item(uint32_t s, double x, double y, double& d2, double& a, double& b, int& r, bool& ix) {
+    double sx0, sy0, sx1, sy1;
+    seg_bounds(s, sx0, sy0, sx1, sy1);
+    if (sx1 < x - NINJA_RADIUS || sx0 > x + NINJA_RADIUS || sy1 < y - NINJA_RADIUS || sy0 > y + NINJA_RADIUS) return false;
+    bool back;
+    seg_closest_point(s, x, y, back, a, b);
+    ix = false;
+    d2 = sq_flag(x - a, ix) + sq_flag(y - b, ix);
+    if (!back) d2 -= 0.1;
+    r = back ? -1 : 1;
+    return true;
+}
+
+// First iteration of the depenetration loop: pooled over the warp.  Besides the result it leaves the
+// owner's gathered segment list (reference order) in wp.lseg[lane][0..nseg) for the later iterations;
+// nseg = -1 when the list does not fit.
 DEV int pooled_closest_point(WarpPool& wp, const Ctx& c, bool active, double gx1, double gy1, double gx2, double gy2,
-                             double xpos, double ypos, double& pa, double& pb) {
+                             double xpos, double ypos, double& pa, double& pb, int& nseg) {
     const int lane = threadIdx.x & 31;
     wp.par[0][lane] = xpos; wp.par[1][lane] = ypos;
     __syncwarp();
     double best = __longlong_as_double(0x7ff0000000000000LL), ba = 0, bb = 0;
     int result = 0;
-    bool uncertain = false;
+    bool uncertain = false, bix = false;
+    nseg = 0;
     pooled_query(wp, c, active, gx1, gy1, gx2, gy2,
         [&](int j, uint32_t s, int o) {
-            const double x = wp.par[0][o], y = wp.par[1][o];
-            double sx0, sy0, sx1, sy1;
-            seg_bounds(s, sx0, sy0, sx1, sy1);
-            if (sx1 < x - NINJA_RADIUS || sx0 > x + NINJA_RADIUS || sy1 < y - NINJA_RADIUS || sy0 > y + NINJA_RADIUS) { wp.aux[j] = 2; return; }
-            bool back; double a, b;
-            seg_closest_point(s, x, y, back, a, b);
-            double ex = x - a, ey = y - b;
-            double d2 = ex * ex + ey * ey;
-            if (!back) d2 -= 0.1;
-            wp.res[j] = d2; wp.ra[j] = a; wp.rb[j] = b; wp.aux[j] = back ? 1 : 0;
+            double d2, a, b; int r; bool ix;
+            if (!closest_item(s, wp.par[0][o], wp.par[1][o], d2, a, b, r, ix)) { wp.aux[j] = 2; return; }
+            wp.res[j] = d2; wp.ra[j] = a; wp.rb[j] = b; wp.aux[j] = (uint8_t)((r < 0 ? 1 : 0) | (ix ? 4 : 0));
         },
         [&](int off, int cnt) {
             #pragma unroll 1
             for (int k = 0; k < cnt; k++) {
+                if (nseg >= 0) { if (nseg < POOL_LCAP) wp.lseg[lane][nseg++] = wp.seg[off + k]; else nseg = -1; }
                 int ax = wp.aux[off + k];
                 if (ax == 2) continue;                                   // AABB-rejected
-                double d2 = wp.res[off + k], a = wp.ra[off + k], b = wp.rb[off + k];
-                int r = ax ? -1 : 1;
-                const double G = 1e-10;                                  // >> 3 ulp of any d2 here (<= 800)
-                if (d2 < best - G) { best = d2; ba = a; bb = b; result = r; }
-                else if (d2 > best + G) { }
-                else if (a == ba && b == bb && r == result) { }          // identical inputs: exact values tie, first wins
-                else uncertain = true;
+                closest_fold(wp.res[off + k], wp.ra[off + k], wp.rb[off + k], (ax & 1) ? -1 : 1, (ax & 4) != 0, best, ba, bb, result, bix, uncertain);
             }
             return true;
         });
@@ -260,30 +279,48 @@ DEV int pooled_closest_point(WarpPool& wp, const Ctx& c, bool active, double gx1
     pa = ba; pb = bb;
     return result;
 }
+// Later iterations: the owner walks its cached list itself (few lanes are still iterating by then, and a
+// pathological corner can take all 32 iterations -- a pooled pass per iteration made such warps 8x slower
+// than the median, profiles/r01_c).
+DEV int cached_closest_point(const WarpPool& wp, const Ctx& c, int nseg, double gx1, double gy1, double gx2, double gy2,
+                             double xpos, double ypos, double& pa, double& pb) {
+    if (nseg < 0) return closest_point_exact(c.cell_hdr, c.segs, gx1, gy1, gx2, gy2, xpos, ypos, pa, pb);
+    const int lane = threadIdx.x & 31;
+    double best = __longlong_as_double(0x7ff0000000000000LL), ba = 0, bb = 0;
+    int result = 0;
+    bool uncertain = false, bix = false;
+    #pragma unroll 1
+    for (int k = 0; k < nseg; k++) {
+        double d2, a, b; int r; bool ix;
+        if (!closest_item(wp.lseg[lane][k], xpos, ypos, d2, a, b, r, ix)) continue;
+        closest_fold(d2, a, b, r, ix, best, ba, bb, result, bix, uncertain);
+    }
+    if (uncertain) return closest_point_exact(c.cell_hdr, c.segs, gx1, gy1, gx2, gy2, xpos, ypos, pa, pb);
+    pa = ba; pb = bb;
+    return result;
+}
 
 // ---- pooled wall test of post_collision (ninja.py:422-441) ----------------------------------------------------
-// Each qualifying segment adds dx/dist = +-(1 - eps), eps < 1e-12, and only the sign of the total is
-// used (ninja.py:447-449).  Returns the counts of positive / negative terms; `uncertain` when a
-// `dist <= rad` test is within the guard band.
-DEV void pooled_wall_test(WarpPool& wp, const Ctx& c, bool active, double xpos, double ypos, int& npos, int& nneg, bool& uncertain) {
+// Items evaluate the literal reference expression on cheap squares; the owner adds the terms to
+// wall_normal in list order.  `uncertain` when a term's squares were flagged inexact (table path needed).
+DEV void pooled_wall_test(WarpPool& wp, const Ctx& c, bool active, double xpos, double ypos, double& wall_normal, bool& uncertain) {
     const int lane = threadIdx.x & 31;
     const double rad = NINJA_RADIUS + 0.1;
     wp.par[0][lane] = xpos; wp.par[1][lane] = ypos;
     __syncwarp();
-    npos = 0; nneg = 0; uncertain = false;
+    uncertain = false;
     pooled_query(wp, c, active, xpos - rad, ypos - rad, xpos + rad, ypos + rad,
         [&](int j, uint32_t s, int o) {
             const double x = wp.par[0][o], y = wp.par[1][o];
             bool back; double a, b;
             seg_closest_point(s, x, y, back, a, b);
             double dx = x - a, dy = y - b;
-            int code = 0;                                                // 0 none, 1 positive, 2 negative, 3 uncertain
+            int code = 0;                                                // 0 no term, 1 term in res[j], 3 needs the exact path
             if (fabs(dy) < 0.00001) {
-                double dist = sqrt(dx * dx + dy * dy);
-                if (dist > 0) {                                          // dist == 0 iff dx == dy == 0, exact either way
-                    if (dist <= rad - 1e-9) code = (dx > 1.0) ? 1 : ((dx < -1.0) ? 2 : 3);   // |dx| > 1: the term is +-(1 - 1e-10)
-                    else if (dist < rad + 1e-9) code = 3;
-                }
+                bool ix = false;
+                double dist = sqrt(sq_flag(dx, ix) + sq_flag(dy, ix));
+                if (ix) code = 3;
+                else if (0 < dist && dist <= rad) { wp.res[j] = dx / dist; code = 1; }
             }
             wp.aux[j] = (uint8_t)code;
         },
@@ -291,7 +328,7 @@ DEV void pooled_wall_test(WarpPool& wp, const Ctx& c, bool active, double xpos, 
             #pragma unroll 1
             for (int k = 0; k < cnt; k++) {
                 int code = wp.aux[off + k];
-                if (code == 1) npos++; else if (code == 2) nneg++; else if (code == 3) uncertain = true;
+                if (code == 1) wall_normal += wp.res[off + k]; else if (code == 3) uncertain = true;
             }
             return true;
         });

@@ -124,4 +124,19 @@ POW2_FN double pow2_exact(double x) {
 
 #ifdef __CUDACC__
 DEV double SQ(double x) { return pow2_exact(x); }
+// x*x, and `inexact` set when that may differ from pow(x, 2.0) (x^2 within 1/64 ulp of a rounding
+// midpoint, ~3 % of inputs).  With the flag clear the product IS the reference's value, so callers can
+// run the literal reference expression on cheap squares and only redo flagged cases on the table path.
+DEV double sq_flag(double x, bool& inexact) {
+    const double hi = x * x;
+    const double lo = __fma_rn(x, x, -hi);
+    const int hw = __double2hiint(hi);
+    const int eb = hw & 0x7ff00000;
+    if ((unsigned)(eb - 0x33700000) <= (unsigned)(0x4c800000 - 0x33700000)) {
+        const double thr = __hiloint2double(eb - 0x03500000, 0) * 0.96875;
+        const bool fast = fabs(lo) < thr && ((hw & 0x000fffff) | __double2loint(hi)) != 0;
+        if (!fast && !(hi == 1.0 && lo == 0)) inexact = true;
+    }
+    return hi;
+}
 #endif
