@@ -5,14 +5,10 @@
 
 // NPP_PROFILE: per-warp cycle counters per phase (debug builds only; tools/phase_profile.py)
 #ifdef NPP_PROFILE
-__device__ unsigned long long g_phase_cycles[16];
 __device__ unsigned long long g_warp_cycles[1 << 16];      // per warp: kernel duration of the last launch
 __device__ unsigned long long g_warp_phase[1 << 16][4];   // per warp: cycles in entities / sweep / closest / post of the last launch
 #define PH_BEGIN long long _ph_t = clock64();
 #define PH_MARK(k) { long long _t2 = clock64(); if ((threadIdx.x & 31) == (__ffs(__activemask()) - 1)) { atomicAdd(&g_phase_cycles[k], (unsigned long long)(_t2 - _ph_t)); int _w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; int _b = (k) <= 3 ? 0 : ((k) == 5 ? 1 : ((k) == 6 ? 2 : (((k) == 9 || (k) == 10) ? 3 : -1))); if (_b >= 0 && _w < (1 << 16)) g_warp_phase[_w][_b] += (unsigned long long)(_t2 - _ph_t); } _ph_t = _t2; }
-#else
-#define PH_BEGIN
-#define PH_MARK(k)
 #endif
 
 DEV void ninja_integrate(Nin& n) {                                       // ninja.py:198-206
@@ -74,17 +70,9 @@ DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
     // segments are gathered once, around the post-sweep position (ninja.py:282-285)
     const double gx1 = xpos - NINJA_RADIUS, gy1 = ypos - NINJA_RADIUS, gx2 = xpos + NINJA_RADIUS, gy2 = ypos + NINJA_RADIUS;
     double xspeed = n.f[F_XSPEED], yspeed = n.f[F_YSPEED];
-    // iteration 0 is pooled over the warp (and caches each lane's gathered list); iterations 1..31 run
-    // per lane on the cached list
-    double a0 = 0, b0 = 0; int nseg = 0;
-    int result0 = pooled_closest_point(wp, c, alive, gx1, gy1, gx2, gy2, xpos, ypos, a0, b0, nseg);
-    bool need = alive;
-    #pragma unroll 1
-    for (int it = 0; it < 32 && need; it++) {
-        double a = a0, b = b0;
-        int result = result0;
-        if (it > 0) result = cached_closest_point(wp, c, nseg, gx1, gy1, gx2, gy2, xpos, ypos, a, b);
-        if (result == 0) { need = false; continue; }
+    // One depenetration push (ninja.py:303-379) from the closest point (a, b); false = the loop ends here.
+    auto depen = [&](int result, double a, double b) -> bool {
+        if (result == 0) return false;
         dx = xpos - a; dy = ypos - b;
         if (fabs(dx) <= 0.0000001) {                  // ninja.py:312-318 band-aid
             dx = 0;
@@ -92,10 +80,10 @@ DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
             if (xpos == 49.153536108584795) dx = 0x1p-47;
         }
         double dist_sq = dx * dx + dy * dy;
-        if (dist_sq < 1e-16) { need = false; continue; }
+        if (dist_sq < 1e-16) return false;
         double dist = sqrt(dist_sq);
         double depen_len = NINJA_RADIUS - dist * result;
-        if (depen_len < 0.0000001) { need = false; continue; }
+        if (depen_len < 0.0000001) return false;
         double inv_dist = 1.0 / dist;
         double norm_dx = dx * inv_dist, norm_dy = dy * inv_dist;
         double depen_x = norm_dx * depen_len, depen_y = norm_dy * depen_len;
@@ -112,6 +100,50 @@ DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
         }
         if (dy >= -0.0001) { n.i[I_CEILING_COUNT] += 1; n.f[F_CEIL_NX] += norm_dx; n.f[F_CEIL_NY] += norm_dy; }
         else { n.i[I_FLOOR_COUNT] += 1; n.f[F_FLOOR_NX] += norm_dx; n.f[F_FLOOR_NY] += norm_dy; }
+        return true;
+    };
+    // Iteration 0 is pooled over the warp (and caches each lane's gathered list); iteration 1 runs per
+    // lane on the cached list (5 % of substeps need it, i.e. most warps); iterations 2..31 are rare per
+    // lane (0.2 %) but long (a wedged ninja takes all 32), so the warp serves one such lane at a time
+    // with its cached segments spread over the lanes.
+    double a0 = 0, b0 = 0; int nseg = 0;
+    int result0 = pooled_closest_point(wp, c, alive, gx1, gy1, gx2, gy2, xpos, ypos, a0, b0, nseg);
+    bool need = alive && depen(result0, a0, b0);
+    if (need) {
+        double a = 0, b = 0;
+        int result = cached_closest_point(wp, c, nseg, gx1, gy1, gx2, gy2, xpos, ypos, a, b);
+        need = depen(result, a, b);
+    }
+    unsigned todo;
+    #pragma unroll 1
+    while ((todo = __ballot_sync(FULL_MASK, need)) != 0) {
+        const int lane = threadIdx.x & 31;
+        const int o = __ffs(todo) - 1;
+        const int ns = __shfl_sync(FULL_MASK, nseg, o);
+        const SegC g = seg_decode(lane < ns ? wp.lseg[o][lane] : 0u);
+        #pragma unroll 1
+        for (int it = 2; it < 32; it++) {
+            double a = 0, b = 0; int result = 0;
+#ifdef NPP_PROFILE
+            long long _c0 = clock64();
+#endif
+            if (ns < 0) {
+                if (lane == o) result = closest_point_exact(c.cell_hdr, c.segs, gx1, gy1, gx2, gy2, xpos, ypos, a, b);
+            } else {
+                result = warp_closest_point(wp, c, o, ns, g, gx1, gy1, gx2, gy2, xpos, ypos, a, b);
+            }
+#ifdef NPP_PROFILE
+            long long _c1 = clock64();
+#endif
+            bool cont = false;
+            if (lane == o) cont = depen(result, a, b);
+            const bool go = __shfl_sync(FULL_MASK, (int)cont, o);
+#ifdef NPP_PROFILE
+            if (lane == o) { long long _c2 = clock64(); atomicAdd(&g_phase_cycles[13], (unsigned long long)(_c1 - _c0)); atomicAdd(&g_phase_cycles[14], (unsigned long long)(_c2 - _c1)); }
+#endif
+            if (!go) break;
+        }
+        if (lane == o) need = false;
     }
     PH_MARK(6)
     if (alive) { n.f[F_XPOS] = xpos; n.f[F_YPOS] = ypos; n.f[F_XSPEED] = xspeed; n.f[F_YSPEED] = yspeed; }

@@ -140,8 +140,12 @@ __host__ __device__ constexpr bool hot_i(int f) {
 // ---- step -----------------------------------------------------------------------------------------------
 // The register budget is left to ptxas (168/thread): capping it to fit more blocks per SM spills the
 // ninja record and costs more than the extra residency gains (measured: 128 regs -> -20 %).
+#ifndef STEP_BLOCK
 #define STEP_BLOCK 128
+#endif
+#ifndef STEP_BLOCKS_PER_SM
 #define STEP_BLOCKS_PER_SM 1
+#endif
 __global__ void __launch_bounds__(STEP_BLOCK, STEP_BLOCKS_PER_SM) step_kernel(nppsim_state_t st, const int8_t* __restrict__ hor, const int8_t* __restrict__ jump,
                                                     const uint8_t* __restrict__ actions, int input_ticks, int n_ticks,
                                                     const int32_t* __restrict__ tick_limit, int stop_on_terminal, int32_t* frames_executed) {

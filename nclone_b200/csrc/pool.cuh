@@ -12,6 +12,15 @@
 #pragma once
 #include "geom.cuh"
 
+#ifdef NPP_PROFILE
+__device__ unsigned long long g_phase_cycles[16];      // [0..10] cycles per phase, [11..14] event counters, [15] kernel cycles
+#define PH_COUNT(k) atomicAdd(&g_phase_cycles[k], 1ULL)
+#else
+#define PH_BEGIN
+#define PH_MARK(k)
+#define PH_COUNT(k)
+#endif
+
 #define POOL_CAP 256                 // 32 lanes x at most 8 segments per cell per round
 #define FULL_MASK 0xffffffffu
 #define POOL_LCAP 24                 // larger gathers fall back to the out-of-line exact walk
@@ -45,8 +54,8 @@ DEV int cell_iter_next(CellIter& it, const Ctx& c, int& cell) {
         uint32_t hdr = __ldg(c.cell_hdr + ci);
         int cnt = hdr & 15;
         if (!cnt) continue;
-        double bx0 = 12.0 * (double)(int)((hdr >> 4) & 127), by0 = 12.0 * (double)(int)((hdr >> 11) & 63);
-        double bx1 = 12.0 * (double)(int)((hdr >> 17) & 127), by1 = 12.0 * (double)(int)((hdr >> 24) & 63);
+        double bx0 = u12((hdr >> 4) & 127), by0 = u12((hdr >> 11) & 63);
+        double bx1 = u12((hdr >> 17) & 127), by1 = u12((hdr >> 24) & 63);
         if (it.max_x < bx0 || it.min_x > bx1 || it.max_y < by0 || it.min_y > by1) continue;
         cell = ci;
         return cnt;
@@ -122,11 +131,17 @@ DEV double toi_circle_guarded(double xpos, double ypos, double vx, double vy, do
     }
     return toi_circle_exact(dx, dy, dot_prod, vx, vy, rr);
 }
-// physics.py:264-285; the segment's end points are integers, so wx**2 + wy**2 is exact as a product
-DEV double toi_lineseg_int(double xpos, double ypos, double dx, double dy, double a1, double b1, double a2, double b2, double radius) {
-    double wx = a2 - a1, wy = b2 - b1;
-    double seg_len = sqrt(wx * wx + wy * wy);
-    double nx = wx / seg_len, ny = wy / seg_len;
+// physics.py:264-285 for a tile segment.  Its direction (wx, wy) is one of (+-12, 0), (0, +-12), (+-24, +-24),
+// (+-24, +-12), (+-12, +-24), so seg_len = sqrt(wx**2 + wy**2) and the unit vector wx / seg_len are table
+// values: seg_len in {12, sqrt(720), sqrt(1152)} and RN(wx / seg_len) = (wx / 12) * RN(12 / seg_len), the
+// factor wx / 12 in {0, +-1, +-2} being an exact scaling.  No sqrt, no division.
+DEV double toi_lineseg_int(uint32_t s, double xpos, double ypos, double dx, double dy, double radius) {
+    const int x1 = s & 127, y1 = (s >> 7) & 63, wxi = (int)((s >> 13) & 127) - x1, wyi = (int)((s >> 20) & 63) - y1;
+    const int l2 = wxi * wxi + wyi * wyi;                                        // 1, 5 or 8 (units of 144)
+    const double seg_len = l2 == 1 ? 12.0 : (l2 == 5 ? 26.832815729997478 : 33.941125496954278);   // sqrt(144), sqrt(720), sqrt(1152)
+    const double k = l2 == 1 ? 1.0 : (l2 == 5 ? 12.0 / 26.832815729997478 : 12.0 / 33.941125496954278);
+    const double nx = s2d(wxi) * k, ny = s2d(wyi) * k;
+    const double a1 = u12(x1), b1 = u12(y1);
     double normal_proj = (xpos - a1) * ny - (ypos - b1) * nx;
     double hor_proj = (xpos - a1) * nx + (ypos - b1) * ny;
     if (fabs(normal_proj) >= radius) {
@@ -169,7 +184,7 @@ DEV double seg_toi_guarded(uint32_t s, double xpos, double ypos, double dx, doub
         SegLin l = dec_lin(s);
         double t1 = toi_circle_guarded(xpos, ypos, dx, dy, vel_a, l.x1, l.y1, rr);
         double t2 = toi_circle_guarded(xpos, ypos, dx, dy, vel_a, l.x2, l.y2, rr);
-        double t3 = toi_lineseg_int(xpos, ypos, dx, dy, l.x1, l.y1, l.x2, l.y2, radius);
+        double t3 = toi_lineseg_int(s, xpos, ypos, dx, dy, radius);
         return min3(t1, t2, t3);
     } else {
         SegArc a = dec_arc(s);
@@ -233,18 +248,59 @@ DEV void closest_fold(double d2, double a, double b, int r, bool ix, double& bes
     else if (a == ba && b == bb && r == result) { }          // identical inputs: exact values tie, first wins
     else uncertain = true;
 }
-// closest point + adjusted squared distance of one segment; false when the AABB test rejects it
-DEV bool closest_item(uint32_t s, double x, double y, double& d2, double& a, double& b, int& r, bool& ix) {
-    double sx0, sy0, sx1, sy1;
-    seg_bounds(s, sx0, sy0, sx1, sy1);
-    if (sx1 < x - NINJA_RADIUS || sx0 > x + NINJA_RADIUS || sy1 < y - NINJA_RADIUS || sy0 > y + NINJA_RADIUS) return false;
+// A tile segment decoded for repeated closest-point queries (the depenetration loop re-tests the same
+// segments up to 32 times): AABB as get_bounds() (entities.py:36-41,121-125) + the closest-point constants.
+struct SegC {
+    double bx0, by0, bx1, by1;
+    double x1, y1, px, py, lensq;        // linear: first end, direction, squared length | arc: centre, (hor, ver), convex ? 1 : 0
+    bool arc;
+};
+DEV SegC seg_decode(uint32_t s) {
+    SegC g;
+    g.arc = (s & NPP_SEG_ARC) != 0;
+    const int ax = s & 127, ay = (s >> 7) & 63;
+    int bx, by;
+    if (g.arc) {
+        const int hn = (s >> 13) & 1, vn = (s >> 14) & 1;
+        bx = ax + (hn ? -2 : 2); by = ay + (vn ? -2 : 2);
+        g.px = hn ? -1.0 : 1.0; g.py = vn ? -1.0 : 1.0; g.lensq = ((s >> 15) & 1) ? 1.0 : 0.0;
+    } else {
+        bx = (s >> 13) & 127; by = (s >> 20) & 63;
+        const int wx = bx - ax, wy = by - ay;
+        g.px = s2d(12 * wx); g.py = s2d(12 * wy); g.lensq = s2d(144 * (wx * wx + wy * wy));
+    }
+    g.x1 = u12(ax); g.y1 = u12(ay);
+    g.bx0 = u12(min(ax, bx)); g.bx1 = u12(max(ax, bx)); g.by0 = u12(min(ay, by)); g.by1 = u12(max(ay, by));
+    return g;
+}
+// closest point + adjusted squared distance (physics.py:155-179); false when the AABB test rejects the segment
+DEV bool closest_eval(const SegC& g, double x, double y, double& d2, double& a, double& b, int& r, bool& ix) {
+    if (g.bx1 < x - NINJA_RADIUS || g.bx0 > x + NINJA_RADIUS || g.by1 < y - NINJA_RADIUS || g.by0 > y + NINJA_RADIUS) return false;
+    const double dx = x - g.x1, dy = y - g.y1;
     bool back;
-    seg_closest_point(s, x, y, back, a, b);
+    if (!g.arc) {                                                            // entities.py:43-59
+        double u = div_seglen(dx * g.px + dy * g.py, g.lensq);
+        if (0 > u) u = 0;
+        if (1 < u) u = 1;
+        a = g.x1 + u * g.px; b = g.y1 + u * g.py;
+        back = (dy * g.px - dx * g.py < 0);
+    } else {                                                                 // entities.py:127-157
+        back = false;
+        if (dx * g.px > 0 && dy * g.py > 0) {
+            double dist = sqrt(SQ(dx) + SQ(dy));
+            a = g.x1 + 24.0 * dx / dist; b = g.y1 + 24.0 * dy / dist;
+            back = (g.lensq != 0) ? (dist < 24.0) : (dist > 24.0);
+        } else if (dx * g.px > dy * g.py) { a = g.x1 + 24.0 * g.px; b = g.y1; }
+        else { a = g.x1; b = g.y1 + 24.0 * g.py; }
+    }
     ix = false;
     d2 = sq_flag(x - a, ix) + sq_flag(y - b, ix);
     if (!back) d2 -= 0.1;
     r = back ? -1 : 1;
     return true;
+}
+DEV bool closest_item(uint32_t s, double x, double y, double& d2, double& a, double& b, int& r, bool& ix) {
+    return closest_eval(seg_decode(s), x, y, d2, a, b, r, ix);
 }
 
 // First iteration of the depenetration loop: pooled over the warp.  Besides the result it leaves the
@@ -297,6 +353,61 @@ DEV int cached_closest_point(const WarpPool& wp, const Ctx& c, int nseg, double 
     }
     if (uncertain) return closest_point_exact(c.cell_hdr, c.segs, gx1, gy1, gx2, gy2, xpos, ypos, pa, pb);
     pa = ba; pb = bb;
+    return result;
+}
+
+// Iterations 2..31 of one owner lane `o`, served by the whole warp: lane k evaluates the owner's k-th
+// cached segment (decoded once per owner by the caller: `g`).  With exact squares everywhere the reference's strict-< scan picks the first minimum,
+// which is a warp min + ballot; when some square is flagged inexact the owner folds the items in list
+// order with the guard band (closest_fold) as in the per-lane version.  All 32 lanes call this; only
+// lane o's (result, pa, pb) are meaningful.
+// min over the warp of non-NaN doubles: order-preserving 64-bit keys, reduced 32 bits at a time with redux.sync
+DEV double warp_min_f64(double v) {
+    long long b = __double_as_longlong(v);
+    unsigned long long key = (unsigned long long)(b ^ ((b >> 63) | (long long)0x8000000000000000ULL));   // monotone in v
+    const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+    const unsigned mhi = __reduce_min_sync(FULL_MASK, hi);
+    const unsigned mlo = __reduce_min_sync(FULL_MASK, hi == mhi ? lo : 0xffffffffu);
+    key = ((unsigned long long)mhi << 32) | mlo;
+    b = (long long)key;
+    b = (b < 0) ? (b ^ (long long)0x8000000000000000ULL) : ~b;
+    return __longlong_as_double(b);
+}
+DEV int warp_closest_point(WarpPool& wp, const Ctx& c, int o, int ns, const SegC& g, double gx1, double gy1, double gx2, double gy2,
+                           double xpos, double ypos, double& pa, double& pb) {
+    const int lane = threadIdx.x & 31;
+    const double x = __shfl_sync(FULL_MASK, xpos, o), y = __shfl_sync(FULL_MASK, ypos, o);
+    const double inf = __longlong_as_double(0x7ff0000000000000LL);
+    double d2 = inf, a = 0, b = 0; int r = 0; bool ix = false, ok = false;
+    if (lane < ns) ok = closest_eval(g, x, y, d2, a, b, r, ix);
+    if (!ok) d2 = inf;
+    int result = 0;
+    if (lane == o) PH_COUNT(11);
+    if (__ballot_sync(FULL_MASK, ok && ix) == 0) {
+        const double mn = warp_min_f64(d2);
+        const unsigned eq = __ballot_sync(FULL_MASK, ok && d2 == mn);
+        if (eq) {
+            const int w = __ffs(eq) - 1;
+            pa = __shfl_sync(FULL_MASK, a, w); pb = __shfl_sync(FULL_MASK, b, w); result = __shfl_sync(FULL_MASK, r, w);
+        }
+        return result;
+    }
+    if (lane == o) PH_COUNT(12);
+    wp.res[lane] = d2; wp.ra[lane] = a; wp.rb[lane] = b; wp.aux[lane] = (uint8_t)(!ok ? 2 : ((r < 0 ? 1 : 0) | (ix ? 4 : 0)));
+    __syncwarp();
+    if (lane == o) {
+        double best = inf, ba = 0, bb = 0;
+        bool uncertain = false, bix = false;
+        #pragma unroll 1
+        for (int k = 0; k < ns; k++) {
+            int ax = wp.aux[k];
+            if (ax == 2) continue;
+            closest_fold(wp.res[k], wp.ra[k], wp.rb[k], (ax & 1) ? -1 : 1, (ax & 4) != 0, best, ba, bb, result, bix, uncertain);
+        }
+        if (uncertain) { result = closest_point_exact(c.cell_hdr, c.segs, gx1, gy1, gx2, gy2, xpos, ypos, pa, pb); }
+        else { pa = ba; pb = bb; }
+    }
+    __syncwarp();
     return result;
 }
 

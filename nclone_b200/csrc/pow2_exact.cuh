@@ -94,16 +94,17 @@ POW2_SLOW double pow2_table_path(double x) {
 
 // Python `x ** 2` for a float x.
 #ifdef __CUDACC__
+// Fast-path test in one FMA: RN(hi + lo * 32/31) == hi  <=>  |lo| < 31/64 ulp(hi) (up to ties, which only
+// widen the table path's share).  Just below a power of two the spacing halves, so the test fails there
+// for lo < 0 at |lo| >= 31/128 ulp -- conservative, the table path is exact anyway; lo == 0 (an exactly
+// representable square, incl. x = +-2^k and 0) always passes.  inf/nan give lo = nan and fail the test.
+POW2_FN bool pow2_fast_ok(double hi, double lo) { return __fma_rn(lo, 0x1.0842108421084p+0, hi) == hi; }
 POW2_FN double pow2_exact(double x) {
     const double hi = x * x;
     const double lo = __fma_rn(x, x, -hi);                     // exact: x*x == hi + lo
-    const int hw = __double2hiint(hi);
-    const int eb = hw & 0x7ff00000;
-    // outside [2^-200, 2^200] (incl. 0, inf, nan) the table path's preconditions are not checked: x*x
-    if ((unsigned)(eb - 0x33700000) > (unsigned)(0x4c800000 - 0x33700000)) return hi;
-    const double thr = __hiloint2double(eb - 0x03500000, 0) * 0.96875;      // (1 - 2/64) * ulp/2, exact
-    if (fabs(lo) < thr && ((hw & 0x000fffff) | __double2loint(hi)) != 0) return hi;
-    if (hi == 1.0 && lo == 0) return hi;                       // |x| == 1: log is exactly 0 (special-cased in glibc)
+    if (pow2_fast_ok(hi, lo)) return hi;
+    // outside [2^-200, 2^200] (incl. inf, nan, squares that underflow) the table path's preconditions do not hold: x*x
+    if ((unsigned)((__double2hiint(hi) & 0x7ff00000) - 0x33700000) > (unsigned)(0x4c800000 - 0x33700000)) return hi;
     return pow2_table_path(x);
 }
 #else
@@ -116,8 +117,7 @@ POW2_FN double pow2_exact(double x) {
     const double half_ulp = POW2_AS_F64(eb - 0x0350000000000000ULL);          // 2^(e-53)
     const double thr = half_ulp * 0.96875;
     const double alo = lo < 0 ? -lo : lo;
-    if (alo < thr && (hb & 0x000fffffffffffffULL) != 0) return hi;
-    if (hi == 1.0 && lo == 0) return hi;
+    if (alo < thr && ((hb & 0x000fffffffffffffULL) != 0 || lo == 0)) return hi;
     return pow2_table_path(x);
 }
 #endif
@@ -130,13 +130,7 @@ DEV double SQ(double x) { return pow2_exact(x); }
 DEV double sq_flag(double x, bool& inexact) {
     const double hi = x * x;
     const double lo = __fma_rn(x, x, -hi);
-    const int hw = __double2hiint(hi);
-    const int eb = hw & 0x7ff00000;
-    if ((unsigned)(eb - 0x33700000) <= (unsigned)(0x4c800000 - 0x33700000)) {
-        const double thr = __hiloint2double(eb - 0x03500000, 0) * 0.96875;
-        const bool fast = fabs(lo) < thr && ((hw & 0x000fffff) | __double2loint(hi)) != 0;
-        if (!fast && !(hi == 1.0 && lo == 0)) inexact = true;
-    }
+    if (!pow2_fast_ok(hi, lo) && (unsigned)((__double2hiint(hi) & 0x7ff00000) - 0x33700000) <= (unsigned)(0x4c800000 - 0x33700000)) inexact = true;
     return hi;
 }
 #endif

@@ -507,6 +507,12 @@ static void ninja_collide_vs_objects(OSim *S) {      /* ninja.py:224-267 */
         else { n->floor_count += 1; n->floor_normal_x += depen_x; n->floor_normal_y += depen_y; }
     }
 }
+#ifdef OSIM_STATS   /* tools/iter_stats.py only: depenetration-loop statistics (not thread safe) */
+long osim_stat_iters[34], osim_stat_nseg[64], osim_stat_calls;
+#define STAT_ITERS(k, ns) do { osim_stat_iters[(k)]++; osim_stat_nseg[(ns) < 63 ? (ns) : 63]++; osim_stat_calls += (k); } while (0)
+#else
+#define STAT_ITERS(k, ns) do { } while (0)
+#endif
 static void ninja_collide_vs_tiles(OSim *S) {        /* ninja.py:269-379 */
     Ninja *n = &S->ninja;
     double dx = n->xpos - n->xpos_old, dy = n->ypos - n->ypos_old;
@@ -519,9 +525,11 @@ static void ninja_collide_vs_tiles(OSim *S) {        /* ninja.py:269-379 */
     /* private copy: nothing else queries inside the loop, but keep the reference's "gather once" shape */
     for (int k = 0; k < S->tmp_segs.n; k++) iv_push(&segments, S->tmp_segs.v[k]);
     double xpos = n->xpos, ypos = n->ypos, xspeed = n->xspeed, yspeed = n->yspeed;
+    int cp_calls = 0;
     for (int it = 0; it < 32; it++) {
         double a, b;
         int result = get_single_closest_point(S, xpos, ypos, NINJA_RADIUS, &segments, &a, &b);
+        cp_calls++;
         if (result == 0) break;
         dx = xpos - a; dy = ypos - b;
         if (fabs(dx) <= 0.0000001) {                 /* ninja.py:312-318 band-aid */
@@ -551,6 +559,8 @@ static void ninja_collide_vs_tiles(OSim *S) {        /* ninja.py:269-379 */
         if (dy >= -0.0001) { n->ceiling_count += 1; n->ceiling_normal_x += norm_dx; n->ceiling_normal_y += norm_dy; }
         else { n->floor_count += 1; n->floor_normal_x += norm_dx; n->floor_normal_y += norm_dy; }
     }
+    STAT_ITERS(cp_calls, segments.n);
+    (void)cp_calls;
     n->xpos = xpos; n->ypos = ypos; n->xspeed = xspeed; n->yspeed = yspeed;
     free(segments.v);
 }

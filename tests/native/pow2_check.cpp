@@ -47,6 +47,18 @@ int main(int argc, char** argv) {
             if (margin > worst) worst = margin;
         }
     }
+    // exactly representable squares, including every x = +-2^k (x*x a power of two: the fast path's lo == 0 case)
+    long exact_n = 0;
+    for (int k = -100; k <= 100; k++)
+        for (int m = 1; m <= 4096; m++) {
+            double x = ldexp((double)m, k);
+            for (int sg = 0; sg < 2; sg++, x = -x) {
+                double ref = pow(x, two), got = pow2_exact(x);
+                exact_n++;
+                if (got != ref || ref != x * x) { if (bad_exact < 10) printf("exact-square mismatch x=%a ref=%a got=%a\n", x, ref, got); bad_exact++; }
+            }
+        }
+    printf("exact squares checked: %ld\n", exact_n);
     printf("n=%ld pow!=x*x: %ld (%.3g)  table-path mismatches: %ld  pow2_exact mismatches: %ld  max midpoint margin among differing: %.6g ulp\n",
            n, differ, (double)differ / n, bad_table, bad_exact, worst);
     return (bad_table || bad_exact) ? 1 : 0;
