@@ -68,6 +68,10 @@ typedef struct {
     const int32_t*  env_map;    /* [N] index into map_off */
     const uint8_t*  map_blob;   /* all compiled maps, concatenated (device) */
     const int64_t*  map_off;    /* [n_maps] byte offset of each map inside map_blob (device) */
+    uint32_t kind_mask;         /* OR of NppMapHeader.kind_mask over the loaded maps (entity-kind census); 0 = unknown.
+                                   Selects the step-kernel variant: level sets without moving / pushing entities run
+                                   on a kernel compiled without those phases. */
+    uint32_t reserved;
 } nppsim_state_t;
 
 int         nppsim_version(void);
@@ -125,6 +129,8 @@ int nppsim_step_host(const nppsim_state_t* st, const uint8_t* actions_host, uint
  * nppsim_sq_mode: 1 = exact pow emulation (default build), 0 = x*x. */
 int nppsim_debug_sq(const double* in_dev, double* out_dev, int32_t n, void* stream);
 int nppsim_sq_mode(void);
+/* Test hook: non-zero forces every launch onto the full (all entity kinds) kernel; returns the previous setting. */
+int nppsim_debug_force_full_kernel(int on);
 
 /* Kernel launch count since library load (bench.py's gpu_launches claim). */
 int64_t nppsim_launch_count(void);

@@ -14,14 +14,14 @@ class NppsimState(C.Structure):
         ("n_envs", C.c_int32), ("ent_cap", C.c_int32), ("dyn_cap", C.c_int32), ("n_maps", C.c_int32),
         ("nin_f", C.c_void_p), ("nin_i", C.c_void_p), ("env_i", C.c_void_p), ("ent_flag", C.c_void_p),
         ("dyn_f", C.c_void_p), ("dyn_i", C.c_void_p), ("env_map", C.c_void_p), ("map_blob", C.c_void_p),
-        ("map_off", C.c_void_p),
+        ("map_off", C.c_void_p), ("kind_mask", C.c_uint32), ("reserved", C.c_uint32),
     ]
 
 
 EXPORTS = (
     "nppsim_version", "nppsim_last_error", "nppsim_map_blob_bound", "nppsim_compile_map",
     "nppsim_reset", "nppsim_reset_terminal", "nppsim_step", "nppsim_step_actions", "nppsim_step_host", "nppsim_launch_count",
-    "nppsim_debug_sq", "nppsim_sq_mode",
+    "nppsim_debug_sq", "nppsim_sq_mode", "nppsim_debug_force_full_kernel",
 )
 
 
@@ -52,6 +52,7 @@ def lib():
     L.nppsim_launch_count.restype = i64
     L.nppsim_debug_sq.argtypes = [vp, vp, i32, vp]; L.nppsim_debug_sq.restype = C.c_int
     L.nppsim_sq_mode.restype = C.c_int
+    L.nppsim_debug_force_full_kernel.argtypes = [i32]; L.nppsim_debug_force_full_kernel.restype = C.c_int
     _lib = L
     return L
 

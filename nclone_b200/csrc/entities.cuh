@@ -6,8 +6,9 @@
 // late insertion take the next value of a per-env counter (append semantics,
 // entities.py:256-264, entity_exit_switch.py:120).  Entities that never change cell live in a
 // per-map static cell->ids table; the few that roam are found by scanning their slots.
-#pragma once
-#include "geom.cuh"
+// Included once per kernel variant (sim_variant.inc) with NPP_KINDS = the entity kinds that variant supports:
+// HAS(kind) is a compile-time constant, so the code of absent kinds (and whole phases: roaming-entity
+// move/think, physical collisions) disappears from the specialised kernel.
 
 struct EntS { double x, y; int kind, p0, p1, dyn, aux, index, load_order; };
 DEV EntS ld_ent(const Ctx& c, int id) {
@@ -316,6 +317,7 @@ __device__ __noinline__ int death_ball_think(Ctx c, double ninja_x, double ninja
 
 // ---- move / think for the dynamic slots (entity_dic order; nsim.py:235-251) --------------------------------
 DEV void dyn_move_phase(Ctx& c) {
+    if (!HAS_ANY(NPP_MOVE_MASK)) return;
     #pragma unroll 1
     for (int s = 0; s < c.n_dyn; s++) {
         uint32_t de = __ldg(c.dyn_ent + s);
@@ -334,6 +336,7 @@ DEV void dyn_move_phase(Ctx& c) {
     }
 }
 DEV void dyn_think_phase(const Nin& n, Ctx& c) {
+    if (!HAS_ANY(NPP_THINK_MASK)) return;
     #pragma unroll 1
     for (int s = 0; s < c.n_dyn; s++) {
         uint32_t de = __ldg(c.dyn_ent + s);
@@ -391,7 +394,7 @@ DEV void static_update_phase(Nin& n, Ctx& c) {
         for (int id = 0; id < c.n_ent && seen < want; id++) {
             uint8_t fl = FLAG(c, id);
             if ((fl & FL_MINE) == 2) { seen++; mine_think(n, c, id, valid); }
-            else if (fl & FL_TOUCH) { seen++; boost_move(n, c, id, valid); }
+            else if (HAS(NPP_K_BOOST) && (fl & FL_TOUCH)) { seen++; boost_move(n, c, id, valid); }
         }
     }
     if (!valid) return;
@@ -408,13 +411,13 @@ DEV void static_update_phase(Nin& n, Ctx& c) {
                 int id = __ldg(c.ecell_ids + k);
                 uint8_t fl = FLAG(c, id);
                 if ((fl & FL_MINE) == 1) mine_think(n, c, id, true);               // only mines use these bits
-                else if ((fl & (FL_IS_BOOST | FL_TOUCH)) == FL_IS_BOOST) nboost++;
+                else if (HAS(NPP_K_BOOST) && (fl & (FL_IS_BOOST | FL_TOUCH)) == FL_IS_BOOST) nboost++;
             }
         }
         // boost pads change the ninja's velocity, so they run in entity_dic (= id) order
         int last = -1;
         #pragma unroll 1
-        for (int r = 0; r < nboost; r++) {
+        for (int r = 0; HAS(NPP_K_BOOST) && r < nboost; r++) {
             int best = 0x7fffffff;
             #pragma unroll 1
             for (int xc = cx - 1; xc <= cx + 1; xc++) {
@@ -435,7 +438,7 @@ DEV void static_update_phase(Nin& n, Ctx& c) {
             int kind = ent_kind(c, id);
             uint8_t fl = FLAG(c, id);
             if (kind == NPP_K_MINE && (fl & FL_MINE) == 1) mine_think(n, c, id, true);
-            else if (kind == NPP_K_BOOST && !(fl & FL_TOUCH)) boost_move(n, c, id, true);
+            else if (HAS(NPP_K_BOOST) && kind == NPP_K_BOOST && !(fl & FL_TOUCH)) boost_move(n, c, id, true);
         }
     }
 }
@@ -550,20 +553,20 @@ DEV void ent_logical_collision(Nin& n, Ctx& c, int id, double& wall_normal) {
     double nx, ny, pen, other;
     const double px = n.f[F_XPOS], py = n.f[F_YPOS];
     switch (e.kind) {
-    case NPP_K_MINE: {                                          // entity_toggle_mine.py:120-128
+    case NPP_K_MINE: if (!HAS(NPP_K_MINE)) break; {                                          // entity_toggle_mine.py:120-128
         uint8_t fl = FLAG(c, id);
         if (ninja_valid_target(n) && (fl & FL_MINE) == 0 && overlap_circle_vs_circle(e.x, e.y, 4.0, px, py, NINJA_RADIUS)) {
             FLAG(c, id) = (fl & ~FL_MINE) | 1;
             ninja_kill(n, c, 0, 0, 0, 0, 1);
         }
         break; }
-    case NPP_K_GOLD:                                            // entity_gold.py:63-72
+    case NPP_K_GOLD: if (!HAS(NPP_K_GOLD)) break; // entity_gold.py:63-72
         if (n.i[I_STATE] != 8 && overlap_circle_vs_circle(e.x, e.y, 6, px, py, NINJA_RADIUS)) { GI(c, I_GOLD) += 1; FLAG(c, id) &= ~FL_ACTIVE; }
         break;
-    case NPP_K_EXIT:                                            // entity_exit.py:66-74
+    case NPP_K_EXIT: if (!HAS(NPP_K_EXIT)) break; // entity_exit.py:66-74
         if (overlap_circle_vs_circle(DYNF(c, e.dyn, 0), DYNF(c, e.dyn, 1), 12, px, py, NINJA_RADIUS)) ninja_win(n, c);
         break;
-    case NPP_K_EXIT_SWITCH:                                     // entity_exit_switch.py:67-129
+    case NPP_K_EXIT_SWITCH: if (!HAS(NPP_K_EXIT_SWITCH)) break; // entity_exit_switch.py:67-129
         if (overlap_circle_vs_circle(DYNF(c, e.dyn, 0), DYNF(c, e.dyn, 1), 6, px, py, NINJA_RADIUS)) {
             FLAG(c, id) &= ~FL_ACTIVE;
             EntS p = ld_ent(c, e.aux);
@@ -576,21 +579,21 @@ DEV void ent_logical_collision(Nin& n, Ctx& c, int id, double& wall_normal) {
             if (c.sw_frame < 0) c.sw_frame = n.i[I_FRAME];
         }
         break;
-    case NPP_K_DOOR_REGULAR:                                    // entity_door_regular.py:55-63
+    case NPP_K_DOOR_REGULAR: if (!HAS(NPP_K_DOOR_REGULAR)) break; // entity_door_regular.py:55-63
         if (overlap_circle_vs_circle(e.x, e.y, 10, px, py, NINJA_RADIUS)) {
             regular_door_change_state(c, id, e.dyn, false);
             DYNI(c, e.dyn, 2) &= ~255;                           // open_timer = 0
         }
         break;
-    case NPP_K_DOOR_LOCKED:                                     // entity_door_locked.py:54-67
+    case NPP_K_DOOR_LOCKED: if (!HAS(NPP_K_DOOR_LOCKED)) break; // entity_door_locked.py:54-67
         if (overlap_circle_vs_circle(e.x, e.y, 5, px, py, NINJA_RADIUS)) {
             GI(c, I_DOORS_OPENED) += 1; door_set_closed(c, id, false); FLAG(c, id) &= ~FL_ACTIVE; c.events |= NPPSIM_EV_LOCKED_DOOR;
         }
         break;
-    case NPP_K_DOOR_TRAP:                                       // entity_door_trap.py:60-67
+    case NPP_K_DOOR_TRAP: if (!HAS(NPP_K_DOOR_TRAP)) break; // entity_door_trap.py:60-67
         if (overlap_circle_vs_circle(e.x, e.y, 5, px, py, NINJA_RADIUS)) { door_set_closed(c, id, true); FLAG(c, id) &= ~FL_ACTIVE; }
         break;
-    case NPP_K_LAUNCH_PAD:                                      // entity_launch_pad.py:82-100
+    case NPP_K_LAUNCH_PAD: if (!HAS(NPP_K_LAUNCH_PAD)) break; // entity_launch_pad.py:82-100
         if (ninja_valid_target(n) && overlap_circle_vs_circle(e.x, e.y, 6, px, py, NINJA_RADIUS)) {
             double vx, vy; orientation_to_vector(e.p0, vx, vy);
             if ((e.x - (px - NINJA_RADIUS * vx)) * vx + (e.y - (py - NINJA_RADIUS * vy)) * vy >= -0.1) {
@@ -609,19 +612,19 @@ DEV void ent_logical_collision(Nin& n, Ctx& c, int id, double& wall_normal) {
             }
         }
         break;
-    case NPP_K_ONE_WAY: {                                       // entity_one_way_platform.py:111-116
+    case NPP_K_ONE_WAY: if (!HAS(NPP_K_ONE_WAY)) break; {                                       // entity_one_way_platform.py:111-116
         double vx, vy, len; orientation_to_vector(e.p0, vx, vy);
         if (one_way_depen(n, e.x, e.y, vx, vy, len) && fabs(vx) == 1) wall_normal += vx;
         break; }
-    case NPP_K_DRONE_ZAP: case NPP_K_MINI_DRONE:                // entity_drone_zap.py:57-64, entity_mini_drone.py:60-67
+    case NPP_K_DRONE_ZAP: case NPP_K_MINI_DRONE: if (!HAS_ANY((1u << NPP_K_DRONE_ZAP) | (1u << NPP_K_MINI_DRONE))) break;                // entity_drone_zap.py:57-64, entity_mini_drone.py:60-67
         if (ninja_valid_target(n) && overlap_circle_vs_circle(DYNF(c, e.dyn, 0), DYNF(c, e.dyn, 1), e.kind == NPP_K_DRONE_ZAP ? 7.5 : 4.0, px, py, NINJA_RADIUS))
             ninja_kill(n, c, 0, 0, 0, 0, 0);
         break;
-    case NPP_K_BOUNCE:                                          // entity_bounce_block.py:147-158
+    case NPP_K_BOUNCE: if (!HAS(NPP_K_BOUNCE)) break; // entity_bounce_block.py:147-158
         if (penetration_square_vs_point(DYNF(c, e.dyn, 0), DYNF(c, e.dyn, 1), px, py, 9 + NINJA_RADIUS + 0.1, nx, ny, pen, other))
             if (nx != 0) wall_normal += nx;
         break;
-    case NPP_K_THWUMP:                                          // entity_thwump.py:215-243
+    case NPP_K_THWUMP: if (!HAS(NPP_K_THWUMP)) break; // entity_thwump.py:215-243
         if (ninja_valid_target(n)) {
             double tx = DYNF(c, e.dyn, 0), ty = DYNF(c, e.dyn, 1);
             if (penetration_square_vs_point(tx, ty, px, py, 9 + NINJA_RADIUS + 0.1, nx, ny, pen, other)) {
@@ -634,7 +637,7 @@ DEV void ent_logical_collision(Nin& n, Ctx& c, int id, double& wall_normal) {
             }
         }
         break;
-    case NPP_K_DEATH_BALL:                                      // entity_death_ball.py:169-181
+    case NPP_K_DEATH_BALL: if (!HAS(NPP_K_DEATH_BALL)) break; // entity_death_ball.py:169-181
         if (ninja_valid_target(n)) {
             double bx = DYNF(c, e.dyn, 0), by = DYNF(c, e.dyn, 1);
             if (overlap_circle_vs_circle(bx, by, 5, px, py, NINJA_RADIUS)) {
@@ -645,7 +648,7 @@ DEV void ent_logical_collision(Nin& n, Ctx& c, int id, double& wall_normal) {
             }
         }
         break;
-    case NPP_K_SHWUMP: {                                        // entity_shove_thwump.py:173-202
+    case NPP_K_SHWUMP: if (!HAS(NPP_K_SHWUMP)) break; {                                        // entity_shove_thwump.py:173-202
         double sx = DYNF(c, e.dyn, 0), sy = DYNF(c, e.dyn, 1);
         uint8_t fl = FLAG(c, id);
         int state = (fl & FL_ST) >> FL_ST_SHIFT;

@@ -84,5 +84,5 @@ typedef struct {
     uint32_t off_dyn_ent;     // u32[n_dyn], slots in entity_dic order: entity id | kind << 16 | (drone: mode, else p0) << 24
     uint32_t off_doors;       // NppDoor[n_doors]
     uint32_t off_tiles;       // u8[1100] tile ids (cx*25+cy), for tile_dic readers
-    uint32_t pad[1];
+    uint32_t kind_mask;       // OR of (1 << NppKind) over the level's entities: picks the step-kernel variant
 } NppMapHeader;

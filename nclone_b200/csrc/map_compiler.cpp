@@ -305,6 +305,8 @@ extern "C" int nppsim_compile_map(const double* m, int32_t len, uint8_t* out, in
     h.magic = NPP_BLOB_MAGIC; h.total_bytes = (uint32_t)off;
     h.n_ent = (uint32_t)ents.size(); h.n_dyn = (uint32_t)dyn_ent.size(); h.n_doors = (uint32_t)doors.size();
     h.n_static_cell = (uint32_t)ids_load.size(); h.flags = reads_edges ? 1u : 0u;
+    h.kind_mask = 1u << NPP_K_NONE;              // never 0: 0 means "census unknown" to the launcher
+    for (size_t k = 0; k < ents.size(); k++) h.kind_mask |= 1u << ents[k].kind;
     h.spawn_x = m[1231] * 6; h.spawn_y = m[1232] * 6; h.db_count = m[1200];
     uint32_t* cell_hdr = (uint32_t*)(out + h.off_cell_hdr);
     uint32_t* segs = (uint32_t*)(out + h.off_segs);

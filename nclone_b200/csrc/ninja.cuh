@@ -1,15 +1,6 @@
 // ninja.cuh -- the ninja's per-frame update.  Reference: /root/reference/nclone/ninja.py.
-#pragma once
-#include "entities.cuh"
-#include "pool.cuh"
+// Included once per kernel variant, after entities.cuh (sim_variant.inc).
 
-// NPP_PROFILE: per-warp cycle counters per phase (debug builds only; tools/phase_profile.py)
-#ifdef NPP_PROFILE
-__device__ unsigned long long g_warp_cycles[1 << 16];      // per warp: kernel duration of the last launch
-__device__ unsigned long long g_warp_phase[1 << 16][4];   // per warp: cycles in entities / sweep / closest / post of the last launch
-#define PH_BEGIN long long _ph_t = clock64();
-#define PH_MARK(k) { long long _t2 = clock64(); if ((threadIdx.x & 31) == (__ffs(__activemask()) - 1)) { atomicAdd(&g_phase_cycles[k], (unsigned long long)(_t2 - _ph_t)); int _w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; int _b = (k) <= 3 ? 0 : ((k) == 5 ? 1 : ((k) == 6 ? 2 : (((k) == 9 || (k) == 10) ? 3 : -1))); if (_b >= 0 && _w < (1 << 16)) g_warp_phase[_w][_b] += (unsigned long long)(_t2 - _ph_t); } _ph_t = _t2; }
-#endif
 
 DEV void ninja_integrate(Nin& n) {                                       // ninja.py:198-206
     n.f[F_XSPEED] *= n.f[F_DRAG];
@@ -29,6 +20,7 @@ DEV bool ninja_pre_collision(Nin& n, Ctx& c, double& gx, double& gy) {
     n.i[I_CRUSHABLE] = 0;
     n.f[F_XCRUSH] = 0; n.f[F_YCRUSH] = 0; n.f[F_CRUSH_LEN] = 0;
     gx = n.f[F_XPOS]; gy = n.f[F_YPOS];
+    if (!HAS_ANY(NPP_PHYS_MASK)) return false;
     int nphys = 0;
     gather_entities(c, gx, gy, [&](int id) { if (is_physical_kind(ent_kind(c, id))) nphys++; });
     return nphys > 0;
@@ -407,7 +399,7 @@ DEV void sim_tick(Nin& n, Ctx& c, WarpPool& wp, bool run, int hor_input, int jum
     bool sub = alive;
     #pragma unroll 1
     for (int s = 0; s < 4 && __any_sync(FULL_MASK, sub); s++) {
-        if (sub && phys) ninja_collide_vs_objects(n, c, gx, gy);
+        if (HAS_ANY(NPP_PHYS_MASK) && sub && phys) ninja_collide_vs_objects(n, c, gx, gy);
         bool idle = ninja_collide_vs_tiles(n, c, wp, sub);
         if (idle && !phys) sub = false;
     }

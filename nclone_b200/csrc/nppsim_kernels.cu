@@ -1,6 +1,6 @@
 // nppsim_kernels.cu -- sm_100a kernels + C ABI launchers (include/nppsim.h).
 // Device code lives in geom.cuh / entities.cuh / ninja.cuh; see geom.cuh for the design notes.
-#include "ninja.cuh"
+#include "pool.cuh"
 
 #include <atomic>
 #include <cstring>
@@ -9,42 +9,12 @@ namespace {
 
 thread_local char g_err[256] = "";
 std::atomic<long long> g_launches{0};
+bool g_force_full = false;     // test hook: run every level set on the full kernel
 
 int fail(int code, const char* msg) { snprintf(g_err, sizeof(g_err), "%s", msg); return code; }
 int cuda_fail(cudaError_t e, const char* what) {
     snprintf(g_err, sizeof(g_err), "%s: %s", what, cudaGetErrorString(e));
     return (int)e > 0 ? (int)e : 1;
-}
-
-// ---- per-thread context ---------------------------------------------------------------------------
-DEV void ctx_init(Ctx& c, const nppsim_state_t& st, int i) {
-    const uint8_t* blob = st.map_blob + __ldg(st.map_off + __ldg(st.env_map + i));
-    const NppMapHeader* h = reinterpret_cast<const NppMapHeader*>(blob);
-    c.cell_hdr = reinterpret_cast<const uint32_t*>(blob + h->off_cell_hdr);
-    c.segs = reinterpret_cast<const uint32_t*>(blob + h->off_segs);
-    c.hedge = reinterpret_cast<const uint32_t*>(blob + h->off_hedge);
-    c.vedge = reinterpret_cast<const uint32_t*>(blob + h->off_vedge);
-    c.ents = reinterpret_cast<const NppStaticEnt*>(blob + h->off_ents);
-    c.ecell_off = reinterpret_cast<const uint16_t*>(blob + h->off_ecell_off);
-    c.dyn_ent = reinterpret_cast<const uint32_t*>(blob + h->off_dyn_ent);
-    c.doors = reinterpret_cast<const NppDoor*>(blob + h->off_doors);
-    c.db_count = h->db_count;
-    c.N = st.n_envs; c.n_ent = h->n_ent; c.n_dyn = h->n_dyn; c.n_doors = h->n_doors;
-    c.flag = st.ent_flag + i; c.dynf = st.dyn_f + i; c.dyni = st.dyn_i + i; c.envi = st.env_i + i;
-    c.gf = st.nin_f + i; c.gi = st.nin_i + i;
-    c.order_mode = c.envi[(size_t)NPPSIM_ENV_ORDER * c.N];
-    c.ecell_ids = reinterpret_cast<const uint16_t*>(blob + (c.order_mode ? h->off_ecell_ids_dic : h->off_ecell_ids));
-    c.stamp = c.envi[(size_t)NPPSIM_ENV_STAMP * c.N];
-    c.hot = c.envi[(size_t)NPPSIM_ENV_HOT * c.N];
-    c.sw_frame = c.envi[(size_t)NPPSIM_ENV_SWFRAME * c.N];
-    c.events = 0;
-    c.pending_doors = false;
-}
-DEV void ctx_flush(const Ctx& c) {
-    c.envi[(size_t)NPPSIM_ENV_STAMP * c.N] = c.stamp;
-    c.envi[(size_t)NPPSIM_ENV_HOT * c.N] = c.hot;
-    c.envi[(size_t)NPPSIM_ENV_SWFRAME * c.N] = c.sw_frame;
-    if (c.events) c.envi[(size_t)NPPSIM_ENV_EVENTS * c.N] |= c.events;
 }
 
 // ---- reset -------------------------------------------------------------------------------------------
@@ -127,82 +97,33 @@ __global__ void __launch_bounds__(128) reset_kernel(nppsim_state_t st, const uin
     envi[NPPSIM_ENV_HOT * N] = hot;
 }
 
-// Fields of the ninja record that live in registers for the launch; the rest is written through (GF/GI).
-__host__ __device__ constexpr bool hot_f(int f) {
-    return !(f == F_FRICTION || f == F_CNX || f == F_CNY || f == F_XLP || f == F_YLP || f == F_DEATH_X || f == F_DEATH_Y ||
-             f == F_DEATH_XS || f == F_DEATH_YS || f == F_X_AT_ACTION || f == F_Y_AT_ACTION);
-}
-__host__ __device__ constexpr bool hot_i(int f) {
-    return !(f == I_JUMP_USELESS || f == I_LAST_JUMP_BUFFERED || f == I_GOLD || f == I_DOORS_OPENED || f == I_TERMINAL_IMPACT ||
-             f == I_DEATH_CAUSE || f == I_HOR_INPUT || f == I_JUMP_INPUT);
-}
+}  // namespace
 
-// ---- step -----------------------------------------------------------------------------------------------
-// The register budget is left to ptxas (168/thread): capping it to fit more blocks per SM spills the
-// ninja record and costs more than the extra residency gains (measured: 128 regs -> -20 %).
+// ---- step kernel variants ------------------------------------------------------------------------------
 #ifndef STEP_BLOCK
 #define STEP_BLOCK 128
 #endif
 #ifndef STEP_BLOCKS_PER_SM
 #define STEP_BLOCKS_PER_SM 1
 #endif
-__global__ void __launch_bounds__(STEP_BLOCK, STEP_BLOCKS_PER_SM) step_kernel(nppsim_state_t st, const int8_t* __restrict__ hor, const int8_t* __restrict__ jump,
-                                                    const uint8_t* __restrict__ actions, int input_ticks, int n_ticks,
-                                                    const int32_t* __restrict__ tick_limit, int stop_on_terminal, int32_t* frames_executed) {
-    __shared__ WarpPool pools[STEP_BLOCK / 32];
-    WarpPool& wp = pools[threadIdx.x >> 5];
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool valid = i < st.n_envs;
-    if (!valid) i = st.n_envs - 1;            // keep the lane in the warp (collectives); it never runs or stores
-    const size_t N = st.n_envs;
-    int limit = n_ticks;
-    if (tick_limit) limit = min(limit, tick_limit[i]);
-    if (!valid) limit = 0;
-#ifdef NPP_PROFILE
-    long long _k0 = clock64();
-#endif
-    Ctx c; ctx_init(c, st, i);
-    Nin n;
-    const double* nf = st.nin_f + i; const int32_t* ni = st.nin_i + i;
-#pragma unroll
-    for (int f = 0; f < NPPSIM_NF; f++) if (hot_f(f)) n.f[f] = nf[f * N];
-#pragma unroll
-    for (int f = 0; f < NPPSIM_NI; f++) if (hot_i(f)) n.i[f] = ni[f * N];
-    int h = 0, j = 0;
-    if (actions) {   // ACTION_TO_INPUTS: action_replayer.py:30-37
-        int a = actions[i]; if (a > 5) a = 0;
-        h = (a == 1 || a == 4) ? -1 : ((a == 2 || a == 5) ? 1 : 0);
-        j = a >= 3;
-    }
-    int done = 0;
-    bool stopped = false;
-    #pragma unroll 1
-    for (int t = 0; t < n_ticks; t++) {
-        bool run = (t < limit) && !stopped;
-        if (!__any_sync(FULL_MASK, run)) break;
-        if (run && !actions && (t == 0 || input_ticks > 1)) { h = hor[(size_t)t * N + i]; j = jump[(size_t)t * N + i]; }
-        sim_tick(n, c, wp, run, h, j);
-        if (run) {
-            done++;
-            if (stop_on_terminal) { int s = n.i[I_STATE]; if (s == 6 || s == 7 || s == 8) stopped = true; }   // base_environment.py:605-609
-        }
-    }
-    if (!valid) return;
-    if (done > 0) {
-        double* of = st.nin_f + i; int32_t* oi = st.nin_i + i;
-#pragma unroll
-        for (int f = 0; f < NPPSIM_NF; f++) if (hot_f(f)) of[f * N] = n.f[f];
-#pragma unroll
-        for (int f = 0; f < NPPSIM_NI; f++) if (hot_i(f)) oi[f * N] = n.i[f];
-        ctx_flush(c);
-        c.envi[(size_t)NPPSIM_ENV_TICKS * N] += done;
-    }
-    if (frames_executed) frames_executed[i] = done;
-#ifdef NPP_PROFILE
-    if ((threadIdx.x & 31) == 0) { unsigned long long d = (unsigned long long)(clock64() - _k0); atomicAdd(&g_phase_cycles[15], d); int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; if (w < (1 << 16)) g_warp_cycles[w] = d; }
-#endif
-}
+#define NPP_MOVE_MASK ((1u << NPP_K_DRONE_ZAP) | (1u << NPP_K_MINI_DRONE) | (1u << NPP_K_BOUNCE) | (1u << NPP_K_THWUMP))
+#define NPP_THINK_MASK ((1u << NPP_K_DOOR_REGULAR) | (1u << NPP_K_THWUMP) | (1u << NPP_K_DEATH_BALL) | (1u << NPP_K_SHWUMP))
+#define NPP_PHYS_MASK ((1u << NPP_K_ONE_WAY) | (1u << NPP_K_BOUNCE) | (1u << NPP_K_THWUMP) | (1u << NPP_K_SHWUMP))
+// "basic" levels: nothing moves, nothing pushes (every generated curriculum category of BASELINE.json's configs)
+#define NPP_BASIC_MASK ((1u << NPP_K_NONE) | (1u << NPP_K_MINE) | (1u << NPP_K_GOLD) | (1u << NPP_K_EXIT) | (1u << NPP_K_EXIT_SWITCH) | (1u << NPP_K_DOOR_LOCKED) | (1u << NPP_K_DOOR_TRAP))
 
+#define NPP_VARIANT sim_full
+#define NPP_KINDS 0xffffffffu
+#include "sim_variant.inc"
+#undef NPP_VARIANT
+#undef NPP_KINDS
+#define NPP_VARIANT sim_basic
+#define NPP_KINDS NPP_BASIC_MASK
+#include "sim_variant.inc"
+#undef NPP_VARIANT
+#undef NPP_KINDS
+
+namespace {
 __global__ void sq_kernel(const double* in, double* out, int n) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = SQ(in[i]);
@@ -227,7 +148,10 @@ int launch_step(const nppsim_state_t* st, const int8_t* hor, const int8_t* jump,
     if (!actions && !(input_ticks == 1 || input_ticks == n_ticks)) return fail(NPPSIM_E_ARG, "input_ticks must be 1 or n_ticks");
     const int block = STEP_BLOCK;
     const int grid = (st->n_envs + block - 1) / block;
-    step_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(*st, hor, jump, actions, input_ticks, n_ticks, tick_limit, stop_on_terminal, frames_executed);
+    // kind_mask == 0: census unknown (older callers) -> the full kernel
+    const bool basic = st->kind_mask != 0 && (st->kind_mask & ~NPP_BASIC_MASK) == 0 && !g_force_full;
+    if (basic) sim_basic::step_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(*st, hor, jump, actions, input_ticks, n_ticks, tick_limit, stop_on_terminal, frames_executed);
+    else sim_full::step_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(*st, hor, jump, actions, input_ticks, n_ticks, tick_limit, stop_on_terminal, frames_executed);
     g_launches++;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_fail(e, "step_kernel launch");
@@ -243,6 +167,7 @@ const char* nppsim_compile_error(void);
 const char* nppsim_last_error(void) { return g_err[0] ? g_err : nppsim_compile_error(); }
 int64_t nppsim_launch_count(void) { return (int64_t)g_launches.load(); }
 int nppsim_sq_mode(void) { return NPP_SQ_MODE; }
+int nppsim_debug_force_full_kernel(int on) { int was = g_force_full; g_force_full = on != 0; return was; }
 #ifdef NPP_PROFILE
 int nppsim_debug_warp_cycles(unsigned long long* out, unsigned long long* phases, int n, int reset) {
     cudaDeviceSynchronize();

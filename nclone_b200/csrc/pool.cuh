@@ -13,8 +13,13 @@
 #include "geom.cuh"
 
 #ifdef NPP_PROFILE
+// NPP_PROFILE: per-warp cycle counters per phase (debug builds only; tools/phase_profile.py)
 __device__ unsigned long long g_phase_cycles[16];      // [0..10] cycles per phase, [11..14] event counters, [15] kernel cycles
+__device__ unsigned long long g_warp_cycles[1 << 16];      // per warp: kernel duration of the last launch
+__device__ unsigned long long g_warp_phase[1 << 16][4];   // per warp: cycles in entities / sweep / closest / post of the last launch
 #define PH_COUNT(k) atomicAdd(&g_phase_cycles[k], 1ULL)
+#define PH_BEGIN long long _ph_t = clock64();
+#define PH_MARK(k) { long long _t2 = clock64(); if ((threadIdx.x & 31) == (__ffs(__activemask()) - 1)) { atomicAdd(&g_phase_cycles[k], (unsigned long long)(_t2 - _ph_t)); int _w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; int _b = (k) <= 3 ? 0 : ((k) == 5 ? 1 : ((k) == 6 ? 2 : (((k) == 9 || (k) == 10) ? 3 : -1))); if (_b >= 0 && _w < (1 << 16)) g_warp_phase[_w][_b] += (unsigned long long)(_t2 - _ph_t); } _ph_t = _t2; }
 #else
 #define PH_BEGIN
 #define PH_MARK(k)

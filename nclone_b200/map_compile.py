@@ -15,7 +15,7 @@ HEADER = np.dtype([
     ("spawn_x", "<f8"), ("spawn_y", "<f8"), ("db_count", "<f8"),
     ("off_cell_hdr", "<u4"), ("off_segs", "<u4"), ("off_hedge", "<u4"), ("off_vedge", "<u4"), ("off_ents", "<u4"),
     ("off_ecell_off", "<u4"), ("off_ecell_ids", "<u4"), ("off_ecell_ids_dic", "<u4"), ("off_dyn_ent", "<u4"),
-    ("off_doors", "<u4"), ("off_tiles", "<u4"), ("pad", "<u4"),
+    ("off_doors", "<u4"), ("off_tiles", "<u4"), ("kind_mask", "<u4"),
 ])
 STATIC_ENT = np.dtype([
     ("x", "<f8"), ("y", "<f8"), ("kind", "u1"), ("type", "u1"), ("p0", "u1"), ("p1", "u1"),
@@ -52,6 +52,7 @@ class MapTables:
             raise ValueError("not a map blob")
         h = self.h
         self.n_ent, self.n_dyn, self.n_doors = int(h["n_ent"]), int(h["n_dyn"]), int(h["n_doors"])
+        self.kind_mask = int(h["kind_mask"])
         self.cell_hdr = np.frombuffer(blob, "<u4", 1100, int(h["off_cell_hdr"]))
         self.segs = np.frombuffer(blob, "<u4", 8800, int(h["off_segs"])).reshape(1100, 8)
         self.hedge = np.frombuffer(blob, "<u4", 142, int(h["off_hedge"]))

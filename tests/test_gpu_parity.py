@@ -231,3 +231,60 @@ def test_large_random_rollout_vs_oracle(golden_replays):
             badi = np.nonzero((gi != ni).any(1))[0]
             assert badf.size == 0 and badi.size == 0, (st, badf[:5], badi[:5], env_to_map[badf[:5]])
         sim.reset_terminal(2000)
+
+
+def test_basic_variant_vs_oracle_and_full_kernel():
+    """Level sets without moving / pushing entities run on the specialised `sim_basic` kernel
+    (nppsim_state_t.kind_mask).  (1) 1,280 envs of the benchmark levels against the oracle;
+    (2) 16,384 envs x 150 agent steps: basic and full kernels must leave identical state everywhere."""
+    import torch
+    from nclone_b200 import BatchedSimulator
+    from nclone_b200._lib import lib
+    import bench
+    BASIC = (1 << 1) | (1 << 2) | (1 << 3) | (1 << 4) | (1 << 6) | (1 << 7) | 1
+    arr, lens = bench.load_maps("simplest_with_mines")
+    arr2, lens2 = bench.load_maps("locked_doors")
+    maps = [arr[k, :lens[k]] for k in range(2048, 3072)] + [arr2[k, :lens2[k]] for k in range(256, 512)]
+    N = len(maps)
+    rng = np.random.default_rng(5)
+    steps, every = 160, 20
+    actions = rng.integers(0, 6, size=(steps, N)).astype(np.uint8)
+    hold = rng.integers(1, 6, size=(steps, N))
+    for st in range(1, steps):
+        keep = (st % hold[st]) != 0
+        actions[st, keep] = actions[st - 1, keep]
+    sim = BatchedSimulator(N)
+    sim.load_maps(maps, np.arange(N))
+    assert sim.kind_mask != 0 and (sim.kind_mask & ~BASIC) == 0
+    ref = _oracle_rollout(maps, np.arange(N), actions, 4, 2000, every)
+    ci = 0
+    for st in range(steps):
+        sim.step(torch.from_numpy(actions[st]).cuda(), 4, True)
+        if (st + 1) % every == 0:
+            _, nf, ni = ref[ci]; ci += 1
+            gf = sim.nin_f.cpu().numpy().T; gi = sim.nin_i.cpu().numpy().T.astype(np.int64)
+            badf = np.nonzero((gf.view(np.int64) != nf.view(np.int64)).any(1))[0]
+            badi = np.nonzero((gi != ni).any(1))[0]
+            assert badf.size == 0 and badi.size == 0, (st, badf[:5], badi[:5])
+        sim.reset_terminal(2000)
+    # (2) kernel against kernel
+    N2 = 16384
+    allmaps = [arr[k, :lens[k]] for k in range(len(arr))] + [arr2[k, :lens2[k]] for k in range(len(arr2))]
+    e2m = np.arange(N2) % len(allmaps)
+    gen = torch.Generator(device="cuda"); gen.manual_seed(7)
+    acts = torch.randint(0, 6, (150, N2), generator=gen, device="cuda", dtype=torch.uint8)
+    states = []
+    L = lib()
+    for force in (0, 1):
+        was = L.nppsim_debug_force_full_kernel(force)
+        try:
+            s2 = BatchedSimulator(N2)
+            s2.load_maps(allmaps, e2m)
+            for st in range(150):
+                s2.step(acts[st], 4, True)
+                s2.reset_terminal(2000)
+            states.append([t.clone() for t in (s2.nin_f, s2.nin_i, s2.env_i, s2.ent_flag, s2.dyn_f, s2.dyn_i)])
+        finally:
+            L.nppsim_debug_force_full_kernel(was)
+    for a, b in zip(*states):
+        assert torch.equal(a.view(torch.uint8), b.view(torch.uint8))
