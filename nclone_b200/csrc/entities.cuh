@@ -445,15 +445,26 @@ DEV void static_update_phase(Nin& n, Ctx& c) {
 
 // ---- ordered 3x3 neighbourhood gather: physics.py:79-101 ------------------------------------------------------
 // f(id) is called for every active entity of the nine cells, x-major over cells, list order inside a cell.
+#define NPP_ROAM_REG 4        // roaming entities of one neighbourhood kept in registers; more take the generic merge
 template <class F>
 DEV void gather_entities(Ctx& c, double xpos, double ypos, F&& f) {
     int cx = clampi(floordiv24(xpos), 0, 43), cy = clampi(floordiv24(ypos), 0, 24);
     int x0 = max(cx - 1, 0), x1 = min(cx + 1, 43), y0 = max(cy - 1, 0), y1 = min(cy + 1, 24);
+    // roaming entities inside the neighbourhood: (cell, stamp, id) of the first few in registers
     int nroam = 0;
+    int rc0 = -1, rc1 = -1, rc2 = -1, rc3 = -1, rs0 = 0, rs1 = 0, rs2 = 0, rs3 = 0, ri0 = 0, ri1 = 0, ri2 = 0, ri3 = 0;
     #pragma unroll 1
     for (int s = 0; s < c.n_dyn; s++) {
         int cell = DYNI(c, s, 0);
-        if (cell >= 0) { int ex = cell / NPP_NCY, ey = cell - ex * NPP_NCY; if (ex >= x0 && ex <= x1 && ey >= y0 && ey <= y1) nroam++; }
+        if (cell < 0) continue;
+        int ex = cell / NPP_NCY, ey = cell - ex * NPP_NCY;
+        if (ex < x0 || ex > x1 || ey < y0 || ey > y1) continue;
+        if (nroam < NPP_ROAM_REG) {
+            int st = DYNI(c, s, 1), id = (int)(__ldg(c.dyn_ent + s) & 0xffff);
+            if (nroam == 0) { rc0 = cell; rs0 = st; ri0 = id; } else if (nroam == 1) { rc1 = cell; rs1 = st; ri1 = id; }
+            else if (nroam == 2) { rc2 = cell; rs2 = st; ri2 = id; } else { rc3 = cell; rs3 = st; ri3 = id; }
+        }
+        nroam++;
     }
     if (nroam == 0) {
         #pragma unroll 1
@@ -465,11 +476,27 @@ DEV void gather_entities(Ctx& c, double xpos, double ypos, F&& f) {
         return;
     }
     #pragma unroll 1
-    for (int xc = x0; xc <= x1; xc++)
+    for (int xc = x0; xc <= x1; xc++) {
+        const int cbase = xc * NPP_NCY;
+        // a column without roaming entities streams its three cells as one CSR range
+        const bool col_has = (nroam > NPP_ROAM_REG) || (rc0 >= cbase + y0 && rc0 <= cbase + y1) || (rc1 >= cbase + y0 && rc1 <= cbase + y1) ||
+                             (rc2 >= cbase + y0 && rc2 <= cbase + y1) || (rc3 >= cbase + y0 && rc3 <= cbase + y1);
+        if (!col_has) {
+            int a = __ldg(c.ecell_off + cbase + y0), b = __ldg(c.ecell_off + cbase + y1 + 1);
+            #pragma unroll 1
+            for (int k = a; k < b; k++) { int id = __ldg(c.ecell_ids + k); if (FLAG(c, id) & FL_ACTIVE) f(id); }
+            continue;
+        }
         #pragma unroll 1
         for (int yc = y0; yc <= y1; yc++) {
-            int cell = xc * NPP_NCY + yc;
+            int cell = cbase + yc;
             int ka = __ldg(c.ecell_off + cell), kb = __ldg(c.ecell_off + cell + 1);
+            const bool cell_has = (nroam > NPP_ROAM_REG) || rc0 == cell || rc1 == cell || rc2 == cell || rc3 == cell;
+            if (!cell_has) {
+                #pragma unroll 1
+                for (int k = ka; k < kb; k++) { int id = __ldg(c.ecell_ids + k); if (FLAG(c, id) & FL_ACTIVE) f(id); }
+                continue;
+            }
             int last = -1;
             #pragma unroll 1
             for (;;) {
@@ -479,15 +506,23 @@ DEV void gather_entities(Ctx& c, double xpos, double ypos, F&& f) {
                     sst = c.order_mode ? sid : (int)(__ldg(reinterpret_cast<const uint32_t*>(c.ents + sid) + 7) & 0xffff);
                 }
                 int rid = -1, rst = 0x7fffffff;
-                #pragma unroll 1
-                for (int s = 0; s < c.n_dyn; s++)
-                    if (DYNI(c, s, 0) == cell) { int st = DYNI(c, s, 1); if (st > last && st < rst) { rst = st; rid = __ldg(c.dyn_ent + s) & 0xffff; } }
+                if (nroam <= NPP_ROAM_REG) {
+                    if (rc0 == cell && rs0 > last && rs0 < rst) { rst = rs0; rid = ri0; }
+                    if (rc1 == cell && rs1 > last && rs1 < rst) { rst = rs1; rid = ri1; }
+                    if (rc2 == cell && rs2 > last && rs2 < rst) { rst = rs2; rid = ri2; }
+                    if (rc3 == cell && rs3 > last && rs3 < rst) { rst = rs3; rid = ri3; }
+                } else {
+                    #pragma unroll 1
+                    for (int s = 0; s < c.n_dyn; s++)
+                        if (DYNI(c, s, 0) == cell) { int st = DYNI(c, s, 1); if (st > last && st < rst) { rst = st; rid = __ldg(c.dyn_ent + s) & 0xffff; } }
+                }
                 if (sid < 0 && rid < 0) break;
                 int id;
                 if (sst < rst) { id = sid; last = sst; ka++; } else { id = rid; last = rst; }
                 if (FLAG(c, id) & FL_ACTIVE) f(id);
             }
         }
+    }
 }
 // after a logical-collision pass: exit doors whose switch was taken join the grid now, so the
 // pass that took the switch never sees them (the reference gathers its list before looping).

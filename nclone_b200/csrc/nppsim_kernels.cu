@@ -148,6 +148,13 @@ int launch_step(const nppsim_state_t* st, const int8_t* hor, const int8_t* jump,
     if (!actions && !(input_ticks == 1 || input_ticks == n_ticks)) return fail(NPPSIM_E_ARG, "input_ticks must be 1 or n_ticks");
     const int block = STEP_BLOCK;
     const int grid = (st->n_envs + block - 1) / block;
+    // let the SM carve out enough shared memory for as many blocks as the register file admits (once per process)
+    static const bool carveout_set = [] {
+        cudaFuncSetAttribute(sim_basic::step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        cudaFuncSetAttribute(sim_full::step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        return true;
+    }();
+    (void)carveout_set;
     // kind_mask == 0: census unknown (older callers) -> the full kernel
     const bool basic = st->kind_mask != 0 && (st->kind_mask & ~NPP_BASIC_MASK) == 0 && !g_force_full;
     if (basic) sim_basic::step_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(*st, hor, jump, actions, input_ticks, n_ticks, tick_limit, stop_on_terminal, frames_executed);

@@ -28,6 +28,34 @@ template <int OP> __global__ void k(double* out, long long* cyc, int arcmask, do
     out[lane] = acc + x;
     if (lane == 0) *cyc = t1 - t0;
 }
+// the cooperative closest-point iteration on the wedge of bench level 32 (11 cached segments, one arc in quadrant)
+__global__ void coop(double* out, long long* cyc, double x0, double y0) {
+    __shared__ WarpPool wp;
+    int lane = threadIdx.x;
+    uint32_t segs[11] = {mk_lin(67, 24, 66, 24), mk_lin(66, 24, 66, 25), mk_lin(67, 25, 67, 24), mk_lin(67, 26, 67, 25), mk_arc(70, 22, 1, 0, 1),
+                         mk_lin(69, 24, 68, 26), mk_lin(68, 26, 69, 26), mk_lin(70, 24, 69, 24), mk_lin(69, 26, 70, 26), mk_lin(70, 25, 70, 24), mk_lin(70, 26, 70, 25)};
+    const int ns = 11;
+    SegC g = seg_decode(lane < ns ? segs[lane] : 0u);
+    Ctx c; c.cell_hdr = nullptr; c.segs = nullptr;
+    double x = x0, y = y0, acc = 0;
+    long long t0 = clock64();
+    #pragma unroll 1
+    for (int i = 0; i < K; i++) {
+        double a = 0, b = 0;
+        int r = warp_closest_point(wp, c, 0, lane < ns, g, 0, 0, 0, 0, x, y, a, b);
+        acc += a + b + r; x += acc * 1e-300;
+    }
+    long long t1 = clock64();
+    out[lane] = acc;
+    if (lane == 0) *cyc = t1 - t0;
+}
+void run_coop(const char* name, double x0, double y0) {
+    double* out; long long* cyc; cudaMalloc(&out, 256); cudaMalloc(&cyc, 8);
+    coop<<<1, 32>>>(out, cyc, x0, y0); coop<<<1, 32>>>(out, cyc, x0, y0);
+    cudaDeviceSynchronize();
+    long long h; cudaMemcpy(&h, cyc, 8, cudaMemcpyDeviceToHost);
+    printf("%-44s %8.1f cycles\n", name, (double)h / K);
+}
 template <int OP> void run(const char* name, int arcmask, double x0, double y0) {
     double* out; long long* cyc; cudaMalloc(&out, 256); cudaMalloc(&cyc, 8);
     k<OP><<<1, 32>>>(out, cyc, arcmask, x0, y0); k<OP><<<1, 32>>>(out, cyc, arcmask, x0, y0);
@@ -36,6 +64,9 @@ template <int OP> void run(const char* name, int arcmask, double x0, double y0) 
     printf("%-44s %8.1f cycles\n", name, (double)h / K);
 }
 int main() {
+    run_coop("coop closest point, wedge (810, 280)", 810.0, 280.0);
+    run_coop("coop closest point, wedge (810.3, 279.9)", 810.3, 279.9);
+    run_coop("coop closest point, far (700, 100)", 700.0, 100.0);
     run<0>("closest_item linear (touching floor)", 0, 400.0, 280.0);
     run<0>("closest_item linear (AABB reject)", 0, 400.0, 200.0);
     run<0>("closest_item arc in quadrant", -1, 400.0, 295.0);
