@@ -72,6 +72,10 @@ typedef struct {
                                    Selects the step-kernel variant: level sets without moving / pushing entities run
                                    on a kernel compiled without those phases. */
     uint32_t reserved;
+    int32_t*  warp_order;       /* optional [ceil(N/32)]: launch slot -> group of 32 consecutive envs (a permutation);
+                                   NULL = identity.  Rewritten by nppsim_step* after each launch when warp_cost is set. */
+    uint32_t* warp_cost;        /* optional [ceil(N/32)]: device-clock cost of each group in the last launch (written by
+                                   the step kernel), the key of the longest-first order */
 } nppsim_state_t;
 
 int         nppsim_version(void);

@@ -80,6 +80,10 @@ class BatchedSimulator:
         st.nin_f, st.nin_i, st.env_i = self.nin_f.data_ptr(), self.nin_i.data_ptr(), self.env_i.data_ptr()
         st.ent_flag, st.dyn_f, st.dyn_i = self.ent_flag.data_ptr(), self.dyn_f.data_ptr(), self.dyn_i.data_ptr()
         st.env_map, st.map_blob, st.map_off = self.env_map.data_ptr(), self.map_blob.data_ptr(), self.map_off.data_ptr()
+        nw = (N + 31) // 32
+        self.warp_order = torch.arange(nw, dtype=torch.int32, device=dev)      # longest-first launch order (csrc/sim_variant.inc)
+        self.warp_cost = torch.zeros(nw, dtype=torch.int32, device=dev)
+        st.warp_order, st.warp_cost = self.warp_order.data_ptr(), self.warp_cost.data_ptr()
         self.kind_mask = 0
         for t in self.maps:
             self.kind_mask |= t.kind_mask      # entity-kind census of the level set -> step-kernel variant

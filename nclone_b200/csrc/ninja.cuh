@@ -101,10 +101,10 @@ DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
     double a0 = 0, b0 = 0; int nseg = 0;
     int result0 = pooled_closest_point(wp, c, alive, gx1, gy1, gx2, gy2, xpos, ypos, a0, b0, nseg);
     bool need = alive && depen(result0, a0, b0);
-    if (need) {
+    if (__any_sync(FULL_MASK, need)) {                      // iteration 1: 5 % of lanes, i.e. most warps -> pooled again
         double a = 0, b = 0;
-        int result = cached_closest_point(wp, c, nseg, gx1, gy1, gx2, gy2, xpos, ypos, a, b);
-        need = depen(result, a, b);
+        int result = pooled_list_closest(wp, c, need, nseg, gx1, gy1, gx2, gy2, xpos, ypos, a, b);
+        if (need) need = depen(result, a, b);
     }
     unsigned todo;
     #pragma unroll 1
@@ -131,7 +131,7 @@ DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
             if (lane == o) cont = depen(result, a, b);
             const bool go = __shfl_sync(FULL_MASK, (int)cont, o);
 #ifdef NPP_PROFILE
-            if (lane == o) { long long _c2 = clock64(); atomicAdd(&g_phase_cycles[13], (unsigned long long)(_c1 - _c0)); atomicAdd(&g_phase_cycles[14], (unsigned long long)(_c2 - _c1)); }
+            (void)_c0; (void)_c1;
 #endif
             if (!go) break;
         }

@@ -124,6 +124,32 @@ __global__ void __launch_bounds__(128) reset_kernel(nppsim_state_t st, const uin
 #undef NPP_KINDS
 
 namespace {
+// Longest-first order for the next launch from the costs of this one (one block; nw <= 2^20 / 32).
+// Three classes by cost relative to the mean -- > 3x, > 1.5x, the rest -- placed in that order; inside a
+// class the order is arbitrary (it only affects scheduling, never results).
+__global__ void __launch_bounds__(1024) sched_kernel(int32_t* __restrict__ order, const uint32_t* __restrict__ cost, int nw) {
+    __shared__ unsigned long long s_sum;
+    __shared__ int s_cnt[3], s_pos[3];
+    if (threadIdx.x == 0) { s_sum = 0; s_cnt[0] = s_cnt[1] = s_cnt[2] = 0; }
+    __syncthreads();
+    unsigned long long loc = 0;
+    for (int w = threadIdx.x; w < nw; w += blockDim.x) loc += cost[w];
+    atomicAdd(&s_sum, loc);
+    __syncthreads();
+    const unsigned long long mean = s_sum / (unsigned long long)max(nw, 1);
+    for (int w = threadIdx.x; w < nw; w += blockDim.x) {
+        const unsigned long long v = cost[w];
+        atomicAdd(&s_cnt[v > 3 * mean ? 0 : (2 * v > 3 * mean ? 1 : 2)], 1);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) { s_pos[0] = 0; s_pos[1] = s_cnt[0]; s_pos[2] = s_cnt[0] + s_cnt[1]; }
+    __syncthreads();
+    for (int w = threadIdx.x; w < nw; w += blockDim.x) {
+        const unsigned long long v = cost[w];
+        order[atomicAdd(&s_pos[v > 3 * mean ? 0 : (2 * v > 3 * mean ? 1 : 2)], 1)] = w;
+    }
+}
+
 __global__ void sq_kernel(const double* in, double* out, int n) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = SQ(in[i]);
@@ -162,6 +188,12 @@ int launch_step(const nppsim_state_t* st, const int8_t* hor, const int8_t* jump,
     g_launches++;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_fail(e, "step_kernel launch");
+    if (st->warp_order && st->warp_cost) {
+        sched_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(st->warp_order, st->warp_cost, (st->n_envs + 31) / 32);
+        g_launches++;
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return cuda_fail(e, "sched_kernel launch");
+    }
     return 0;
 }
 

@@ -18,12 +18,16 @@ __device__ unsigned long long g_phase_cycles[16];      // [0..10] cycles per pha
 __device__ unsigned long long g_warp_cycles[1 << 16];      // per warp: kernel duration of the last launch
 __device__ unsigned long long g_warp_phase[1 << 16][4];   // per warp: cycles in entities / sweep / closest / post of the last launch
 #define PH_COUNT(k) atomicAdd(&g_phase_cycles[k], 1ULL)
+#define PH_T0 long long _q0 = clock64();
+#define PH_ACC(k) { long long _q1 = clock64(); if ((threadIdx.x & 31) == 0) atomicAdd(&g_phase_cycles[k], (unsigned long long)(_q1 - _q0)); _q0 = _q1; }
 #define PH_BEGIN long long _ph_t = clock64();
 #define PH_MARK(k) { long long _t2 = clock64(); if ((threadIdx.x & 31) == (__ffs(__activemask()) - 1)) { atomicAdd(&g_phase_cycles[k], (unsigned long long)(_t2 - _ph_t)); int _w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; int _b = (k) <= 3 ? 0 : ((k) == 5 ? 1 : ((k) == 6 ? 2 : (((k) == 9 || (k) == 10) ? 3 : -1))); if (_b >= 0 && _w < (1 << 16)) g_warp_phase[_w][_b] += (unsigned long long)(_t2 - _ph_t); } _ph_t = _t2; }
 #else
 #define PH_BEGIN
 #define PH_MARK(k)
 #define PH_COUNT(k)
+#define PH_T0
+#define PH_ACC(k)
 #endif
 
 #define POOL_CAP 256                 // 32 lanes x at most 8 segments per cell per round
@@ -39,61 +43,92 @@ struct WarpPool {
     uint32_t lseg[32][POOL_LCAP];   // per-lane copy of the segments gathered for the current substep (ninja.py:282-285)
 };
 
-// ---- per-lane iterator over the cells of a query box (SpatialSegmentIndex.query_region order) ----------
-struct CellIter { int cx1, cy0, cy1, xc, yc; double min_x, min_y, max_x, max_y; bool more; };
-DEV void cell_iter_init(CellIter& it, bool active, double x1, double y1, double x2, double y2) {
-    it.min_x = (x2 < x1) ? x2 : x1; it.min_y = (y2 < y1) ? y2 : y1;
-    it.max_x = (x2 > x1) ? x2 : x1; it.max_y = (y2 > y1) ? y2 : y1;
-    it.xc = clampi(floordiv24(it.min_x), 0, 43); it.cx1 = clampi(floordiv24(it.max_x), 0, 43);
-    it.cy0 = clampi(floordiv24(it.min_y), 0, 24); it.cy1 = clampi(floordiv24(it.max_y), 0, 24);
-    it.yc = it.cy0;
-    it.more = active;
+// ---- gather: the segments of a query box, per lane, in SpatialSegmentIndex.query_region order -----------
+// (utils/spatial_segment_index.py:112-158: cells x-major / y-inner, a cell is skipped when absent or when
+// its AABB misses the box, segments in cell order).  Each lane fills its own list wp.lseg[lane][0..n); no
+// warp-level step is needed here, and the loads of two cells are issued before anything waits on them (a box
+// is at most 2 x 2 cells unless the ninja moves more than a cell per frame).  Returns n, or -1 when the list
+// does not fit (callers then run the literal per-thread version).
+DEV bool cell_pass(uint32_t hdr, double min_x, double min_y, double max_x, double max_y) {
+    if (!(hdr & 15)) return false;
+    const double bx0 = u12((hdr >> 4) & 127), by0 = u12((hdr >> 11) & 63), bx1 = u12((hdr >> 17) & 127), by1 = u12((hdr >> 24) & 63);
+    return !(max_x < bx0 || min_x > bx1 || max_y < by0 || min_y > by1);                    // _bounds_intersect :175-188
 }
-// next cell that is present in cell_data and whose AABB meets the query; returns its segment count (0 = exhausted)
-DEV int cell_iter_next(CellIter& it, const Ctx& c, int& cell) {
-    #pragma unroll 1
-    while (it.xc <= it.cx1) {
-        int xc = it.xc, yc = it.yc;
-        if (++it.yc > it.cy1) { it.yc = it.cy0; it.xc++; }
-        int ci = xc * NPP_NCY + yc;
-        uint32_t hdr = __ldg(c.cell_hdr + ci);
-        int cnt = hdr & 15;
-        if (!cnt) continue;
-        double bx0 = u12((hdr >> 4) & 127), by0 = u12((hdr >> 11) & 63);
-        double bx1 = u12((hdr >> 17) & 127), by1 = u12((hdr >> 24) & 63);
-        if (it.max_x < bx0 || it.min_x > bx1 || it.max_y < by0 || it.min_y > by1) continue;
-        cell = ci;
-        return cnt;
+DEV int list_append(uint32_t* dst, int n, const uint4& a, const uint4& b, int cnt) {
+    if (n < 0 || n + cnt > POOL_LCAP) return -1;
+    dst[n] = a.x;
+    if (cnt > 1) dst[n + 1] = a.y;
+    if (cnt > 2) dst[n + 2] = a.z;
+    if (cnt > 3) dst[n + 3] = a.w;
+    if (cnt > 4) dst[n + 4] = b.x;
+    if (cnt > 5) dst[n + 5] = b.y;
+    if (cnt > 6) dst[n + 6] = b.z;
+    if (cnt > 7) dst[n + 7] = b.w;
+    return n + cnt;
+}
+DEV int gather_list(WarpPool& wp, const Ctx& c, bool active, double x1, double y1, double x2, double y2) {
+    int n = 0;
+    PH_T0
+    if (active) {
+        const double min_x = (x2 < x1) ? x2 : x1, min_y = (y2 < y1) ? y2 : y1;
+        const double max_x = (x2 > x1) ? x2 : x1, max_y = (y2 > y1) ? y2 : y1;
+        const int cx0 = clampi(floordiv24(min_x), 0, 43), cx1 = clampi(floordiv24(max_x), 0, 43);
+        const int cy0 = clampi(floordiv24(min_y), 0, 24), cy1 = clampi(floordiv24(max_y), 0, 24);
+        uint32_t* dst = wp.lseg[threadIdx.x & 31];
+        const uint4 z = make_uint4(0, 0, 0, 0);
+        #pragma unroll 1
+        for (int xc = cx0; xc <= cx1; xc++) {
+            #pragma unroll 1
+            for (int yc = cy0; yc <= cy1; yc += 2) {
+                const int ci = xc * NPP_NCY + yc;
+                const uint32_t h0 = __ldg(c.cell_hdr + ci), h1 = (yc < cy1) ? __ldg(c.cell_hdr + ci + 1) : 0u;
+                const bool p0 = cell_pass(h0, min_x, min_y, max_x, max_y), p1 = cell_pass(h1, min_x, min_y, max_x, max_y);
+                const uint4* sp = reinterpret_cast<const uint4*>(c.segs + ci * NPP_SEGS_PER_CELL);
+                uint4 a0 = z, b0 = z, a1 = z, b1 = z;
+                if (p0) { a0 = __ldg(sp); if ((h0 & 15) > 4) b0 = __ldg(sp + 1); }
+                if (p1) { a1 = __ldg(sp + 2); if ((h1 & 15) > 4) b1 = __ldg(sp + 3); }
+                if (p0) n = list_append(dst, n, a0, b0, h0 & 15);
+                if (p1) n = list_append(dst, n, a1, b1, h1 & 15);
+            }
+        }
     }
-    it.more = false;
-    return 0;
+    __syncwarp();
+    PH_ACC(11)
+    return n;
 }
 
-// All 32 lanes must call this together.  item(j, seg, owner) fills wp.res/ra/rb/aux[j];
-// fold(off, cnt) lets an owner consume its items [off, off+cnt) in order and returns false to stop early.
+// ---- evaluate + fold: the lists of all 32 lanes as one flat queue ---------------------------------------------
+// All 32 lanes call this together; lane l contributes its first n entries of wp.lseg[l] (n <= 0: none).
+// item(j, seg, owner) fills wp.res/ra/rb/aux[j] for queue slot j; fold(off, cnt) lets an owner consume its
+// slots [off, off+cnt) in list order and returns false to stop early.  The queue holds POOL_CAP slots, so
+// more than that (never observed: it needs 8+ segments on average around every ninja of the warp) takes
+// several passes; an owner's fold state lives in its caller's variables and carries over.
 template <class ItemF, class FoldF>
-DEV void pooled_query(WarpPool& wp, const Ctx& c, bool active, double x1, double y1, double x2, double y2, ItemF&& item, FoldF&& fold) {
+DEV void pooled_eval(WarpPool& wp, int n, ItemF&& item, FoldF&& fold) {
     const int lane = threadIdx.x & 31;
-    CellIter it;
-    cell_iter_init(it, active, x1, y1, x2, y2);
-    #pragma unroll 1
-    while (__any_sync(FULL_MASK, it.more)) {
-        int cell = 0, cnt = 0;
-        if (it.more) cnt = cell_iter_next(it, c, cell);
-        int incl = cnt;
+    const int cnt = n > 0 ? n : 0;
+    PH_T0
+    int incl = cnt;
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) { int v = __shfl_up_sync(FULL_MASK, incl, d); if (lane >= d) incl += v; }
-        const int off = incl - cnt;
-        const int total = __shfl_sync(FULL_MASK, incl, 31);
-        if (total == 0) continue;
+    for (int d = 1; d < 32; d <<= 1) { int v = __shfl_up_sync(FULL_MASK, incl, d); if (lane >= d) incl += v; }
+    const int off = incl - cnt;
+    const int total = __shfl_sync(FULL_MASK, incl, 31);
+    bool go = true;
+    #pragma unroll 1
+    for (int base = 0; base < total; base += POOL_CAP) {
+        const int lo = max(off, base), hi = min(off + cnt, base + POOL_CAP);
         #pragma unroll 1
-        for (int k = 0; k < cnt; k++) { wp.seg[off + k] = __ldg(c.segs + cell * NPP_SEGS_PER_CELL + k); wp.own[off + k] = (uint8_t)lane; }
+        for (int j = lo; j < hi; j++) { wp.seg[j - base] = wp.lseg[lane][j - off]; wp.own[j - base] = (uint8_t)lane; }
         __syncwarp();
+        PH_ACC(12)
+        const int m = min(total - base, POOL_CAP);
         #pragma unroll 1
-        for (int j = lane; j < total; j += 32) item(j, wp.seg[j], (int)wp.own[j]);
+        for (int j = lane; j < m; j += 32) item(j, wp.seg[j], (int)wp.own[j]);
         __syncwarp();
-        if (cnt > 0 && !fold(off, cnt)) it.more = false;
+        PH_ACC(13)
+        if (go && hi > lo) go = fold(lo - base, hi - lo);
         __syncwarp();
+        PH_ACC(14)
     }
 }
 
@@ -203,6 +238,11 @@ DEV double seg_toi_guarded(uint32_t s, double xpos, double ypos, double dx, doub
 // ---- pooled sweep_circle_vs_tiles (physics.py:104-128), ninja radius 5 -----------------------------------
 // The reference returns 0 as soon as a segment reports exactly 0, else the minimum; the owner's fold
 // walks its items in list order with the same early exit.
+// literal per-thread sweep (out of line: only for a box whose segment list does not fit the per-lane cache)
+__device__ __noinline__ double sweep_exact(const uint32_t* cell_hdr, const uint32_t* segs, double xpos_old, double ypos_old, double dx, double dy, double radius) {
+    Ctx c; c.cell_hdr = cell_hdr; c.segs = segs;
+    return sweep_circle_vs_tiles(c, xpos_old, ypos_old, dx, dy, radius);
+}
 DEV double pooled_sweep(WarpPool& wp, const Ctx& c, bool active, double xpos_old, double ypos_old, double dx, double dy) {
     const int lane = threadIdx.x & 31;
     const double radius = NINJA_RADIUS * 0.5;
@@ -213,9 +253,10 @@ DEV double pooled_sweep(WarpPool& wp, const Ctx& c, bool active, double xpos_old
     double x2 = (xpos_old > xpos_new ? xpos_old : xpos_new) + width;
     double y2 = (ypos_old > ypos_new ? ypos_old : ypos_new) + width;
     wp.par[0][lane] = xpos_old; wp.par[1][lane] = ypos_old; wp.par[2][lane] = dx; wp.par[3][lane] = dy; wp.par[4][lane] = dx * dx + dy * dy;
+    const int n = gather_list(wp, c, active, x1, y1, x2, y2);
     __syncwarp();
     double shortest = 1;
-    pooled_query(wp, c, active, x1, y1, x2, y2,
+    pooled_eval(wp, n,
         [&](int j, uint32_t s, int o) {
             wp.res[j] = seg_toi_guarded(s, wp.par[0][o], wp.par[1][o], wp.par[2][o], wp.par[3][o], wp.par[4][o], radius, radius * radius);
         },
@@ -228,6 +269,7 @@ DEV double pooled_sweep(WarpPool& wp, const Ctx& c, bool active, double xpos_old
             }
             return true;
         });
+    if (n < 0) shortest = sweep_exact(c.cell_hdr, c.segs, xpos_old, ypos_old, dx, dy, radius);
     return shortest;
 }
 
@@ -308,19 +350,17 @@ DEV bool closest_item(uint32_t s, double x, double y, double& d2, double& a, dou
     return closest_eval(seg_decode(s), x, y, d2, a, b, r, ix);
 }
 
-// First iteration of the depenetration loop: pooled over the warp.  Besides the result it leaves the
-// owner's gathered segment list (reference order) in wp.lseg[lane][0..nseg) for the later iterations;
-// nseg = -1 when the list does not fit.
-DEV int pooled_closest_point(WarpPool& wp, const Ctx& c, bool active, double gx1, double gy1, double gx2, double gy2,
-                             double xpos, double ypos, double& pa, double& pb, int& nseg) {
+// One closest-point query per participating lane, pooled over the warp, on the lists in wp.lseg (n entries each,
+// n = -1: list overflow, the lane runs the literal version).  (gx..) is the box the list was gathered from.
+DEV int pooled_list_closest(WarpPool& wp, const Ctx& c, bool active, int n, double gx1, double gy1, double gx2, double gy2,
+                            double xpos, double ypos, double& pa, double& pb) {
     const int lane = threadIdx.x & 31;
     wp.par[0][lane] = xpos; wp.par[1][lane] = ypos;
     __syncwarp();
     double best = __longlong_as_double(0x7ff0000000000000LL), ba = 0, bb = 0;
     int result = 0;
     bool uncertain = false, bix = false;
-    nseg = 0;
-    pooled_query(wp, c, active, gx1, gy1, gx2, gy2,
+    pooled_eval(wp, active ? n : 0,
         [&](int j, uint32_t s, int o) {
             double d2, a, b; int r; bool ix;
             if (!closest_item(s, wp.par[0][o], wp.par[1][o], d2, a, b, r, ix)) { wp.aux[j] = 2; return; }
@@ -329,38 +369,23 @@ DEV int pooled_closest_point(WarpPool& wp, const Ctx& c, bool active, double gx1
         [&](int off, int cnt) {
             #pragma unroll 1
             for (int k = 0; k < cnt; k++) {
-                if (nseg >= 0) { if (nseg < POOL_LCAP) wp.lseg[lane][nseg++] = wp.seg[off + k]; else nseg = -1; }
                 int ax = wp.aux[off + k];
                 if (ax == 2) continue;                                   // AABB-rejected
                 closest_fold(wp.res[off + k], wp.ra[off + k], wp.rb[off + k], (ax & 1) ? -1 : 1, (ax & 4) != 0, best, ba, bb, result, bix, uncertain);
             }
             return true;
         });
-    if (uncertain) return closest_point_exact(c.cell_hdr, c.segs, gx1, gy1, gx2, gy2, xpos, ypos, pa, pb);
+    if (active && (uncertain || n < 0)) return closest_point_exact(c.cell_hdr, c.segs, gx1, gy1, gx2, gy2, xpos, ypos, pa, pb);
     pa = ba; pb = bb;
     return result;
 }
-// Later iterations: the owner walks its cached list itself (few lanes are still iterating by then, and a
-// pathological corner can take all 32 iterations -- a pooled pass per iteration made such warps 8x slower
-// than the median, profiles/r01_c).
-DEV int cached_closest_point(const WarpPool& wp, const Ctx& c, int nseg, double gx1, double gy1, double gx2, double gy2,
-                             double xpos, double ypos, double& pa, double& pb) {
-    if (nseg < 0) return closest_point_exact(c.cell_hdr, c.segs, gx1, gy1, gx2, gy2, xpos, ypos, pa, pb);
-    const int lane = threadIdx.x & 31;
-    double best = __longlong_as_double(0x7ff0000000000000LL), ba = 0, bb = 0;
-    int result = 0;
-    bool uncertain = false, bix = false;
-    #pragma unroll 1
-    for (int k = 0; k < nseg; k++) {
-        double d2, a, b; int r; bool ix;
-        if (!closest_item(wp.lseg[lane][k], xpos, ypos, d2, a, b, r, ix)) continue;
-        closest_fold(d2, a, b, r, ix, best, ba, bb, result, bix, uncertain);
-    }
-    if (uncertain) return closest_point_exact(c.cell_hdr, c.segs, gx1, gy1, gx2, gy2, xpos, ypos, pa, pb);
-    pa = ba; pb = bb;
-    return result;
+// First iteration of the depenetration loop: gathers each lane's segment list around the post-sweep
+// position (ninja.py:282-285; it stays in wp.lseg[lane][0..nseg) for the later iterations) and queries it.
+DEV int pooled_closest_point(WarpPool& wp, const Ctx& c, bool active, double gx1, double gy1, double gx2, double gy2,
+                             double xpos, double ypos, double& pa, double& pb, int& nseg) {
+    nseg = gather_list(wp, c, active, gx1, gy1, gx2, gy2);
+    return pooled_list_closest(wp, c, active, nseg, gx1, gy1, gx2, gy2, xpos, ypos, pa, pb);
 }
-
 // Iterations 2..31 of one owner lane `o`, served by the whole warp: lane k evaluates the owner's k-th
 // cached segment (decoded once per owner by the caller: `g`).  With exact squares everywhere the reference's strict-< scan picks the first minimum,
 // which is a warp min + ballot; when some square is flagged inexact the owner folds the items in list
@@ -387,7 +412,6 @@ DEV int warp_closest_point(WarpPool& wp, const Ctx& c, int o, int ns, const SegC
     if (lane < ns) ok = closest_eval(g, x, y, d2, a, b, r, ix);
     if (!ok) d2 = inf;
     int result = 0;
-    if (lane == o) PH_COUNT(11);
     if (__ballot_sync(FULL_MASK, ok && ix) == 0) {
         const double mn = warp_min_f64(d2);
         const unsigned eq = __ballot_sync(FULL_MASK, ok && d2 == mn);
@@ -397,7 +421,6 @@ DEV int warp_closest_point(WarpPool& wp, const Ctx& c, int o, int ns, const SegC
         }
         return result;
     }
-    if (lane == o) PH_COUNT(12);
     wp.res[lane] = d2; wp.ra[lane] = a; wp.rb[lane] = b; wp.aux[lane] = (uint8_t)(!ok ? 2 : ((r < 0 ? 1 : 0) | (ix ? 4 : 0)));
     __syncwarp();
     if (lane == o) {
@@ -425,7 +448,9 @@ DEV void pooled_wall_test(WarpPool& wp, const Ctx& c, bool active, double xpos, 
     wp.par[0][lane] = xpos; wp.par[1][lane] = ypos;
     __syncwarp();
     uncertain = false;
-    pooled_query(wp, c, active, xpos - rad, ypos - rad, xpos + rad, ypos + rad,
+    const int n = gather_list(wp, c, active, xpos - rad, ypos - rad, xpos + rad, ypos + rad);
+    if (n < 0) uncertain = true;                                         // list overflow: the caller's literal version
+    pooled_eval(wp, n,
         [&](int j, uint32_t s, int o) {
             const double x = wp.par[0][o], y = wp.par[1][o];
             bool back; double a, b;

@@ -42,7 +42,7 @@ __global__ void coop(double* out, long long* cyc, double x0, double y0) {
     #pragma unroll 1
     for (int i = 0; i < K; i++) {
         double a = 0, b = 0;
-        int r = warp_closest_point(wp, c, 0, lane < ns, g, 0, 0, 0, 0, x, y, a, b);
+        int r = warp_closest_point(wp, c, 0, ns, g, 0, 0, 0, 0, x, y, a, b);
         acc += a + b + r; x += acc * 1e-300;
     }
     long long t1 = clock64();

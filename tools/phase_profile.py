@@ -40,7 +40,7 @@ tot = v[15]
 print(f"envs {n_envs}, warps {nw}, launches {K}; per-warp cycles per launch: {tot / nw / K:,.0f}")
 for k in sorted(names):
     print(f"  {names[k]:34s} {v[k] / nw / K:12,.0f} cycles/warp/launch  {100 * v[k] / tot:5.1f}%")
-print(f"  cooperative depenetration iterations {v[11] / K:,.0f} per launch; flagged-square folds {v[12] / K:,.0f}; cycles per iteration: closest point {v[13] / max(v[11], 1):,.0f}, push {v[14] / max(v[11], 1):,.0f}")
+print(f"  segment queries, cycles/warp/launch: gather {v[11] / nw / K:,.0f}, scan+queue {v[12] / nw / K:,.0f}, evaluate {v[13] / nw / K:,.0f}, fold {v[14] / nw / K:,.0f}")
 print(f"  {'(load/store/loop overhead)':34s} {(tot - v[:11].sum()) / nw / K:12,.0f}  {100 * (tot - v[:11].sum()) / tot:5.1f}%")
 
 # ---- distribution over warps of the last launch
