@@ -57,6 +57,7 @@ DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
     PH_BEGIN
     double time = pooled_sweep(wp, c, alive, n.f[F_XPOS_OLD], n.f[F_YPOS_OLD], dx, dy);
     PH_MARK(5)
+    NPP_BLOCK_SYNC();
     double xpos = n.f[F_XPOS_OLD] + time * dx;       // recomputed even when time == 1 (not a no-op in fp)
     double ypos = n.f[F_YPOS_OLD] + time * dy;
     // segments are gathered once, around the post-sweep position (ninja.py:282-285)
@@ -101,6 +102,7 @@ DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
     double a0 = 0, b0 = 0; int nseg = 0;
     int result0 = pooled_closest_point(wp, c, alive, gx1, gy1, gx2, gy2, xpos, ypos, a0, b0, nseg);
     bool need = alive && depen(result0, a0, b0);
+    NPP_BLOCK_SYNC();
     if (__any_sync(FULL_MASK, need)) {                      // iteration 1: 5 % of lanes, i.e. most warps -> pooled again
         double a = 0, b = 0;
         int result = pooled_list_closest(wp, c, need, nseg, gx1, gy1, gx2, gy2, xpos, ypos, a, b);
@@ -168,6 +170,7 @@ DEV void ninja_post_collision(Nin& n, Ctx& c, WarpPool& wp, bool alive) {
         commit_pending_doors(c);
     }
     PH_MARK(9)
+    NPP_BLOCK_SYNC();
     const double wall_entities = wall_normal;
     bool uncertain;
     pooled_wall_test(wp, c, alive, n.f[F_XPOS], n.f[F_YPOS], wall_normal, uncertain);
@@ -398,14 +401,16 @@ DEV void sim_tick(Nin& n, Ctx& c, WarpPool& wp, bool run, int hor_input, int jum
     // substeps would repeat it verbatim: they are skipped (typical: free flight, or resting after substep 2).
     bool sub = alive;
     #pragma unroll 1
-    for (int s = 0; s < 4 && __any_sync(FULL_MASK, sub); s++) {
+    for (int s = 0; s < 4 && NPP_BLOCK_ANY(sub); s++) {
         if (HAS_ANY(NPP_PHYS_MASK) && sub && phys) ninja_collide_vs_objects(n, c, gx, gy);
         bool idle = ninja_collide_vs_tiles(n, c, wp, sub);
         if (idle && !phys) sub = false;
     }
     PH_MARK(4)
+    NPP_BLOCK_SYNC();
     ninja_post_collision(n, c, wp, alive);
     PH_MARK(7)
+    NPP_BLOCK_SYNC();
     if (run && n.i[I_STATE] != 9) ninja_think(n, c, hor_input, jump_input);
     PH_MARK(8)
 }

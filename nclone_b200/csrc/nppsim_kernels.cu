@@ -106,6 +106,7 @@ __global__ void __launch_bounds__(128) reset_kernel(nppsim_state_t st, const uin
 #ifndef STEP_BLOCKS_PER_SM
 #define STEP_BLOCKS_PER_SM 1
 #endif
+#define STEP_SMEM ((STEP_BLOCK / 32) * sizeof(WarpPool))
 #define NPP_MOVE_MASK ((1u << NPP_K_DRONE_ZAP) | (1u << NPP_K_MINI_DRONE) | (1u << NPP_K_BOUNCE) | (1u << NPP_K_THWUMP))
 #define NPP_THINK_MASK ((1u << NPP_K_DOOR_REGULAR) | (1u << NPP_K_THWUMP) | (1u << NPP_K_DEATH_BALL) | (1u << NPP_K_SHWUMP))
 #define NPP_PHYS_MASK ((1u << NPP_K_ONE_WAY) | (1u << NPP_K_BOUNCE) | (1u << NPP_K_THWUMP) | (1u << NPP_K_SHWUMP))
@@ -178,13 +179,15 @@ int launch_step(const nppsim_state_t* st, const int8_t* hor, const int8_t* jump,
     static const bool carveout_set = [] {
         cudaFuncSetAttribute(sim_basic::step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         cudaFuncSetAttribute(sim_full::step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        cudaFuncSetAttribute(sim_basic::step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)STEP_SMEM);
+        cudaFuncSetAttribute(sim_full::step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)STEP_SMEM);
         return true;
     }();
     (void)carveout_set;
     // kind_mask == 0: census unknown (older callers) -> the full kernel
     const bool basic = st->kind_mask != 0 && (st->kind_mask & ~NPP_BASIC_MASK) == 0 && !g_force_full;
-    if (basic) sim_basic::step_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(*st, hor, jump, actions, input_ticks, n_ticks, tick_limit, stop_on_terminal, frames_executed);
-    else sim_full::step_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(*st, hor, jump, actions, input_ticks, n_ticks, tick_limit, stop_on_terminal, frames_executed);
+    if (basic) sim_basic::step_kernel<<<grid, block, STEP_SMEM, (cudaStream_t)stream>>>(*st, hor, jump, actions, input_ticks, n_ticks, tick_limit, stop_on_terminal, frames_executed);
+    else sim_full::step_kernel<<<grid, block, STEP_SMEM, (cudaStream_t)stream>>>(*st, hor, jump, actions, input_ticks, n_ticks, tick_limit, stop_on_terminal, frames_executed);
     g_launches++;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_fail(e, "step_kernel launch");
