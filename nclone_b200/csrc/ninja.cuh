@@ -74,10 +74,10 @@ DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
         }
         double dist_sq = dx * dx + dy * dy;
         if (dist_sq < 1e-16) return false;
-        double dist = sqrt(dist_sq);
+        double dist = SQRT(dist_sq);
         double depen_len = NINJA_RADIUS - dist * result;
         if (depen_len < 0.0000001) return false;
-        double inv_dist = 1.0 / dist;
+        double inv_dist = DIV(1.0, dist);
         double norm_dx = dx * inv_dist, norm_dy = dy * inv_dist;
         double depen_x = norm_dx * depen_len, depen_y = norm_dy * depen_len;
         pushed = true;
@@ -179,12 +179,12 @@ DEV void ninja_post_collision(Nin& n, Ctx& c, WarpPool& wp, bool alive) {
     if (uncertain) wall_normal = wall_terms_exact(c.cell_hdr, c.segs, n.f[F_XPOS], n.f[F_YPOS], wall_entities);
     n.i[I_AIRBORN_OLD] = n.i[I_AIRBORN];
     n.i[I_AIRBORN] = 1; n.i[I_WALLED] = 0;
-    if (wall_normal != 0) { n.i[I_WALLED] = 1; n.f[F_WALL_NORMAL] = wall_normal / fabs(wall_normal); }
+    if (wall_normal != 0) { n.i[I_WALLED] = 1; n.f[F_WALL_NORMAL] = DIV(wall_normal, fabs(wall_normal)); }
     if (n.i[I_FLOOR_COUNT] > 0) {
         n.i[I_AIRBORN] = 0;
-        double floor_scalar = sqrt(SQ(n.f[F_FLOOR_NX]) + SQ(n.f[F_FLOOR_NY]));
+        double floor_scalar = SQRT(SQ(n.f[F_FLOOR_NX]) + SQ(n.f[F_FLOOR_NY]));
         if (floor_scalar == 0) { n.f[F_FNX] = 0; n.f[F_FNY] = -1; }
-        else { n.f[F_FNX] = n.f[F_FLOOR_NX] / floor_scalar; n.f[F_FNY] = n.f[F_FLOOR_NY] / floor_scalar; }
+        else { n.f[F_FNX] = DIV(n.f[F_FLOOR_NX], floor_scalar); n.f[F_FNY] = DIV(n.f[F_FLOOR_NY], floor_scalar); }
         if (n.i[I_STATE] != 8 && n.i[I_AIRBORN_OLD]) {
             double impact_vel = -(n.f[F_FNX] * n.f[F_XSPEED_OLD] + n.f[F_FNY] * n.f[F_YSPEED_OLD]);
             if (impact_vel > MAX_SURVIVABLE_IMPACT - 4.0 / 3 * fabs(n.f[F_FNY])) {
@@ -198,10 +198,10 @@ DEV void ninja_post_collision(Nin& n, Ctx& c, WarpPool& wp, bool alive) {
     if (!n.i[I_AIRBORN]) n.i[I_CONSEC_FLOOR] += 1; else n.i[I_CONSEC_FLOOR] = 0;
     if (n.i[I_WALLED]) n.i[I_CONSEC_WALL] += 1; else n.i[I_CONSEC_WALL] = 0;
     if (n.i[I_CEILING_COUNT] > 0) {
-        double ceiling_scalar = sqrt(SQ(n.f[F_CEIL_NX]) + SQ(n.f[F_CEIL_NY]));
+        double ceiling_scalar = SQRT(SQ(n.f[F_CEIL_NX]) + SQ(n.f[F_CEIL_NY]));
         double cnx, cny;
         if (ceiling_scalar == 0) { cnx = 0; cny = 1; }
-        else { cnx = n.f[F_CEIL_NX] / ceiling_scalar; cny = n.f[F_CEIL_NY] / ceiling_scalar; }
+        else { cnx = DIV(n.f[F_CEIL_NX], ceiling_scalar); cny = DIV(n.f[F_CEIL_NY], ceiling_scalar); }
         GF(c, F_CNX) = cnx; GF(c, F_CNY) = cny;
         if (n.i[I_STATE] != 8) {
             double impact_vel = -(cnx * n.f[F_XSPEED_OLD] + cny * n.f[F_YSPEED_OLD]);
@@ -213,7 +213,7 @@ DEV void ninja_post_collision(Nin& n, Ctx& c, WarpPool& wp, bool alive) {
         }
     }
     if (n.i[I_CRUSHABLE] && n.f[F_CRUSH_LEN] > 0) {
-        if (sqrt(SQ(n.f[F_XCRUSH]) + SQ(n.f[F_YCRUSH])) / n.f[F_CRUSH_LEN] < MIN_SURVIVABLE_CRUSHING)
+        if (DIV(SQRT(SQ(n.f[F_XCRUSH]) + SQ(n.f[F_YCRUSH])), n.f[F_CRUSH_LEN]) < MIN_SURVIVABLE_CRUSHING)
             ninja_kill(n, c, n.f[F_XPOS], n.f[F_YPOS], 0, 0, 0);
     }
 }
@@ -303,11 +303,11 @@ DEV void ninja_think_body(Nin& n, const Ctx& c, const int hor_input, const int j
                 if (hor_input * projection * n.f[F_XSPEED] > 0) { n.i[I_STATE] = 1; return; }
                 if (projection < 0.1 && n.f[F_FNX] == 0) { n.i[I_STATE] = 0; return; }
                 if (n.f[F_YSPEED] < 0 && n.f[F_FNX] != 0) {
-                    double speed_scalar = sqrt(SQ(n.f[F_XSPEED]) + SQ(n.f[F_YSPEED]));
+                    double speed_scalar = SQRT(SQ(n.f[F_XSPEED]) + SQ(n.f[F_YSPEED]));
                     double fric_force = fabs(n.f[F_XSPEED] * (1 - FRICTION_GROUND) * n.f[F_FNY]);
                     double fric_force2 = speed_scalar - fric_force * SQ(n.f[F_FNY]);
-                    n.f[F_XSPEED] = n.f[F_XSPEED] / speed_scalar * fric_force2;
-                    n.f[F_YSPEED] = n.f[F_YSPEED] / speed_scalar * fric_force2;
+                    n.f[F_XSPEED] = DIV(n.f[F_XSPEED], speed_scalar) * fric_force2;
+                    n.f[F_YSPEED] = DIV(n.f[F_YSPEED], speed_scalar) * fric_force2;
                     return;
                 }
                 n.f[F_XSPEED] *= FRICTION_GROUND;

@@ -153,7 +153,7 @@ __device__ __noinline__ double toi_circle_exact(double dx, double dy, double dot
     double dist_sq = SQ(dx) + SQ(dy);
     if (dist_sq - rr > 0) {
         double radicand = SQ(dot_prod) - vel_sq * (dist_sq - rr);
-        if (vel_sq > 0.0001 && dot_prod < 0 && radicand >= 0) return (-dot_prod - sqrt(radicand)) / vel_sq;
+        if (vel_sq > 0.0001 && dot_prod < 0 && radicand >= 0) return DIV(-dot_prod - SQRT(radicand), vel_sq);
         return 1;
     }
     return 0;
@@ -176,7 +176,7 @@ DEV double toi_circle_guarded(double xpos, double ypos, double vx, double vy, do
             const double E = 1e-13 * (d2 + vel_a * (m + rr));
             if (R < -E) return 1;                         // radicand certainly negative
             if (R > E) {
-                const double t_lo = (-dot_prod - sqrt(R + E)) / vel_a;   // below the true root
+                const double t_lo = DIV(-dot_prod - SQRT(R + E), vel_a);   // below the true root
                 if (t_lo > 1.000000001) return 1;         // certainly later than this frame
             }
         }
@@ -201,7 +201,7 @@ DEV double toi_lineseg_int(uint32_t s, double xpos, double ypos, double dx, doub
     if (fabs(normal_proj) >= radius) {
         double dir = dx * ny - dy * nx;
         if (dir * normal_proj < 0) {
-            double q = (fabs(normal_proj) - radius) / fabs(dir);
+            double q = DIV(fabs(normal_proj) - radius, fabs(dir));
             double t = (1 < q) ? 1 : q;
             double hor_proj2 = hor_proj + t * (dx * nx + dy * ny);
             if (0 <= hor_proj2 && hor_proj2 <= seg_len) return t;
@@ -222,10 +222,10 @@ __device__ __noinline__ double toi_arc_exact(double xpos, double ypos, double vx
     double t = 1;
     if (dist_sq > rr1) {
         double radicand = SQ(dot_prod) - vel_sq * (dist_sq - rr1);
-        if (vel_sq > 0.0001 && dot_prod < 0 && radicand >= 0) t = (-dot_prod - sqrt(radicand)) / vel_sq;
+        if (vel_sq > 0.0001 && dot_prod < 0 && radicand >= 0) t = DIV(-dot_prod - SQRT(radicand), vel_sq);
     } else if (dist_sq < rr2) {
         double radicand = SQ(dot_prod) - vel_sq * (dist_sq - rr2);
-        if (vel_sq > 0.0001) { double q = (-dot_prod + sqrt(radicand)) / vel_sq; t = (1 < q) ? 1 : q; }
+        if (vel_sq > 0.0001) { double q = DIV(-dot_prod + SQRT(radicand), vel_sq); t = (1 < q) ? 1 : q; }
     } else {
         t = 0;
     }
@@ -348,8 +348,8 @@ DEV bool closest_eval(const SegC& g, double x, double y, double& d2, double& a, 
     } else {                                                                 // entities.py:127-157
         back = false;
         if (dx * g.px > 0 && dy * g.py > 0) {
-            double dist = sqrt(SQ(dx) + SQ(dy));
-            a = g.x1 + 24.0 * dx / dist; b = g.y1 + 24.0 * dy / dist;
+            double dist = SQRT(SQ(dx) + SQ(dy));
+            a = g.x1 + DIV(24.0 * dx, dist); b = g.y1 + DIV(24.0 * dy, dist);
             back = (g.lensq != 0) ? (dist < 24.0) : (dist > 24.0);
         } else if (dx * g.px > dy * g.py) { a = g.x1 + 24.0 * g.px; b = g.y1; }
         else { a = g.x1; b = g.y1 + 24.0 * g.py; }
@@ -473,9 +473,9 @@ DEV void pooled_wall_test(WarpPool& wp, const Ctx& c, bool active, double xpos, 
             int code = 0;                                                // 0 no term, 1 term in res[j], 3 needs the exact path
             if (fabs(dy) < 0.00001) {
                 bool ix = false;
-                double dist = sqrt(sq_flag(dx, ix) + sq_flag(dy, ix));
+                double dist = SQRT(sq_flag(dx, ix) + sq_flag(dy, ix));
                 if (ix) code = 3;
-                else if (0 < dist && dist <= rad) { wp.res[j] = dx / dist; code = 1; }
+                else if (0 < dist && dist <= rad) { wp.res[j] = DIV(dx, dist); code = 1; }
             }
             wp.aux[j] = (uint8_t)code;
         },

@@ -123,7 +123,13 @@ POW2_FN double pow2_exact(double x) {
 #endif
 
 #ifdef __CUDACC__
+// Out of line on purpose: the step kernel is bound by instruction fetch, and ~60 call sites sharing one hot copy
+// (fast path included) beat 60 inlined copies.  Same for division and square root below (geom.cuh).
+#ifdef NPP_OUTLINE_SQ
+__device__ __noinline__ double SQ(double x) { return pow2_exact(x); }
+#else
 DEV double SQ(double x) { return pow2_exact(x); }
+#endif
 // x*x, and `inexact` set when that may differ from pow(x, 2.0) (x^2 within 1/64 ulp of a rounding
 // midpoint, ~3 % of inputs).  With the flag clear the product IS the reference's value, so callers can
 // run the literal reference expression on cheap squares and only redo flagged cases on the table path.
