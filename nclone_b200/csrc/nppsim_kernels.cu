@@ -131,23 +131,40 @@ namespace {
 __global__ void __launch_bounds__(1024) sched_kernel(int32_t* __restrict__ order, const uint32_t* __restrict__ cost, int nw) {
     __shared__ unsigned long long s_sum;
     __shared__ int s_cnt[3], s_pos[3];
+    const int lane = threadIdx.x & 31;
     if (threadIdx.x == 0) { s_sum = 0; s_cnt[0] = s_cnt[1] = s_cnt[2] = 0; }
     __syncthreads();
     unsigned long long loc = 0;
     for (int w = threadIdx.x; w < nw; w += blockDim.x) loc += cost[w];
-    atomicAdd(&s_sum, loc);
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) loc += __shfl_xor_sync(0xffffffffu, loc, d);
+    if (lane == 0) atomicAdd(&s_sum, loc);
     __syncthreads();
     const unsigned long long mean = s_sum / (unsigned long long)max(nw, 1);
-    for (int w = threadIdx.x; w < nw; w += blockDim.x) {
-        const unsigned long long v = cost[w];
-        atomicAdd(&s_cnt[v > 3 * mean ? 0 : (2 * v > 3 * mean ? 1 : 2)], 1);
+    const int rounds = (nw + blockDim.x - 1) / blockDim.x;
+    // warp-aggregated counting / placement: one shared-memory atomic per warp and class
+    for (int r = 0; r < rounds; r++) {
+        const int w = r * blockDim.x + threadIdx.x;
+        const unsigned long long v = w < nw ? cost[w] : 0;
+        const int cls = w < nw ? (v > 3 * mean ? 0 : (2 * v > 3 * mean ? 1 : 2)) : 3;
+#pragma unroll
+        for (int k = 0; k < 3; k++) { unsigned m = __ballot_sync(0xffffffffu, cls == k); if (lane == 0 && m) atomicAdd(&s_cnt[k], __popc(m)); }
     }
     __syncthreads();
     if (threadIdx.x == 0) { s_pos[0] = 0; s_pos[1] = s_cnt[0]; s_pos[2] = s_cnt[0] + s_cnt[1]; }
     __syncthreads();
-    for (int w = threadIdx.x; w < nw; w += blockDim.x) {
-        const unsigned long long v = cost[w];
-        order[atomicAdd(&s_pos[v > 3 * mean ? 0 : (2 * v > 3 * mean ? 1 : 2)], 1)] = w;
+    for (int r = 0; r < rounds; r++) {
+        const int w = r * blockDim.x + threadIdx.x;
+        const unsigned long long v = w < nw ? cost[w] : 0;
+        const int cls = w < nw ? (v > 3 * mean ? 0 : (2 * v > 3 * mean ? 1 : 2)) : 3;
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            unsigned m = __ballot_sync(0xffffffffu, cls == k);
+            int base = 0;
+            if (lane == 0 && m) base = atomicAdd(&s_pos[k], __popc(m));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (cls == k) order[base + __popc(m & ((1u << lane) - 1))] = w;
+        }
     }
 }
 

@@ -9,7 +9,12 @@ rows = list(csv.reader(io.StringIO(out)))
 hi = next(k for k, r in enumerate(rows) if r and r[0] == "Address")
 hdr = rows[hi]
 col = {h: k for k, h in enumerate(hdr)}
-ins = [r for r in rows[hi + 1:] if len(r) == len(hdr)]
+ins = []
+for r in rows[hi + 1:]:                      # first captured launch only
+    if r and r[0] in ("Kernel Name", "Address"):
+        break
+    if len(r) == len(hdr):
+        ins.append(r)
 tmp = tempfile.mkdtemp()
 subprocess.run(["cuobjdump", "-xelf", "all", so], cwd=tmp, capture_output=True)
 cubin = [f for f in os.listdir(tmp) if f.endswith(".cubin") and "map_compiler" not in f][0]
