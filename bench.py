@@ -292,7 +292,7 @@ def main():
                 "note": "branchy fp64 scalar code: bound by issue slots / fp64 latency, not HBM (DESIGN.md); frac is reported as required"}
 
     cpu = None
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and world == 1:          # rank 0 at N=1 only
         threads = os.cpu_count() or 1
         v, sample = cpu_baseline(arr, lens, threads, 12.0)
         cpu = {"value": v, "unit": "env-steps/s", "cores": threads, "kind": "port", "sample": sample}
