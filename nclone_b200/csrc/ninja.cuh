@@ -117,6 +117,7 @@ DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
         const SegC g = seg_decode(lane < ns ? wp.lseg[o][lane] : 0u);
         #pragma unroll 1
         for (int it = 2; it < 32; it++) {
+            if (lane == o) wp.coop++;
             double a = 0, b = 0; int result = 0;
 #ifdef NPP_PROFILE
             long long _c0 = clock64();

@@ -55,6 +55,7 @@ struct WarpPool {
     uint32_t seg[POOL_CAP];
     uint8_t own[POOL_CAP], aux[POOL_CAP];
     uint32_t lseg[32][POOL_LCAP];   // per-lane copy of the segments gathered for the current substep (ninja.py:282-285)
+    int coop;                       // cooperative depenetration iterations this launch: the warp's cost for longest-first scheduling
 };
 
 // ---- gather: the segments of a query box, per lane, in SpatialSegmentIndex.query_region order -----------
