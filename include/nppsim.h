@@ -128,6 +128,13 @@ int nppsim_step_host(const nppsim_state_t* st, const uint8_t* actions_host, uint
                      int32_t n_ticks, int32_t stop_on_terminal, double* pos_vel_host, int32_t* state_host,
                      void* stream);
 
+/* nppsim_observe: the two per-step observation primitives the env wrapper calls.
+ *   ninja_state_out  optional device float32 [N][40]: NPlayHeadless.get_ninja_state (nplay_headless.py:735-917);
+ *   mask_out         optional device uint8 [N][6]: Ninja.get_valid_action_mask (ninja.py:628-839), masking mode
+ *                    "hard"; path_dir optional device uint8 [N] = sim._path_straightness_direction
+ *                    (0 None, 1 "left", 2 "right", 3 "down"; NULL = None). */
+int nppsim_observe(const nppsim_state_t* st, const uint8_t* path_dir, uint8_t* mask_out, float* ninja_state_out, void* stream);
+
 /* Test hooks.  nppsim_debug_sq: out[i] = the device's SQ(in[i]) -- the reference's `x ** 2`, i.e. glibc
  * pow(x, 2.0) (ninja.py:412 and ~45 other sites) -- for cross-checking against the host libm.
  * nppsim_sq_mode: 1 = exact pow emulation (default build), 0 = x*x. */

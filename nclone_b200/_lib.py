@@ -22,7 +22,7 @@ class NppsimState(C.Structure):
 EXPORTS = (
     "nppsim_version", "nppsim_last_error", "nppsim_map_blob_bound", "nppsim_compile_map",
     "nppsim_reset", "nppsim_reset_terminal", "nppsim_step", "nppsim_step_actions", "nppsim_step_host", "nppsim_launch_count",
-    "nppsim_debug_sq", "nppsim_sq_mode", "nppsim_debug_force_full_kernel",
+    "nppsim_observe", "nppsim_debug_sq", "nppsim_sq_mode", "nppsim_debug_force_full_kernel",
 )
 
 
@@ -51,6 +51,7 @@ def lib():
     L.nppsim_step_actions.argtypes = [st, vp, i32, i32, vp, vp]; L.nppsim_step_actions.restype = C.c_int
     L.nppsim_step_host.argtypes = [st, vp, vp, i32, i32, vp, vp, vp]; L.nppsim_step_host.restype = C.c_int
     L.nppsim_launch_count.restype = i64
+    L.nppsim_observe.argtypes = [st, vp, vp, vp, vp]; L.nppsim_observe.restype = C.c_int
     L.nppsim_debug_sq.argtypes = [vp, vp, i32, vp]; L.nppsim_debug_sq.restype = C.c_int
     L.nppsim_sq_mode.restype = C.c_int
     L.nppsim_debug_force_full_kernel.argtypes = [i32]; L.nppsim_debug_force_full_kernel.restype = C.c_int

@@ -186,6 +186,31 @@ class BatchedSimulator:
     def _i(self, name):
         return self.nin_i[FD.I[name]]
 
+    # ------------------------------------------------------------------ observation primitives
+    def get_action_mask(self, path_direction=None):
+        """Ninja.get_valid_action_mask for every env (nplay_headless.py:433-442, ninja.py:628-839): bool [N, 6].
+        path_direction: optional uint8 tensor [N], 0 None / 1 "left" / 2 "right" / 3 "down"
+        (sim._path_straightness_direction, masking mode "hard")."""
+        self._need_maps()
+        out = torch.empty((self.n_envs, 6), dtype=torch.uint8, device=self.device)
+        pd = None
+        if path_direction is not None:
+            pd = torch.as_tensor(path_direction, dtype=torch.uint8, device=self.device).contiguous()
+            if pd.shape != (self.n_envs,):
+                raise ValueError("path_direction must hold one value per env")
+        with torch.cuda.device(self.device):
+            check(self.L.nppsim_observe(C.byref(self._state), C.c_void_p(pd.data_ptr()) if pd is not None else None,
+                                        C.c_void_p(out.data_ptr()), None, self._stream()))
+        return out.bool()
+
+    def get_ninja_state(self):
+        """NPlayHeadless.get_ninja_state for every env (nplay_headless.py:735-917): float32 [N, 40]."""
+        self._need_maps()
+        out = torch.empty((self.n_envs, 40), dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            check(self.L.nppsim_observe(C.byref(self._state), None, None, C.c_void_p(out.data_ptr()), self._stream()))
+        return out
+
     def ninja_position(self):            # nplay_headless.py:415-416
         return self.nin_f[0], self.nin_f[1]
 

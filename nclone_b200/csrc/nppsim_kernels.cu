@@ -168,6 +168,102 @@ __global__ void __launch_bounds__(1024) sched_kernel(int32_t* __restrict__ order
     }
 }
 
+// ---- observation primitives -----------------------------------------------------------
+// One thread per env, straight from the SoA state.  ninja_state: NPlayHeadless.get_ninja_state
+// (nplay_headless.py:735-917 + Ninja.get_temporal_features ninja.py:1217-1244), computed in double and stored
+// as the float32 the env wrapper converts it to; `x ** 0.5` is evaluated as sqrt (differs from libm pow(x, 0.5)
+// by at most one double ulp, invisible after the float32 rounding except on a rounding boundary).
+// mask: Ninja.get_valid_action_mask (ninja.py:628-839), masking mode "hard"; path_dir[i] in {0 None, 1 "left",
+// 2 "right", 3 "down"} is sim._path_straightness_direction (NULL: None everywhere).
+DEV double obs_min(double a, double b) { return b < a ? b : a; }      // Python min(a, b) / max(a, b)
+DEV double obs_max(double a, double b) { return b > a ? b : a; }
+__global__ void __launch_bounds__(128) obs_kernel(nppsim_state_t st, const uint8_t* __restrict__ path_dir, uint8_t* __restrict__ mask_out, float* __restrict__ state_out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= st.n_envs) return;
+    const size_t N = st.n_envs;
+    const double* f = st.nin_f + i; const int32_t* q = st.nin_i + i;
+#define NF_(k) f[(size_t)(k) * N]
+#define NI_(k) q[(size_t)(k) * N]
+    const int state = NI_(I_STATE), airborn = NI_(I_AIRBORN), walled = NI_(I_WALLED), jump_input = NI_(I_JUMP_INPUT);
+    const int jump_buffer = NI_(I_JUMP_BUFFER), floor_buffer = NI_(I_FLOOR_BUFFER), wall_buffer = NI_(I_WALL_BUFFER), lp_buffer = NI_(I_LP_BUFFER);
+    const double wall_normal = NF_(F_WALL_NORMAL), yspeed = NF_(F_YSPEED);
+    if (mask_out) {
+        bool m[6] = {true, true, true, true, true, true};
+        const bool has_active_buffer = (-1 < jump_buffer && jump_buffer < 5) || (-1 < floor_buffer && floor_buffer < 5) ||
+                                       (-1 < wall_buffer && wall_buffer < 5) || (-1 < lp_buffer && lp_buffer < 4);
+        bool jump_useless = false;
+        if (airborn && state != 3) jump_useless = jump_input != 0 ? !has_active_buffer : false;
+        if (jump_useless) { m[3] = false; m[4] = false; m[5] = false; }
+        if (walled) {
+            if (!airborn || state == 5) { if (wall_normal > 0) m[1] = false; else if (wall_normal < 0) m[2] = false; }
+            else {
+                const bool would_trigger_wall_slide = yspeed >= 0;
+                if (wall_normal > 0) { if (!would_trigger_wall_slide) m[1] = false; }
+                else if (wall_normal < 0) { if (!would_trigger_wall_slide) m[2] = false; }
+            }
+        }
+        const int pd = path_dir ? path_dir[i] : 0;
+        if (pd == 1) { m[2] = false; m[3] = false; m[4] = false; m[5] = false; }
+        else if (pd == 2) { m[1] = false; m[3] = false; m[4] = false; m[5] = false; }
+        else if (pd == 3) { m[3] = false; m[4] = false; m[5] = false; }
+        if (!(m[0] || m[1] || m[2] || m[3] || m[4] || m[5])) m[0] = true;
+#pragma unroll
+        for (int k = 0; k < 6; k++) mask_out[(size_t)i * 6 + k] = m[k] ? 1 : 0;
+    }
+    if (!state_out) return;
+    const double xspeed = NF_(F_XSPEED), xspeed_old = NF_(F_XSPEED_OLD), yspeed_old = NF_(F_YSPEED_OLD);
+    const double fnx = NF_(F_FNX), fny = NF_(F_FNY), gravity = NF_(F_GRAVITY);
+    const int floor_count = NI_(I_FLOOR_COUNT), ceiling_count = NI_(I_CEILING_COUNT);
+    const int wall_count = 0;                                  // never written by the reference
+    float* o = state_out + (size_t)i * 40;
+    const double v2 = SQ(xspeed) + SQ(yspeed);
+    const double velocity_magnitude = sqrt(v2);
+    o[0] = (float)(obs_min(velocity_magnitude / (MAX_HOR_SPEED * 2), 1.0) * 2 - 1);
+    o[1] = velocity_magnitude > 1e-6 ? (float)(xspeed / velocity_magnitude) : 0.0f;
+    o[2] = velocity_magnitude > 1e-6 ? (float)(yspeed / velocity_magnitude) : 0.0f;
+    o[3] = (state >= 0 && state <= 2) ? 1.0f : -1.0f;
+    o[4] = (state == 3 || state == 4) ? 1.0f : -1.0f;
+    o[5] = state == 5 ? 1.0f : -1.0f;
+    o[6] = (state >= 6 && state <= 9) ? 1.0f : -1.0f;
+    o[7] = airborn ? 1.0f : -1.0f;
+    o[8] = (float)NI_(I_HOR_INPUT);
+    o[9] = jump_input ? 1.0f : -1.0f;
+    o[10] = (float)((max(jump_buffer, 0) / 5.0) * 2 - 1);
+    o[11] = (float)((max(floor_buffer, 0) / 5.0) * 2 - 1);
+    o[12] = (float)((max(wall_buffer, 0) / 5.0) * 2 - 1);
+    o[13] = (float)(min(floor_count, 1) * 2 - 1);
+    o[14] = (float)(min(wall_count, 1) * 2 - 1);
+    o[15] = (float)(min(ceiling_count, 1) * 2 - 1);
+    o[16] = (float)(sqrt(SQ(fnx) + SQ(fny)) * 2 - 1);
+    o[17] = 0.0f;                                              // wall_count > 0 never holds
+    o[18] = (float)fny;
+    o[19] = (float)((gravity - GRAVITY_JUMP) / (GRAVITY_FALL - GRAVITY_JUMP) * 2 - 1);
+    o[20] = walled ? 1.0f : -1.0f;
+    o[21] = (float)fnx;
+    o[22] = (float)NF_(F_CNX);
+    o[23] = (float)NF_(F_CNY);
+    o[24] = (float)((NF_(F_DRAG) - DRAG_SLOW) / (DRAG_REGULAR - DRAG_SLOW) * 2 - 1);
+    o[25] = (float)((NF_(F_FRICTION) - FRICTION_GROUND_SLOW) / (FRICTION_GROUND - FRICTION_GROUND_SLOW) * 2 - 1);
+    o[26] = (float)obs_max(-1.0, obs_min(1.0, (xspeed - xspeed_old) / MAX_HOR_SPEED));
+    o[27] = (float)obs_max(-1.0, obs_min(1.0, (yspeed - yspeed_old) / MAX_HOR_SPEED));
+    o[28] = (float)(obs_min(velocity_magnitude / (MAX_HOR_SPEED * 1.5), 1.0) * 2 - 1);
+    o[29] = (float)(obs_min(NI_(I_FRAMES_AIRBORNE) / 60.0, 1.0) * 2 - 1);
+    o[30] = (float)(obs_min((double)NI_(I_JUMP_DURATION) / MAX_JUMP_DURATION, 1.0) * 2 - 1);
+    o[31] = (float)(obs_min(NI_(I_STATE_CHANGE_FRAME) / 30.0, 1.0) * 2 - 1);
+    const double kinetic_energy = 0.5 * v2;
+    o[32] = (float)(obs_min(kinetic_energy / SQ(MAX_HOR_SPEED), 1.0) * 2 - 1);
+    o[33] = (float)((NF_(F_YPOS) / 600.0) * 2 - 1);
+    o[34] = (float)(obs_min(sqrt(SQ(gravity) + SQ(!airborn ? GROUND_ACCEL : AIR_ACCEL)) / 0.1, 1.0) * 2 - 1);
+    const double prev_kinetic = 0.5 * (SQ(xspeed_old) + SQ(yspeed_old));
+    o[35] = (float)obs_max(-1.0, obs_min(1.0, (kinetic_energy - prev_kinetic) / obs_max(kinetic_energy + 0.01, 0.01)));
+    o[36] = (float)(obs_min(floor_count / 5.0, 1.0) * 2 - 1);
+    o[37] = (float)(obs_min(wall_count / 3.0, 1.0) * 2 - 1);
+    o[38] = (float)(atan2(fny, fnx) / 3.141592653589793);
+    o[39] = walled ? (float)wall_normal : 0.0f;
+#undef NF_
+#undef NI_
+}
+
 __global__ void sq_kernel(const double* in, double* out, int n) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = SQ(in[i]);
@@ -278,6 +374,18 @@ int nppsim_reset_terminal(const nppsim_state_t* st, int32_t max_frames, int32_t 
     g_launches++;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_fail(e, "reset_kernel launch");
+    return 0;
+}
+
+int nppsim_observe(const nppsim_state_t* st, const uint8_t* path_dir, uint8_t* mask_out, float* ninja_state_out, void* stream) {
+    g_err[0] = 0;
+    int rc = check_state(st);
+    if (rc) return rc;
+    if (!mask_out && !ninja_state_out) return fail(NPPSIM_E_ARG, "no output buffer");
+    obs_kernel<<<(st->n_envs + 127) / 128, 128, 0, (cudaStream_t)stream>>>(*st, path_dir, mask_out, ninja_state_out);
+    g_launches++;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "obs_kernel launch");
     return 0;
 }
 

@@ -1575,6 +1575,103 @@ int osim_num_entities(const OSim *S) { return S->ndic; }
 int osim_num_segments(const OSim *S) { return S->nsegs; }
 int osim_events(OSim *S) { int e = S->events; S->events = 0; return e; }
 
+/* ------------------------------------------------------------------------- */
+/* observation primitives                                 */
+/* ------------------------------------------------------------------------- */
+static double dmin(double a, double b) { return b < a ? b : a; }      /* Python min(a, b): first on ties */
+static double dmax(double a, double b) { return b > a ? b : a; }
+/* NPlayHeadless.get_ninja_state: nplay_headless.py:735-917 (+ Ninja.get_temporal_features ninja.py:1217-1244).
+   `x ** 0.5` is libm pow(x, 0.5); math.sqrt / math.atan2 are libm sqrt / atan2. */
+void osim_ninja_state(const OSim *S, double *o) {
+    const Ninja *n = &S->ninja;
+    int k = 0;
+    double velocity_magnitude = pow(SQ(n->xspeed) + SQ(n->yspeed), 0.5);
+    double max_velocity = MAX_HOR_SPEED * 2;
+    o[k++] = dmin(velocity_magnitude / max_velocity, 1.0) * 2 - 1;
+    if (velocity_magnitude > 1e-6) { o[k++] = n->xspeed / velocity_magnitude; o[k++] = n->yspeed / velocity_magnitude; }
+    else { o[k++] = 0.0; o[k++] = 0.0; }
+    o[k++] = (n->state >= 0 && n->state <= 2) ? 1.0 : -1.0;
+    o[k++] = (n->state == 3 || n->state == 4) ? 1.0 : -1.0;
+    o[k++] = n->state == 5 ? 1.0 : -1.0;
+    o[k++] = (n->state >= 6 && n->state <= 9) ? 1.0 : -1.0;
+    o[k++] = n->airborn ? 1.0 : -1.0;
+    o[k++] = (double)n->hor_input;
+    o[k++] = n->jump_input ? 1.0 : -1.0;
+    o[k++] = ((n->jump_buffer > 0 ? n->jump_buffer : 0) / 5.0) * 2 - 1;
+    o[k++] = ((n->floor_buffer > 0 ? n->floor_buffer : 0) / 5.0) * 2 - 1;
+    o[k++] = ((n->wall_buffer > 0 ? n->wall_buffer : 0) / 5.0) * 2 - 1;
+    o[k++] = (double)((n->floor_count < 1 ? n->floor_count : 1) * 2 - 1);
+    o[k++] = (double)((n->wall_count < 1 ? n->wall_count : 1) * 2 - 1);
+    o[k++] = (double)((n->ceiling_count < 1 ? n->ceiling_count : 1) * 2 - 1);
+    o[k++] = pow(SQ(n->floor_normalized_x) + SQ(n->floor_normalized_y), 0.5) * 2 - 1;
+    o[k++] = n->wall_count > 0 ? n->wall_normal : 0.0;
+    o[k++] = n->floor_normalized_y;
+    {
+        double gravity_range = GRAVITY_FALL - GRAVITY_JUMP;
+        o[k++] = gravity_range > 1e-6 ? (n->applied_gravity - GRAVITY_JUMP) / gravity_range * 2 - 1 : 0.0;
+    }
+    o[k++] = n->walled ? 1.0 : -1.0;
+    o[k++] = n->floor_normalized_x;
+    o[k++] = n->ceiling_normalized_x;
+    o[k++] = n->ceiling_normalized_y;
+    {
+        double drag_range = DRAG_REGULAR - DRAG_SLOW;
+        o[k++] = drag_range > 1e-6 ? (n->applied_drag - DRAG_SLOW) / drag_range * 2 - 1 : 0.0;
+        double friction_range = FRICTION_GROUND - FRICTION_GROUND_SLOW;
+        o[k++] = friction_range > 1e-6 ? (n->applied_friction - FRICTION_GROUND_SLOW) / friction_range * 2 - 1 : 0.0;
+    }
+    /* temporal features */
+    o[k++] = dmax(-1.0, dmin(1.0, (n->xspeed - n->xspeed_old) / MAX_HOR_SPEED));
+    o[k++] = dmax(-1.0, dmin(1.0, (n->yspeed - n->yspeed_old) / MAX_HOR_SPEED));
+    o[k++] = dmin(sqrt(SQ(n->xspeed) + SQ(n->yspeed)) / (MAX_HOR_SPEED * 1.5), 1.0) * 2 - 1;
+    o[k++] = dmin(n->frames_airborne / 60.0, 1.0) * 2 - 1;
+    o[k++] = dmin((double)n->jump_duration / MAX_JUMP_DURATION, 1.0) * 2 - 1;
+    o[k++] = dmin(n->state_change_frame / 30.0, 1.0) * 2 - 1;
+    /* physics features */
+    double kinetic_energy = 0.5 * (SQ(n->xspeed) + SQ(n->yspeed));
+    o[k++] = dmin(kinetic_energy / SQ(MAX_HOR_SPEED), 1.0) * 2 - 1;
+    o[k++] = (n->ypos / 600.0) * 2 - 1;
+    {
+        double force_magnitude = sqrt(SQ(n->applied_gravity) + SQ(!n->airborn ? GROUND_ACCEL : AIR_ACCEL));
+        o[k++] = dmin(force_magnitude / 0.1, 1.0) * 2 - 1;
+    }
+    {
+        double prev_kinetic = 0.5 * (SQ(n->xspeed_old) + SQ(n->yspeed_old));
+        double energy_change_rate = (kinetic_energy - prev_kinetic) / dmax(kinetic_energy + 0.01, 0.01);
+        o[k++] = dmax(-1.0, dmin(1.0, energy_change_rate));
+    }
+    o[k++] = dmin(n->floor_count / 5.0, 1.0) * 2 - 1;
+    o[k++] = dmin(n->wall_count / 3.0, 1.0) * 2 - 1;
+    o[k++] = atan2(n->floor_normalized_y, n->floor_normalized_x) / 3.141592653589793;   /* math.pi */
+    o[k++] = n->walled ? n->wall_normal : 0.0;
+}
+/* Ninja.get_valid_action_mask: ninja.py:628-839, masking mode "hard" with straightness masking enabled (the
+   defaults); path_dir: 0 None, 1 "left", 2 "right", 3 "down" (sim._path_straightness_direction). */
+void osim_action_mask(const OSim *S, int path_dir, uint8_t *mask) {
+    const Ninja *n = &S->ninja;
+    for (int i = 0; i < 6; i++) mask[i] = 1;
+    int has_active_buffer = (-1 < n->jump_buffer && n->jump_buffer < 5) || (-1 < n->floor_buffer && n->floor_buffer < 5) ||
+                            (-1 < n->wall_buffer && n->wall_buffer < 5) || (-1 < n->launch_pad_buffer && n->launch_pad_buffer < 4);
+    int jump_useless = 0;
+    if (n->airborn && n->state != 3) jump_useless = n->jump_input != 0 ? !has_active_buffer : 0;
+    if (jump_useless) { mask[3] = 0; mask[4] = 0; mask[5] = 0; }
+    if (n->walled) {
+        if (!n->airborn || n->state == 5) {
+            if (n->wall_normal > 0) mask[1] = 0; else if (n->wall_normal < 0) mask[2] = 0;
+        } else {
+            int would_trigger_wall_slide = n->yspeed >= 0;
+            if (n->wall_normal > 0) { if (!would_trigger_wall_slide) mask[1] = 0; }
+            else if (n->wall_normal < 0) { if (!would_trigger_wall_slide) mask[2] = 0; }
+        }
+    }
+    if (path_dir == 1) { mask[2] = 0; mask[3] = 0; mask[4] = 0; mask[5] = 0; }
+    else if (path_dir == 2) { mask[1] = 0; mask[3] = 0; mask[4] = 0; mask[5] = 0; }
+    else if (path_dir == 3) { mask[3] = 0; mask[4] = 0; mask[5] = 0; }
+    int any = 0;
+    for (int i = 0; i < 6; i++) any |= mask[i];
+    if (!any) mask[0] = 1;
+}
+
 /* canonical record of oracle/schema.py: nin_f[31], nin_i[27], ent_f[E][4], ent_i[E][8] */
 void osim_get_state(const OSim *S, double *nf, int64_t *ni, double *ef, int64_t *ei) {
     const Ninja *n = &S->ninja;

@@ -50,6 +50,8 @@ def lib():
         L.osim_get_cell_counts.argtypes = [C.c_void_p, i32p, i32p]
         L.osim_get_segments.argtypes = [C.c_void_p, dp]
         L.osim_get_grid_edges.argtypes = [C.c_void_p, i32p, i32p]
+        L.osim_ninja_state.argtypes = [C.c_void_p, dp]
+        L.osim_action_mask.argtypes = [C.c_void_p, C.c_int, u8p]
         L.osim_baseline_run.argtypes = [dp, i32p, C.c_int, C.c_int, u8p, C.c_int, C.c_int, C.c_int, C.c_int, dp, dp]
         L.osim_baseline_run.restype = C.c_long
         _lib = L
@@ -96,6 +98,18 @@ class OracleSim:
 
     def events(self):
         return self.L.osim_events(self.h)
+
+    def ninja_state(self):
+        """NPlayHeadless.get_ninja_state: 40 floats."""
+        o = np.zeros(40)
+        self.L.osim_ninja_state(self.h, _p(o, C.c_double))
+        return o
+
+    def action_mask(self, path_dir=0):
+        """Ninja.get_valid_action_mask; path_dir 0 None / 1 left / 2 right / 3 down."""
+        m = np.zeros(6, dtype=np.uint8)
+        self.L.osim_action_mask(self.h, int(path_dir), _p(m, C.c_uint8))
+        return m
 
     def state(self):
         E = self.num_entities

@@ -288,3 +288,39 @@ def test_basic_variant_vs_oracle_and_full_kernel():
             L.nppsim_debug_force_full_kernel(was)
     for a, b in zip(*states):
         assert torch.equal(a.view(torch.uint8), b.view(torch.uint8))
+
+
+def test_observation_primitives_vs_reference():
+    """SURVEY 8(f) f1 on the device: action mask bit-exact, the 40-float ninja state within one float32 ulp
+    of the reference's float64 values (the kernel stores float32 like the env wrapper does; `x ** 0.5` is
+    sqrt and atan2 is CUDA's, both within 2 double ulp of glibc's).  Tolerance: |d| <= 1.2e-7 * max(1, |x|)."""
+    import os
+    import torch
+    from conftest import Golden, GOLDEN
+    from nclone_b200 import BatchedSimulator
+    d = dict(np.load(os.path.join(GOLDEN, "obs.npz")))          # NpzFile decompresses on every access
+    G = {"bc_replays": Golden(os.path.join(GOLDEN, "bc_replays.npz")), "generated": Golden(os.path.join(GOLDEN, "generated.npz"))}
+    trajs = [G[str(s)].traj(int(i)) for s, i in zip(d["src"], d["idx"])]
+    N = len(trajs)
+    lens = np.array([len(t["hor"]) for t in trajs]); T = int(lens.max())
+    hor = np.zeros((T, N), dtype=np.int8); jump = np.zeros((T, N), dtype=np.int8)
+    for k, t in enumerate(trajs):
+        hor[:lens[k], k] = t["hor"]; jump[:lens[k], k] = t["jump"]
+    sim = BatchedSimulator(N)
+    sim.load_maps([t["map_data"] for t in trajs], np.arange(N))
+    hor_d = torch.from_numpy(hor).cuda(); jump_d = torch.from_numpy(jump).cuda()
+    off = d["frame_off"]
+    worst = 0.0
+    for f in range(T + 1):
+        if f > 0:
+            sim.tick(hor_d[f - 1], jump_d[f - 1], n_ticks=1, tick_limit=(lens > f - 1).astype(np.int32))
+        pd = torch.full((N,), f % 4, dtype=torch.uint8, device="cuda")
+        mask = sim.get_action_mask(pd).cpu().numpy().astype(np.uint8)
+        st = sim.get_ninja_state().cpu().numpy().astype(np.float64)
+        for k in np.nonzero(lens >= f)[0]:
+            want = d["ninja_state"][off[k] + f]
+            assert np.array_equal(mask[k], d["mask"][off[k] + f]), (k, f)
+            err = np.abs(st[k] - want) / np.maximum(1.0, np.abs(want))
+            worst = max(worst, float(err.max()))
+            assert err.max() <= 1.2e-7, (k, f, int(err.argmax()), st[k][err.argmax()], want[err.argmax()])
+    assert worst <= 1.2e-7

@@ -81,3 +81,23 @@ def test_reset_and_fast_reset_replay_first_golden(golden_replays):
         assert np.array_equal(np.asarray(a).view(np.int64), np.asarray(b).view(np.int64))
     nf, ni, _, _ = s.run(t["hor"], t["jump"])
     assert nf[-1][0] == 812.0036311681246 and ni[-1][0] == 8
+
+
+def test_oracle_observation_primitives_match_reference():
+    """get_ninja_state (40 floats) and get_valid_action_mask of the C restatement against
+    the reference's own outputs (tests/golden/obs.npz from oracle/gen_golden_obs.py): bit-exact."""
+    import os
+    from conftest import Golden, GOLDEN
+    d = dict(np.load(os.path.join(GOLDEN, "obs.npz")))          # NpzFile decompresses on every access
+    G = {"bc_replays": Golden(os.path.join(GOLDEN, "bc_replays.npz")), "generated": Golden(os.path.join(GOLDEN, "generated.npz"))}
+    frames = 0
+    for k, (src, i) in enumerate(zip(d["src"], d["idx"])):
+        t = G[str(src)].traj(int(i)); f0 = int(d["frame_off"][k])
+        s = oracle.OracleSim(); s.load(t["map_data"])
+        for f in range(len(t["hor"]) + 1):
+            if f > 0:
+                s.tick(t["hor"][f - 1], t["jump"][f - 1])
+            assert np.array_equal(s.ninja_state().view(np.int64), d["ninja_state"][f0 + f].view(np.int64)), (src, i, f)
+            assert np.array_equal(s.action_mask(f % 4), d["mask"][f0 + f]), (src, i, f)
+            frames += 1
+    assert frames == len(d["mask"]) == 11327
