@@ -16,7 +16,8 @@ import bench
 from nclone_b200 import BatchedSimulator
 from nclone_b200._lib import lib as L
 n_envs = int(sys.argv[1]) if len(sys.argv) > 1 and sys.argv[1].isdigit() else 65536
-arr, lens = bench.load_maps("simplest_with_mines")
+fixture = next((a for a in sys.argv[1:] if a in ("simplest_with_mines", "locked_doors")), "simplest_with_mines")
+arr, lens = bench.load_maps(fixture)
 sim = BatchedSimulator(n_envs)
 sim.load_maps([arr[k, :lens[k]] for k in range(len(arr))], np.arange(n_envs) % len(arr))
 gen = torch.Generator(device="cuda"); gen.manual_seed(1)
