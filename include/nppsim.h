@@ -90,6 +90,23 @@ int64_t nppsim_map_blob_bound(int32_t map_len);
 int     nppsim_compile_map(const double* map_data, int32_t map_len, uint8_t* out, int64_t out_cap,
                            int64_t* out_used, int32_t* n_entities, int32_t* n_dyn_slots);
 
+/* nppsim_compile_maps_device: the same compile for a whole batch of levels in ONE launch on the device
+ * (replaces per-level Simulator.load work: map_loader.py:18-145,
+ * utils/tile_segment_factory.py:169-344, utils/spatial_segment_index.py:69-110, nsim.py:194-219).
+ *   map_data    device float64 [n_maps][row_stride], map_loader format;
+ *   map_len     optional device int32 [n_maps] valid values per row (NULL: default_len for every row);
+ *   blobs       device, 16-byte aligned, n_maps * blob_stride bytes; level m's blob starts at m * blob_stride and is
+ *               byte-identical to nppsim_compile_map's output for the same row (blob_stride >=
+ *               nppsim_map_blob_bound(longest row), multiple of 16);
+ *   map_off     optional device int64 [n_maps], receives m * blob_stride (ready for nppsim_state_t.map_off);
+ *   status      device int32 [n_maps]: 0 or the NPPSIM_E_* code nppsim_compile_map would return for that row (a failed
+ *               level's blob has magic 0); levels with more than NPPSIM_DEVICE_COMPILE_MAX_ENT entities -> NPPSIM_E_CAPACITY;
+ *   summary     device int32 [4]: {max n_entities, max n_dyn_slots, OR of kind_mask, number of failed levels}. */
+#define NPPSIM_DEVICE_COMPILE_MAX_ENT 1024
+int nppsim_compile_maps_device(const double* map_data, int64_t row_stride, const int32_t* map_len, int32_t default_len,
+                               int32_t n_maps, uint8_t* blobs, int64_t blob_stride, int64_t* map_off, int32_t* status,
+                               int32_t* summary, void* stream);
+
 /* ---- device side ------------------------------------------------------------------------
  * nppsim_reset: Simulator.load()'s dynamic part / reset() (mode 0, nsim.py:62-76) or
  * fast_reset() (mode 1, nsim.py:78-140) for every env whose mask byte is non-zero

@@ -22,7 +22,7 @@ class NppsimState(C.Structure):
 EXPORTS = (
     "nppsim_version", "nppsim_last_error", "nppsim_map_blob_bound", "nppsim_compile_map",
     "nppsim_reset", "nppsim_reset_terminal", "nppsim_step", "nppsim_step_actions", "nppsim_step_host", "nppsim_launch_count",
-    "nppsim_observe", "nppsim_debug_sq", "nppsim_sq_mode", "nppsim_debug_force_full_kernel",
+    "nppsim_observe", "nppsim_compile_maps_device", "nppsim_debug_sq", "nppsim_sq_mode", "nppsim_debug_force_full_kernel",
 )
 
 
@@ -44,6 +44,8 @@ def lib():
     L.nppsim_map_blob_bound.argtypes = [i32]; L.nppsim_map_blob_bound.restype = i64
     L.nppsim_compile_map.argtypes = [vp, i32, vp, i64, C.POINTER(i64), C.POINTER(i32), C.POINTER(i32)]
     L.nppsim_compile_map.restype = C.c_int
+    L.nppsim_compile_maps_device.argtypes = [vp, i64, vp, i32, i32, vp, i64, vp, vp, vp, vp]
+    L.nppsim_compile_maps_device.restype = C.c_int
     st = C.POINTER(NppsimState)
     L.nppsim_reset.argtypes = [st, vp, i32, vp]; L.nppsim_reset.restype = C.c_int
     L.nppsim_reset_terminal.argtypes = [st, i32, i32, vp, vp]; L.nppsim_reset_terminal.restype = C.c_int

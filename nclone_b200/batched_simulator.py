@@ -64,8 +64,62 @@ class BatchedSimulator:
         self.map_off = torch.from_numpy(offs).to(dev)
         self.env_map_host = remap[env_to_map].astype(np.int32)
         self.env_map = torch.from_numpy(self.env_map_host).to(dev)
-        self.ent_cap = max(1, max(t.n_ent for t in self.maps))
-        self.dyn_cap = max(1, max(t.n_dyn for t in self.maps))
+        kind_mask = 0
+        for t in self.maps:
+            kind_mask |= t.kind_mask           # entity-kind census of the level set -> step-kernel variant
+        self._alloc_state(len(blobs), max(t.n_ent for t in self.maps), max(t.n_dyn for t in self.maps), kind_mask)
+        self.reset()
+
+    def load_maps_device(self, map_data, map_len=None, env_to_map=None):
+        """Simulator.load for levels that are already in HBM: map_data is a CUDA float64 tensor
+        [M, L] of map_loader rows (map_len: optional int32 [M] valid lengths), compiled to blobs by ONE kernel launch
+        (nppsim_compile_maps_device) -- no per-level host work, nothing crosses PCIe but a 16-byte summary.  Levels are
+        not deduplicated (the caller chooses env_to_map; default env i -> level i % M).  Raises ValueError if any level
+        is malformed (first offender reported), like load_maps."""
+        N, dev = self.n_envs, self.device
+        md = torch.as_tensor(map_data)
+        if md.device.type != "cuda" or md.dtype != torch.float64 or md.dim() != 2:
+            raise ValueError("map_data must be a CUDA float64 tensor [M, L]")
+        md = md.contiguous()
+        M, Lrow = md.shape
+        if env_to_map is None:
+            env_map = torch.arange(N, device=dev, dtype=torch.int32) % M
+        else:
+            env_map = torch.as_tensor(env_to_map).to(device=dev, dtype=torch.int32).contiguous()
+            if env_map.shape != (N,) or int(env_map.min()) < 0 or int(env_map.max()) >= M:
+                raise ValueError("env_to_map must hold one valid map index per env")
+        ml = None
+        if map_len is not None:
+            ml = torch.as_tensor(map_len).to(device=dev, dtype=torch.int32).contiguous()
+            if ml.shape != (M,):
+                raise ValueError("map_len must hold one length per level")
+        stride = (int(self.L.nppsim_map_blob_bound(int(Lrow))) + 255) & ~255
+        self.map_blob = torch.empty(M * stride, dtype=torch.uint8, device=dev)
+        self.map_off = torch.empty(M, dtype=torch.int64, device=dev)
+        self.compile_status = torch.empty(M, dtype=torch.int32, device=dev)
+        summary = torch.empty(4, dtype=torch.int32, device=dev)
+        with torch.cuda.device(dev):
+            check(self.L.nppsim_compile_maps_device(C.c_void_p(md.data_ptr()), int(Lrow), C.c_void_p(ml.data_ptr()) if ml is not None else None,
+                                                    int(Lrow), int(M), C.c_void_p(self.map_blob.data_ptr()), stride,
+                                                    C.c_void_p(self.map_off.data_ptr()), C.c_void_p(self.compile_status.data_ptr()),
+                                                    C.c_void_p(summary.data_ptr()), self._stream()))
+        ent_cap, dyn_cap, kind_mask, n_bad = (int(v) for v in summary.cpu().numpy().view(np.uint32))
+        if n_bad:
+            bad = torch.nonzero(self.compile_status)[0].item()
+            raise ValueError(f"map compile failed for {n_bad} level(s); first: level {bad}, code {int(self.compile_status[bad])}")
+        self._blob_stride = stride
+        self.maps = _DeviceMaps(self.map_blob, stride, M)
+        self._keys = {}
+        self.env_map = env_map
+        self.env_map_host = env_map.cpu().numpy()
+        self._alloc_state(M, ent_cap, dyn_cap, kind_mask)
+        self.reset()
+
+    def _alloc_state(self, n_blobs, ent_cap, dyn_cap, kind_mask):
+        N, dev = self.n_envs, self.device
+        self._exit_cache = None
+        self.ent_cap = max(1, int(ent_cap))
+        self.dyn_cap = max(1, int(dyn_cap))
         self.nin_f = torch.zeros((FD.NF, N), dtype=torch.float64, device=dev)
         self.nin_i = torch.zeros((FD.NI, N), dtype=torch.int32, device=dev)
         self.env_i = torch.zeros((FD.NENV, N), dtype=torch.int32, device=dev)
@@ -76,7 +130,7 @@ class BatchedSimulator:
         self._actions_dev = torch.zeros(N, dtype=torch.uint8, device=dev)
         self.stats = torch.zeros(4, dtype=torch.int64, device=dev)
         st = NppsimState()
-        st.n_envs, st.ent_cap, st.dyn_cap, st.n_maps = N, self.ent_cap, self.dyn_cap, len(blobs)
+        st.n_envs, st.ent_cap, st.dyn_cap, st.n_maps = N, self.ent_cap, self.dyn_cap, int(n_blobs)
         st.nin_f, st.nin_i, st.env_i = self.nin_f.data_ptr(), self.nin_i.data_ptr(), self.env_i.data_ptr()
         st.ent_flag, st.dyn_f, st.dyn_i = self.ent_flag.data_ptr(), self.dyn_f.data_ptr(), self.dyn_i.data_ptr()
         st.env_map, st.map_blob, st.map_off = self.env_map.data_ptr(), self.map_blob.data_ptr(), self.map_off.data_ptr()
@@ -84,12 +138,9 @@ class BatchedSimulator:
         self.warp_order = torch.arange(nw, dtype=torch.int32, device=dev)      # longest-first launch order (csrc/sim_variant.inc)
         self.warp_cost = torch.zeros(nw, dtype=torch.int32, device=dev)
         st.warp_order, st.warp_cost = self.warp_order.data_ptr(), self.warp_cost.data_ptr()
-        self.kind_mask = 0
-        for t in self.maps:
-            self.kind_mask |= t.kind_mask      # entity-kind census of the level set -> step-kernel variant
+        self.kind_mask = int(kind_mask)
         st.kind_mask = self.kind_mask
         self._state = st
-        self.reset()
 
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
@@ -321,6 +372,30 @@ class BatchedSimulator:
 
     def launch_count(self):
         return int(self.L.nppsim_launch_count())
+
+
+class _DeviceMaps:
+    """self.maps for device-compiled levels: MapTables views are pulled from HBM on first use (host getters and
+    parity tests only; the step path never needs them)."""
+
+    def __init__(self, blob, stride, n):
+        self._blob, self._stride, self._n, self._cache = blob, stride, n, {}
+
+    def __len__(self):
+        return self._n
+
+    def __getitem__(self, k):
+        k = int(k)
+        if k < 0 or k >= self._n:
+            raise IndexError(k)
+        if k not in self._cache:
+            head = self._blob[k * self._stride:k * self._stride + 8].cpu().numpy().view(np.uint32)
+            raw = self._blob[k * self._stride:k * self._stride + int(head[1])].cpu().numpy().tobytes()
+            self._cache[k] = MapTables(raw)
+        return self._cache[k]
+
+    def __iter__(self):
+        return (self[k] for k in range(self._n))
 
 
 def _entity_rows(t, fl, df, di, order_mode):

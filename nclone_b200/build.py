@@ -6,8 +6,8 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libnppsim.so")
-SOURCES = ["nppsim_kernels.cu", "map_compiler.cpp"]
-HEADERS = ["geom.cuh", "pool.cuh", "entities.cuh", "ninja.cuh", "sim_variant.inc", "pow2.cuh", "pow2_exact.cuh", "pow2_tables.h", "map_blob.h", "../../include/nppsim.h"]
+SOURCES = ["nppsim_kernels.cu", "map_compile_device.cu", "map_compiler.cpp"]
+HEADERS = ["geom.cuh", "pool.cuh", "entities.cuh", "ninja.cuh", "sim_variant.inc", "pow2.cuh", "pow2_exact.cuh", "pow2_tables.h", "map_blob.h", "tile_tables.h", "../../include/nppsim.h"]
 
 # fp64 discipline: no FMA contraction, IEEE sqrt/div (nvcc's defaults for
 # double; stated explicitly), no fast-math.

@@ -17,55 +17,11 @@
 #include <cstdio>
 
 #include "map_blob.h"
+#include "tile_tables.h"
 #include "../../include/nppsim.h"
 
 namespace {
 
-// tile_definitions.py:84-132 (grid edges) and 137-185 (oriented orthogonal half-segments),
-// one row per tile id 0..33 (34..37 are skipped by the reference), bit-packed would be
-// unreadable so they stay as rows: 6 horizontal halves (left->right, top->bottom) then
-// 6 vertical halves (top->bottom, left->right).
-const int8_t kEdge[34][12] = {
-    {0,0,0,0,0,0, 0,0,0,0,0,0}, {1,1,0,0,1,1, 1,1,0,0,1,1}, {1,1,1,1,0,0, 1,0,0,0,1,0}, {0,1,0,0,0,1, 0,0,1,1,1,1},
-    {0,0,1,1,1,1, 0,1,0,0,0,1}, {1,0,0,0,1,0, 1,1,1,1,0,0}, {1,1,0,1,1,0, 1,1,0,1,1,0}, {1,1,1,0,0,1, 1,0,0,1,1,1},
-    {0,1,1,0,1,1, 0,1,1,0,1,1}, {1,0,0,1,1,1, 1,1,1,0,0,1}, {1,1,0,0,1,1, 1,1,0,0,1,1}, {1,1,0,0,1,1, 1,1,0,0,1,1},
-    {1,1,0,0,1,1, 1,1,0,0,1,1}, {1,1,0,0,1,1, 1,1,0,0,1,1}, {1,1,0,1,1,0, 1,1,0,1,1,0}, {1,1,1,0,0,1, 1,0,0,1,1,1},
-    {0,1,1,0,1,1, 0,1,1,0,1,1}, {1,0,0,1,1,1, 1,1,1,0,0,1}, {1,1,1,1,0,0, 1,0,0,0,1,0}, {1,1,1,1,0,0, 1,0,0,0,1,0},
-    {0,0,1,1,1,1, 0,1,0,0,0,1}, {0,0,1,1,1,1, 0,1,0,0,0,1}, {1,1,0,0,1,1, 1,1,0,0,1,1}, {1,1,0,0,1,1, 1,1,0,0,1,1},
-    {1,1,0,0,1,1, 1,1,0,0,1,1}, {1,1,0,0,1,1, 1,1,0,0,1,1}, {1,0,0,0,1,0, 1,1,1,1,0,0}, {0,1,0,0,0,1, 0,0,1,1,1,1},
-    {0,1,0,0,0,1, 0,0,1,1,1,1}, {1,0,0,0,1,0, 1,1,1,1,0,0}, {1,1,0,0,1,1, 1,1,0,0,1,1}, {1,1,0,0,1,1, 1,1,0,0,1,1},
-    {1,1,0,0,1,1, 1,1,0,0,1,1}, {1,1,0,0,1,1, 1,1,0,0,1,1},
-};
-const int8_t kOrtho[34][12] = {
-    {0,0,0,0,0,0, 0,0,0,0,0,0}, {-1,-1,0,0,1,1, -1,-1,0,0,1,1}, {-1,-1,1,1,0,0, -1,0,0,0,1,0}, {0,-1,0,0,0,1, 0,0,-1,-1,1,1},
-    {0,0,-1,-1,1,1, 0,-1,0,0,0,1}, {-1,0,0,0,1,0, -1,-1,1,1,0,0}, {-1,-1,0,0,0,0, -1,-1,0,0,0,0}, {-1,-1,0,0,0,0, 0,0,0,0,1,1},
-    {0,0,0,0,1,1, 0,0,0,0,1,1}, {0,0,0,0,1,1, -1,-1,0,0,0,0}, {-1,-1,0,0,0,0, -1,-1,0,0,0,0}, {-1,-1,0,0,0,0, 0,0,0,0,1,1},
-    {0,0,0,0,1,1, 0,0,0,0,1,1}, {0,0,0,0,1,1, -1,-1,0,0,0,0}, {-1,-1,0,0,0,0, -1,-1,0,0,0,0}, {-1,-1,0,0,0,0, 0,0,0,0,1,1},
-    {0,0,0,0,1,1, 0,0,0,0,1,1}, {0,0,0,0,1,1, -1,-1,0,0,0,0}, {-1,-1,0,0,0,0, -1,0,0,0,0,0}, {-1,-1,0,0,0,0, 0,0,0,0,1,0},
-    {0,0,0,0,1,1, 0,0,0,0,0,1}, {0,0,0,0,1,1, 0,-1,0,0,0,0}, {-1,-1,0,0,0,0, -1,-1,0,0,1,0}, {-1,-1,0,0,0,0, -1,0,0,0,1,1},
-    {0,0,0,0,1,1, 0,-1,0,0,1,1}, {0,0,0,0,1,1, -1,-1,0,0,0,1}, {-1,0,0,0,0,0, -1,-1,0,0,0,0}, {0,-1,0,0,0,0, 0,0,0,0,1,1},
-    {0,0,0,0,0,1, 0,0,0,0,1,1}, {0,0,0,0,1,0, -1,-1,0,0,0,0}, {-1,-1,0,0,1,0, -1,-1,0,0,0,0}, {-1,-1,0,0,0,1, 0,0,0,0,1,1},
-    {0,-1,0,0,1,1, 0,0,0,0,1,1}, {-1,0,0,0,1,1, -1,-1,0,0,0,0},
-};
-// tile_definitions.py:189-223 in half-tile units (x12): diagonal end points, or arc centre + quadrant + convex
-struct Slanted { int8_t kind; int8_t a, b, c, d; int8_t convex; };   // kind 0 none, 1 diagonal (a,b)->(c,d), 2 arc centre (a,b) quadrant (c,d)
-const Slanted kSlanted[34] = {
-    {0,0,0,0,0,0},{0,0,0,0,0,0},{0,0,0,0,0,0},{0,0,0,0,0,0},{0,0,0,0,0,0},{0,0,0,0,0,0},
-    {1,0,2,2,0,0},{1,0,0,2,2,0},{1,2,0,0,2,0},{1,2,2,0,0,0},
-    {2,0,0,1,1,1},{2,2,0,-1,1,1},{2,2,2,-1,-1,1},{2,0,2,1,-1,1},
-    {2,2,2,-1,-1,0},{2,0,2,1,-1,0},{2,0,0,1,1,0},{2,2,0,-1,1,0},
-    {1,0,1,2,0,0},{1,0,0,2,1,0},{1,2,1,0,2,0},{1,2,2,0,1,0},
-    {1,0,2,2,1,0},{1,0,1,2,2,0},{1,2,0,0,1,0},{1,2,1,0,0,0},
-    {1,0,2,1,0,0},{1,1,0,2,2,0},{1,2,0,1,2,0},{1,1,2,0,0,0},
-    {1,1,2,2,0,0},{1,0,0,1,2,0},{1,1,0,0,2,0},{1,2,2,1,0,0},
-};
-
-inline uint32_t pack_linear(int x1, int y1, int x2, int y2) {      // units of 12 px
-    return (uint32_t)x1 | ((uint32_t)y1 << 7) | ((uint32_t)x2 << 13) | ((uint32_t)y2 << 20);
-}
-inline uint32_t pack_arc(int cx, int cy, int hor, int ver, int convex) {
-    return NPP_SEG_ARC | (uint32_t)cx | ((uint32_t)cy << 7) | ((hor < 0 ? 1u : 0u) << 13) | ((ver < 0 ? 1u : 0u) << 14) | ((convex ? 1u : 0u) << 15);
-}
 struct Box { int x0, y0, x1, y1; };
 inline Box seg_box(uint32_t s) {   // entities.py:36-41, 121-125
     Box b;
@@ -79,11 +35,6 @@ inline Box seg_box(uint32_t s) {   // entities.py:36-41, 121-125
     }
     return b;
 }
-inline int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
-inline int cell_of(double x, double y) {     // entities.py:233 with clamp_cell (physics.py:11-13)
-    return clampi((int)std::floor(x / 24), 0, 43) * NPP_NCY + clampi((int)std::floor(y / 24), 0, 24);
-}
-inline bool is_int(double v) { return v == std::floor(v); }
 // physics.py:317-332: orientation dict has keys 0..7 only
 inline bool orientation_vec(double o, double* vx, double* vy) {
     if (!is_int(o) || o < 0 || o > 7) return false;
@@ -171,7 +122,6 @@ extern "C" int nppsim_compile_map(const double* m, int32_t len, uint8_t* out, in
     int counts[40] = {0};
     double dexit = m[1156];
     if (!is_int(dexit)) return fail(NPPSIM_E_MAP, "map_data[1156] (exit door count) is not an integer");
-    int exit_door_count = (int)dexit;
     auto make = [&](int kind, int type, int key, double xc, double yc) -> Draft& {
         Draft d; std::memset(&d, 0, sizeof(d));
         d.se.kind = (uint8_t)kind; d.se.type = (uint8_t)type; d.dic_key = key;
@@ -187,8 +137,8 @@ extern "C" int nppsim_compile_map(const double* m, int32_t len, uint8_t* out, in
         double vx, vy;
         if (!orientation_vec(orientation, &vx, &vy)) return fail(NPPSIM_E_MAP, "door orientation not in 0..7");
         bool vertical = (orientation == 0 || orientation == 4);
-        int dcx = clampi((int)std::floor((d.se.x - 12 * vx) / 24), 0, 43);
-        int dcy = clampi((int)std::floor((d.se.y - 12 * vy) / 24), 0, 24);
+        int dcx = cell_axis(d.se.x - 12 * vx, 43);
+        int dcy = cell_axis(d.se.y - 12 * vy, 24);
         int hx = 2 * (dcx + 1), hy = 2 * (dcy + 1);
         d.has_door = true; d.door.vertical = vertical ? 1 : 0;
         if (vertical) { d.door.x0 = (uint8_t)hx; d.door.y0 = (uint8_t)(hy - 2); d.door.x1 = (uint8_t)hx; d.door.y1 = (uint8_t)(hy - 1); }
@@ -212,8 +162,9 @@ extern "C" int nppsim_compile_map(const double* m, int32_t len, uint8_t* out, in
             Draft& p = make(NPP_K_EXIT, 3, 3, xc, yc);
             p.in_grid = false; p.roaming = true;
             int parent_pos = (int)drafts.size() - 1;
-            long ci = (long)index + 5L * exit_door_count + 1;
-            if (ci < 0 || ci + 1 >= len) return fail(NPPSIM_E_MAP, "exit switch coordinates out of range");
+            double cd = (double)index + 5.0 * dexit + 1;         // in the double domain: no overflow on garbage counts
+            if (!(cd >= 0 && cd + 1 < len)) return fail(NPPSIM_E_MAP, "exit switch coordinates out of range");
+            long ci = (long)cd;
             Draft& s = make(NPP_K_EXIT_SWITCH, 4, 3, m[ci], m[ci + 1]);
             s.roaming = true; s.se.aux = (int16_t)parent_pos;   // creation position; remapped to entity id below
             break; }

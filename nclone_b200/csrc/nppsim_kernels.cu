@@ -5,10 +5,12 @@
 #include <atomic>
 #include <cstring>
 
+std::atomic<long long> g_nppsim_launches{0};     // shared with map_compile_device.cu
+
 namespace {
 
 thread_local char g_err[256] = "";
-std::atomic<long long> g_launches{0};
+std::atomic<long long>& g_launches = g_nppsim_launches;
 bool g_force_full = false;     // test hook: run every level set on the full kernel
 
 int fail(int code, const char* msg) { snprintf(g_err, sizeof(g_err), "%s", msg); return code; }
@@ -321,7 +323,12 @@ extern "C" {
 
 int nppsim_version(void) { return NPPSIM_VERSION; }
 const char* nppsim_compile_error(void);
-const char* nppsim_last_error(void) { return g_err[0] ? g_err : nppsim_compile_error(); }
+const char* nppsim_compile_device_error(void);
+const char* nppsim_last_error(void) {
+    if (g_err[0]) return g_err;
+    const char* d = nppsim_compile_device_error();
+    return d[0] ? d : nppsim_compile_error();
+}
 int64_t nppsim_launch_count(void) { return (int64_t)g_launches.load(); }
 int nppsim_sq_mode(void) { return NPP_SQ_MODE; }
 int nppsim_debug_force_full_kernel(int on) { int was = g_force_full; g_force_full = on != 0; return was; }
