@@ -78,6 +78,17 @@ typedef struct {
                                    the step kernel), the key of the longest-first order */
 } nppsim_state_t;
 
+/* Per-env input streams for nppsim_step_stream: env i owns data[offset[i] .. offset[i+1]) -- ragged, no padding. */
+#define NPPSIM_STREAM_ACTIONS      0   /* Discrete(6) actions, ACTION_TO_INPUTS (action_replayer.py:30-37); > 5 -> NOOP (:236-240) */
+#define NPPSIM_STREAM_REPLAY_BYTES 1   /* .replay input bytes: bit0 jump, bit1 right, bit2 left, both -> 0 (replay/replay_executor.py:61-86) */
+typedef struct {
+    const uint8_t* data;        /* device: all envs' entries, concatenated */
+    const int64_t* offset;      /* device [N+1] */
+    int32_t encoding;           /* NPPSIM_STREAM_* */
+    int32_t repeat;             /* ticks each entry is held for (ActionReplayer.frame_skip, action_replayer.py:104-107); >= 1 */
+    int64_t start_tick;         /* position (in ticks) inside every env's stream of the launch's first tick: chunked execution */
+} nppsim_input_stream_t;
+
 int         nppsim_version(void);
 const char* nppsim_last_error(void);
 
@@ -120,6 +131,20 @@ int nppsim_reset(const nppsim_state_t* st, const uint8_t* mask, int32_t mode, vo
 int nppsim_reset_terminal(const nppsim_state_t* st, int32_t max_frames, int32_t mode,
                           unsigned long long* stats, void* stream);
 
+/* nppsim_set_exit_positions: the curriculum's mutation from outside tick -- IntermediateGoalManager.apply_to_simulator
+ * (gym_environment/reward_calculation/intermediate_goal_manager.py:698-960) for every env whose mask byte is non-zero
+ * (mask == NULL: all).  The last exit switch of entity_dic[3] moves to switch_xy and is re-armed while sim.frame <= 10;
+ * its parent door moves to door_xy; cells and grid_entity order follow the reference (a re-celled switch is re-appended,
+ * a re-celled door leaves the grid until the switch is taken).  A later reset / fast_reset restores the level's own positions.
+ *   switch_xy, door_xy  device float64 [2][N] (row 0 x, row 1 y);
+ *   status              optional device int32 [N]: 0, or -1 for a masked env whose level has no exit switch (the reference
+ *                       raises RuntimeError); unmasked envs are left untouched.
+ * Not modelled: re-arming a switch that was already taken in the first 10 frames and taking it again appends the door to
+ * its cell list a second time in the reference; here the door stays listed once (the physics is identical -- the door's
+ * collision is idempotent -- only later list positions in that cell differ). */
+int nppsim_set_exit_positions(const nppsim_state_t* st, const uint8_t* mask, const double* switch_xy, const double* door_xy,
+                              int32_t* status, void* stream);
+
 /* nppsim_step: Simulator.tick (nsim.py:221-292) n_ticks times for every env in one launch.
  *   hor, jump   device int8, hor in {-1,0,1}, jump in {0,1}; input_ticks == 1: one value per
  *               env held for all ticks ([N]); input_ticks == n_ticks: per-tick rows ([n_ticks][N]).
@@ -136,6 +161,27 @@ int nppsim_step(const nppsim_state_t* st, const int8_t* hor, const int8_t* jump,
  * decoded with ACTION_TO_INPUTS (action_replayer.py:30-37 == base_environment.py:384-402). */
 int nppsim_step_actions(const nppsim_state_t* st, const uint8_t* actions, int32_t n_ticks,
                         int32_t stop_on_terminal, int32_t* frames_executed, void* stream);
+
+/* nppsim_step_stream: up to n_ticks ticks with every env reading its own input stream -- the hot loop of
+ * ActionReplayer.replay_to_checkpoint / replay_partial (action_replayer.py:79-163: reset, then frame_skip ticks per
+ * stored action) and of ReplayExecutor.execute_replay (replay/replay_executor.py:431-436) for a whole ragged batch in
+ * one launch.  Env i runs min(n_ticks, len_i * repeat - start_tick) ticks (0 once its stream is exhausted). */
+int nppsim_step_stream(const nppsim_state_t* st, const nppsim_input_stream_t* in, int32_t n_ticks, int32_t stop_on_terminal,
+                       int32_t* frames_executed, void* stream);
+
+/* nppsim_replay_rows: one dataset row per env whose replay is still running -- the simulator-derived part of
+ * ReplayExecutor._get_raw_observation (replay/replay_executor.py:470-600) written straight into ragged per-replay
+ * tables.  Call after the step that executed stream ticks [.., obs_tick]; env i (replay of
+ * in->offset[i+1]-in->offset[i] input bytes, in->repeat = 1) writes row row_off[i] + k, k = obs_tick / frame_skip - 1,
+ * iff obs_tick <= its length:
+ *   game_state [rows][41] f32   get_ninja_state()[:40] + time_remaining = max(0, (len - sim.frame) / len)   (:530-545)
+ *   pos        [rows][6]  f64   player x,y | exit switch x,y | exit door x,y   (nplay_headless.py:415, 577-616)
+ *   flags      [rows][4]  u8    switch_activated, player_won, player_dead, action = map_input_to_action(byte of the
+ *                               row's last tick) (:42-58, :448)
+ *   frame      [rows]     i32   frame_idx = obs_tick - 1 (:453)
+ * Any output pointer may be NULL. */
+int nppsim_replay_rows(const nppsim_state_t* st, const nppsim_input_stream_t* in, const int64_t* row_off, int32_t obs_tick,
+                       int32_t frame_skip, float* game_state, double* pos, uint8_t* flags, int32_t* frame, void* stream);
 
 /* nppsim_step_host: the call a host-resident caller makes (one NppEnvironment.step worth of
  * physics for the batch): copies `actions_host` [N] to `actions_dev`, runs nppsim_step_actions,

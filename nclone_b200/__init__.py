@@ -9,7 +9,7 @@ def __getattr__(name):
     if name == "BatchedSimulator":
         from .batched_simulator import BatchedSimulator
         return BatchedSimulator
-    if name in ("parse_replay", "decode_input_byte"):
+    if name in ("parse_replay", "decode_input_byte", "execute_replays"):
         from . import replay
         return getattr(replay, name)
     raise AttributeError(name)

@@ -19,10 +19,19 @@ class NppsimState(C.Structure):
     ]
 
 
+class NppsimInputStream(C.Structure):
+    """nppsim_input_stream_t"""
+    _fields_ = [("data", C.c_void_p), ("offset", C.c_void_p), ("encoding", C.c_int32), ("repeat", C.c_int32),
+                ("start_tick", C.c_int64)]
+
+
+STREAM_ACTIONS, STREAM_REPLAY_BYTES = 0, 1
+
 EXPORTS = (
     "nppsim_version", "nppsim_last_error", "nppsim_map_blob_bound", "nppsim_compile_map",
-    "nppsim_reset", "nppsim_reset_terminal", "nppsim_step", "nppsim_step_actions", "nppsim_step_host", "nppsim_launch_count",
-    "nppsim_observe", "nppsim_compile_maps_device", "nppsim_debug_sq", "nppsim_sq_mode", "nppsim_debug_force_full_kernel",
+    "nppsim_reset", "nppsim_reset_terminal", "nppsim_step", "nppsim_step_actions", "nppsim_step_stream", "nppsim_replay_rows",
+    "nppsim_step_host", "nppsim_launch_count",
+    "nppsim_observe", "nppsim_set_exit_positions", "nppsim_compile_maps_device", "nppsim_debug_sq", "nppsim_sq_mode", "nppsim_debug_force_full_kernel",
 )
 
 
@@ -51,9 +60,13 @@ def lib():
     L.nppsim_reset_terminal.argtypes = [st, i32, i32, vp, vp]; L.nppsim_reset_terminal.restype = C.c_int
     L.nppsim_step.argtypes = [st, vp, vp, i32, i32, vp, i32, vp, vp]; L.nppsim_step.restype = C.c_int
     L.nppsim_step_actions.argtypes = [st, vp, i32, i32, vp, vp]; L.nppsim_step_actions.restype = C.c_int
+    sp = C.POINTER(NppsimInputStream)
+    L.nppsim_step_stream.argtypes = [st, sp, i32, i32, vp, vp]; L.nppsim_step_stream.restype = C.c_int
+    L.nppsim_replay_rows.argtypes = [st, sp, vp, i32, i32, vp, vp, vp, vp, vp]; L.nppsim_replay_rows.restype = C.c_int
     L.nppsim_step_host.argtypes = [st, vp, vp, i32, i32, vp, vp, vp]; L.nppsim_step_host.restype = C.c_int
     L.nppsim_launch_count.restype = i64
     L.nppsim_observe.argtypes = [st, vp, vp, vp, vp]; L.nppsim_observe.restype = C.c_int
+    L.nppsim_set_exit_positions.argtypes = [st, vp, vp, vp, vp, vp]; L.nppsim_set_exit_positions.restype = C.c_int
     L.nppsim_debug_sq.argtypes = [vp, vp, i32, vp]; L.nppsim_debug_sq.restype = C.c_int
     L.nppsim_sq_mode.restype = C.c_int
     L.nppsim_debug_force_full_kernel.argtypes = [i32]; L.nppsim_debug_force_full_kernel.restype = C.c_int

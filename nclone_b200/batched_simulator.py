@@ -12,7 +12,7 @@ import numpy as np
 import torch
 
 from . import fields as FD
-from ._lib import lib, check, NppsimState
+from ._lib import lib, check, NppsimState, NppsimInputStream, STREAM_ACTIONS, STREAM_REPLAY_BYTES
 from .map_compile import compile_map, content_key, MapTables
 
 
@@ -172,6 +172,31 @@ class BatchedSimulator:
             check(self.L.nppsim_reset_terminal(C.byref(self._state), int(max_frames), {"reset": 0, "fast": 1}[mode],
                                                C.c_void_p(self.stats.data_ptr()), self._stream()))
 
+    # ------------------------------------------------------------------ curriculum mutation from outside tick
+    def set_exit_positions(self, switch_xy, door_xy, mask=None):
+        """IntermediateGoalManager.apply_to_simulator for the batch
+        (gym_environment/reward_calculation/intermediate_goal_manager.py:698-960): move every masked env's exit switch
+        to switch_xy[:, i] and its door to door_xy[:, i] (float64 [2, N]), re-arm the switch while frame <= 10, and
+        re-home both in the entity grid as the reference does.  reset()/fast_reset() restore the level's own positions.
+        Raises RuntimeError if a masked env's level has no exit switch, like the reference."""
+        self._need_maps()
+        N, dev = self.n_envs, self.device
+        sxy = torch.as_tensor(switch_xy).to(device=dev, dtype=torch.float64).contiguous()
+        dxy = torch.as_tensor(door_xy).to(device=dev, dtype=torch.float64).contiguous()
+        if sxy.shape != (2, N) or dxy.shape != (2, N):
+            raise ValueError("switch_xy and door_xy must be [2, n_envs]")
+        ptr = None
+        if mask is not None:
+            mask = torch.as_tensor(mask, device=dev).to(torch.uint8).contiguous()
+            ptr = C.c_void_p(mask.data_ptr())
+        status = torch.zeros(N, dtype=torch.int32, device=dev)
+        with torch.cuda.device(dev):
+            check(self.L.nppsim_set_exit_positions(C.byref(self._state), ptr, C.c_void_p(sxy.data_ptr()), C.c_void_p(dxy.data_ptr()),
+                                                   C.c_void_p(status.data_ptr()), self._stream()))
+        if bool((status != 0).any()):
+            bad = torch.nonzero(status)[0].item()
+            raise RuntimeError(f"No EntityExitSwitch found in entity_dic[3] (env {bad})")
+
     def total_ticks(self):
         return int(self.env_i[FD.ENV_TICKS].to(torch.int64).sum().item())
 
@@ -219,6 +244,53 @@ class BatchedSimulator:
                                              int(bool(stop_on_terminal)), C.c_void_p(self.frames_executed.data_ptr()),
                                              self._stream()))
         return self.frames_executed
+
+    # ------------------------------------------------------------------ per-env input streams
+    def make_stream(self, sequences, encoding="actions", repeat=1):
+        """Pack one input sequence per env (any lengths, may be empty) into the ragged device layout of
+        nppsim_input_stream_t.  encoding: "actions" (Discrete(6)) or "replay" (.replay input bytes)."""
+        if len(sequences) != self.n_envs:
+            raise ValueError("one sequence per env")
+        lens = np.fromiter((len(q) for q in sequences), dtype=np.int64, count=self.n_envs)
+        off = np.zeros(self.n_envs + 1, dtype=np.int64)
+        np.cumsum(lens, out=off[1:])
+        flat = np.zeros(max(int(off[-1]), 1), dtype=np.uint8)
+        for k, q in enumerate(sequences):
+            if lens[k]:
+                flat[off[k]:off[k + 1]] = np.asarray(q, dtype=np.uint8)
+        sp = NppsimInputStream()
+        data = torch.from_numpy(flat).to(self.device); offset = torch.from_numpy(off).to(self.device)
+        sp.data, sp.offset = data.data_ptr(), offset.data_ptr()
+        sp.encoding = {"actions": STREAM_ACTIONS, "replay": STREAM_REPLAY_BYTES}[encoding]
+        sp.repeat, sp.start_tick = int(repeat), 0
+        sp._keep = (data, offset)                  # the struct only holds raw pointers
+        sp._lens = lens
+        return sp
+
+    def step_stream(self, stream, n_ticks, start_tick=0, stop_on_terminal=False):
+        """nppsim_step_stream: every env runs up to n_ticks ticks of its own stream, from stream tick start_tick."""
+        self._need_maps()
+        stream.start_tick = int(start_tick)
+        with torch.cuda.device(self.device):
+            check(self.L.nppsim_step_stream(C.byref(self._state), C.byref(stream), int(n_ticks), int(bool(stop_on_terminal)),
+                                            C.c_void_p(self.frames_executed.data_ptr()), self._stream()))
+        return self.frames_executed
+
+    def replay_to_checkpoint(self, action_sequences, frame_skip=1, mask=None):
+        """ActionReplayer.replay_to_checkpoint for the batch (action_replayer.py:79-134): reset the masked envs
+        (Simulator.reset), then replay env i's stored Discrete(6) actions, frame_skip ticks each, in ONE launch
+        however ragged the sequences are.  Unmasked envs are left untouched (their sequences are ignored).
+        Returns the ninja positions (x, y) like _get_ninja_position."""
+        self._need_maps()
+        if mask is not None:
+            m = np.asarray(torch.as_tensor(mask).cpu()).astype(bool)
+            action_sequences = [q if m[k] else () for k, q in enumerate(action_sequences)]
+        self.reset(mask)
+        sp = self.make_stream(action_sequences, "actions", max(1, int(frame_skip)))
+        total = int(sp._lens.max()) * sp.repeat
+        if total > 0:
+            self.step_stream(sp, total)
+        return self.ninja_position()
 
     def step_host(self, actions_host, pos_vel_host, state_host, frame_skip=4, stop_on_terminal=True):
         """Host-buffer entry point (nppsim_step_host): numpy uint8 actions in, pos/vel [4,N] f64 and

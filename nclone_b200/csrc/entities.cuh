@@ -607,8 +607,8 @@ DEV void ent_logical_collision(Nin& n, Ctx& c, int id, double& wall_normal) {
             EntS p = ld_ent(c, e.aux);
             // grid_entity[parent.cell].append(parent): next stamp; visible to gathers from the next pass on.
             // parent.cell is kept in the door slot's aux word while the door is outside the grid.
-            DYNI(c, p.dyn, 0) = -(DYNI(c, p.dyn, 2) + 2); DYNI(c, p.dyn, 1) = c.stamp++;
-            c.pending_doors = true;
+            // (a door already listed -- only after the curriculum re-armed a taken switch -- stays listed once)
+            if (DYNI(c, p.dyn, 0) == -1) { DYNI(c, p.dyn, 0) = -(DYNI(c, p.dyn, 2) + 2); DYNI(c, p.dyn, 1) = c.stamp++; c.pending_doors = true; }
             FLAG(c, e.aux) |= FL_CLOSED;                         // parent.switch_hit = True
             c.events |= NPPSIM_EV_EXIT_SWITCH;
             if (c.sw_frame < 0) c.sw_frame = n.i[I_FRAME];

@@ -179,45 +179,19 @@ __global__ void __launch_bounds__(1024) sched_kernel(int32_t* __restrict__ order
 // 2 "right", 3 "down"} is sim._path_straightness_direction (NULL: None everywhere).
 DEV double obs_min(double a, double b) { return b < a ? b : a; }      // Python min(a, b) / max(a, b)
 DEV double obs_max(double a, double b) { return b > a ? b : a; }
-__global__ void __launch_bounds__(128) obs_kernel(nppsim_state_t st, const uint8_t* __restrict__ path_dir, uint8_t* __restrict__ mask_out, float* __restrict__ state_out) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= st.n_envs) return;
+// NPlayHeadless.get_ninja_state for env i -> o[0..39]
+DEV void ninja_state_row(const nppsim_state_t& st, int i, float* __restrict__ o) {
     const size_t N = st.n_envs;
     const double* f = st.nin_f + i; const int32_t* q = st.nin_i + i;
 #define NF_(k) f[(size_t)(k) * N]
 #define NI_(k) q[(size_t)(k) * N]
     const int state = NI_(I_STATE), airborn = NI_(I_AIRBORN), walled = NI_(I_WALLED), jump_input = NI_(I_JUMP_INPUT);
-    const int jump_buffer = NI_(I_JUMP_BUFFER), floor_buffer = NI_(I_FLOOR_BUFFER), wall_buffer = NI_(I_WALL_BUFFER), lp_buffer = NI_(I_LP_BUFFER);
+    const int jump_buffer = NI_(I_JUMP_BUFFER), floor_buffer = NI_(I_FLOOR_BUFFER), wall_buffer = NI_(I_WALL_BUFFER);
     const double wall_normal = NF_(F_WALL_NORMAL), yspeed = NF_(F_YSPEED);
-    if (mask_out) {
-        bool m[6] = {true, true, true, true, true, true};
-        const bool has_active_buffer = (-1 < jump_buffer && jump_buffer < 5) || (-1 < floor_buffer && floor_buffer < 5) ||
-                                       (-1 < wall_buffer && wall_buffer < 5) || (-1 < lp_buffer && lp_buffer < 4);
-        bool jump_useless = false;
-        if (airborn && state != 3) jump_useless = jump_input != 0 ? !has_active_buffer : false;
-        if (jump_useless) { m[3] = false; m[4] = false; m[5] = false; }
-        if (walled) {
-            if (!airborn || state == 5) { if (wall_normal > 0) m[1] = false; else if (wall_normal < 0) m[2] = false; }
-            else {
-                const bool would_trigger_wall_slide = yspeed >= 0;
-                if (wall_normal > 0) { if (!would_trigger_wall_slide) m[1] = false; }
-                else if (wall_normal < 0) { if (!would_trigger_wall_slide) m[2] = false; }
-            }
-        }
-        const int pd = path_dir ? path_dir[i] : 0;
-        if (pd == 1) { m[2] = false; m[3] = false; m[4] = false; m[5] = false; }
-        else if (pd == 2) { m[1] = false; m[3] = false; m[4] = false; m[5] = false; }
-        else if (pd == 3) { m[3] = false; m[4] = false; m[5] = false; }
-        if (!(m[0] || m[1] || m[2] || m[3] || m[4] || m[5])) m[0] = true;
-#pragma unroll
-        for (int k = 0; k < 6; k++) mask_out[(size_t)i * 6 + k] = m[k] ? 1 : 0;
-    }
-    if (!state_out) return;
     const double xspeed = NF_(F_XSPEED), xspeed_old = NF_(F_XSPEED_OLD), yspeed_old = NF_(F_YSPEED_OLD);
     const double fnx = NF_(F_FNX), fny = NF_(F_FNY), gravity = NF_(F_GRAVITY);
     const int floor_count = NI_(I_FLOOR_COUNT), ceiling_count = NI_(I_CEILING_COUNT);
     const int wall_count = 0;                                  // never written by the reference
-    float* o = state_out + (size_t)i * 40;
     const double v2 = SQ(xspeed) + SQ(yspeed);
     const double velocity_magnitude = sqrt(v2);
     o[0] = (float)(obs_min(velocity_magnitude / (MAX_HOR_SPEED * 2), 1.0) * 2 - 1);
@@ -266,6 +240,136 @@ __global__ void __launch_bounds__(128) obs_kernel(nppsim_state_t st, const uint8
 #undef NI_
 }
 
+__global__ void __launch_bounds__(128) obs_kernel(nppsim_state_t st, const uint8_t* __restrict__ path_dir, uint8_t* __restrict__ mask_out, float* __restrict__ state_out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= st.n_envs) return;
+    const size_t N = st.n_envs;
+    const double* f = st.nin_f + i; const int32_t* q = st.nin_i + i;
+#define NF_(k) f[(size_t)(k) * N]
+#define NI_(k) q[(size_t)(k) * N]
+    const int state = NI_(I_STATE), airborn = NI_(I_AIRBORN), walled = NI_(I_WALLED), jump_input = NI_(I_JUMP_INPUT);
+    const int jump_buffer = NI_(I_JUMP_BUFFER), floor_buffer = NI_(I_FLOOR_BUFFER), wall_buffer = NI_(I_WALL_BUFFER), lp_buffer = NI_(I_LP_BUFFER);
+    const double wall_normal = NF_(F_WALL_NORMAL), yspeed = NF_(F_YSPEED);
+    if (mask_out) {
+        bool m[6] = {true, true, true, true, true, true};
+        const bool has_active_buffer = (-1 < jump_buffer && jump_buffer < 5) || (-1 < floor_buffer && floor_buffer < 5) ||
+                                       (-1 < wall_buffer && wall_buffer < 5) || (-1 < lp_buffer && lp_buffer < 4);
+        bool jump_useless = false;
+        if (airborn && state != 3) jump_useless = jump_input != 0 ? !has_active_buffer : false;
+        if (jump_useless) { m[3] = false; m[4] = false; m[5] = false; }
+        if (walled) {
+            if (!airborn || state == 5) { if (wall_normal > 0) m[1] = false; else if (wall_normal < 0) m[2] = false; }
+            else {
+                const bool would_trigger_wall_slide = yspeed >= 0;
+                if (wall_normal > 0) { if (!would_trigger_wall_slide) m[1] = false; }
+                else if (wall_normal < 0) { if (!would_trigger_wall_slide) m[2] = false; }
+            }
+        }
+        const int pd = path_dir ? path_dir[i] : 0;
+        if (pd == 1) { m[2] = false; m[3] = false; m[4] = false; m[5] = false; }
+        else if (pd == 2) { m[1] = false; m[3] = false; m[4] = false; m[5] = false; }
+        else if (pd == 3) { m[3] = false; m[4] = false; m[5] = false; }
+        if (!(m[0] || m[1] || m[2] || m[3] || m[4] || m[5])) m[0] = true;
+#pragma unroll
+        for (int k = 0; k < 6; k++) mask_out[(size_t)i * 6 + k] = m[k] ? 1 : 0;
+    }
+    if (state_out) ninja_state_row(st, i, state_out + (size_t)i * 40);
+#undef NF_
+#undef NI_
+}
+
+// ---- replay -> dataset rows --------------------------------------------------------------
+// The simulator-derived columns of ReplayExecutor._get_raw_observation (replay/replay_executor.py:470-600) for the
+// observation taken after stream tick `obs_tick` (frame_idx = obs_tick - 1, kept iff (frame_idx + 1) % frame_skip == 0,
+// :441), one row per env whose replay is at least that long, at row_off[env] + obs_tick / frame_skip - 1.
+__global__ void __launch_bounds__(128) replay_rows_kernel(nppsim_state_t st, nppsim_input_stream_t in, const int64_t* __restrict__ row_off, int obs_tick,
+                                                          int frame_skip, float* __restrict__ game_state, double* __restrict__ pos,
+                                                          uint8_t* __restrict__ flags, int32_t* __restrict__ frame) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= st.n_envs) return;
+    const long long len = in.offset[i + 1] - in.offset[i];
+    if (obs_tick > len) return;
+    const size_t N = st.n_envs;
+    const size_t row = (size_t)(row_off[i] + obs_tick / frame_skip - 1);
+    const int state = st.nin_i[(size_t)I_STATE * N + i];
+    if (game_state) {
+        float* o = game_state + row * 41;
+        ninja_state_row(st, i, o);
+        const double est = (double)len;                                   // len(_current_input_sequence) or 2000: len >= 1 here
+        const double tr = (est - (double)st.nin_i[(size_t)I_FRAME * N + i]) / est;
+        o[40] = (float)(tr > 0.0 ? tr : 0.0);
+    }
+    if (pos || flags) {
+        const uint8_t* blob = st.map_blob + st.map_off[st.env_map[i]];
+        const NppMapHeader* h = reinterpret_cast<const NppMapHeader*>(blob);
+        const NppStaticEnt* ents = reinterpret_cast<const NppStaticEnt*>(blob + h->off_ents);
+        int sw = -1;                                                      // NPlayHeadless._sim_exit_switch: reversed(entity_dic[3])
+        #pragma unroll 1
+        for (int id = (int)h->n_ent - 1; id >= 0; id--) if (ents[id].kind == NPP_K_EXIT_SWITCH) { sw = id; break; }
+        if (pos) {
+            double* p = pos + row * 6;
+            p[0] = st.nin_f[(size_t)F_XPOS * N + i]; p[1] = st.nin_f[(size_t)F_YPOS * N + i];
+            p[2] = p[3] = p[4] = p[5] = 0.0;                              // (0, 0) without an exit switch (nplay_headless.py:577-616)
+            if (sw >= 0) {
+                const int s = ents[sw].dyn, d = ents[ents[sw].aux].dyn;
+                p[2] = st.dyn_f[(size_t)(s * 4 + 0) * N + i]; p[3] = st.dyn_f[(size_t)(s * 4 + 1) * N + i];
+                p[4] = st.dyn_f[(size_t)(d * 4 + 0) * N + i]; p[5] = st.dyn_f[(size_t)(d * 4 + 1) * N + i];
+            }
+        }
+        if (flags) {
+            uint8_t* fl = flags + row * 4;
+            fl[0] = sw < 0 ? 1 : ((st.ent_flag[(size_t)sw * N + i] & FL_ACTIVE) ? 0 : 1);   // exit_switch_activated (:566-575)
+            fl[1] = state == 8;                                           // ninja_has_won
+            fl[2] = (state == 6 || state == 7);                           // Ninja.has_died
+            const int b = in.data[in.offset[i] + obs_tick - 1];
+            const uint8_t to_action[8] = {0, 3, 2, 5, 1, 4, 0, 0};        // map_input_to_action (replay_executor.py:42-58)
+            fl[3] = b < 8 ? to_action[b] : 0;
+        }
+    }
+    if (frame) frame[row] = obs_tick - 1;
+}
+
+// ---- curriculum repositioning (SURVEY.md 8(b) "mutation from outside tick", 8(f) f2) -----------------------
+// IntermediateGoalManager.apply_to_simulator (gym_environment/reward_calculation/intermediate_goal_manager.py:698-960)
+// for every masked env: the LAST exit switch of entity_dic[3] (reversed() scan, :725-729) moves to switch_xy and is
+// re-armed while sim.frame <= 10 (:843-845); changing cell = list.remove + append, i.e. a fresh insertion stamp
+// (:877-894).  Its parent door moves to door_xy; a door that changes cell leaves grid_entity and is NOT re-added
+// (:938-953) -- it comes back when the switch is taken (entity_exit_switch.py:120).
+__global__ void __launch_bounds__(128) curriculum_kernel(nppsim_state_t st, const uint8_t* __restrict__ mask, const double* __restrict__ switch_xy,
+                                                         const double* __restrict__ door_xy, int32_t* __restrict__ status) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= st.n_envs) return;
+    if (mask && !mask[i]) return;
+    const size_t N = st.n_envs;
+    const uint8_t* blob = st.map_blob + st.map_off[st.env_map[i]];
+    const NppMapHeader* h = reinterpret_cast<const NppMapHeader*>(blob);
+    const NppStaticEnt* ents = reinterpret_cast<const NppStaticEnt*>(blob + h->off_ents);
+    int sw = -1;
+    #pragma unroll 1
+    for (int id = (int)h->n_ent - 1; id >= 0; id--) if (ents[id].kind == NPP_K_EXIT_SWITCH) { sw = id; break; }
+    if (status) status[i] = sw < 0 ? -1 : 0;
+    if (sw < 0) return;                                       // the reference raises RuntimeError (:768-781)
+    double* dynf = st.dyn_f + i; int32_t* dyni = st.dyn_i + i;
+    const int s = ents[sw].dyn, d = ents[ents[sw].aux].dyn;
+    const double sx = switch_xy[i], sy = switch_xy[N + i];
+    dynf[(size_t)(s * 4 + 0) * N] = sx; dynf[(size_t)(s * 4 + 1) * N] = sy;
+    if (st.nin_i[(size_t)I_FRAME * N + i] <= 10) st.ent_flag[(size_t)sw * N + i] |= FL_ACTIVE;
+    int cx = min(max((int)floor(sx / 24), 0), NPP_NCX - 1), cy = min(max((int)floor(sy / 24), 0), NPP_NCY - 1);
+    int cell = cx * NPP_NCY + cy;
+    if (cell != dyni[(size_t)(s * 3 + 0) * N]) {
+        dyni[(size_t)(s * 3 + 0) * N] = cell;
+        dyni[(size_t)(s * 3 + 1) * N] = st.env_i[(size_t)NPPSIM_ENV_STAMP * N + i]++;
+    }
+    const double dx = door_xy[i], dy = door_xy[N + i];
+    dynf[(size_t)(d * 4 + 0) * N] = dx; dynf[(size_t)(d * 4 + 1) * N] = dy;
+    cx = min(max((int)floor(dx / 24), 0), NPP_NCX - 1); cy = min(max((int)floor(dy / 24), 0), NPP_NCY - 1);
+    cell = cx * NPP_NCY + cy;
+    if (cell != dyni[(size_t)(d * 3 + 2) * N]) {              // slot word 2 always holds door.cell; word 0 is -1 outside the grid
+        dyni[(size_t)(d * 3 + 0) * N] = -1;
+        dyni[(size_t)(d * 3 + 2) * N] = cell;
+    }
+}
+
 __global__ void sq_kernel(const double* in, double* out, int n) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = SQ(in[i]);
@@ -281,13 +385,26 @@ int check_state(const nppsim_state_t* st) {
     return 0;
 }
 
+int check_stream(const nppsim_input_stream_t* in) {
+    if (!in || !in->data || !in->offset) return fail(NPPSIM_E_ARG, "input stream (data / offset) is NULL");
+    if (in->repeat < 1) return fail(NPPSIM_E_ARG, "stream repeat must be >= 1");
+    if (in->start_tick < 0) return fail(NPPSIM_E_ARG, "stream start_tick must be >= 0");
+    if (in->encoding != NPPSIM_STREAM_ACTIONS && in->encoding != NPPSIM_STREAM_REPLAY_BYTES) return fail(NPPSIM_E_ARG, "unknown stream encoding");
+    return 0;
+}
+
 int launch_step(const nppsim_state_t* st, const int8_t* hor, const int8_t* jump, const uint8_t* actions, int input_ticks, int n_ticks,
-                const int32_t* tick_limit, int stop_on_terminal, int32_t* frames_executed, void* stream) {
+                const int32_t* tick_limit, int stop_on_terminal, int32_t* frames_executed, void* stream,
+                const nppsim_input_stream_t* in = nullptr) {
     int rc = check_state(st);
     if (rc) return rc;
     if (n_ticks <= 0) return fail(NPPSIM_E_ARG, "n_ticks must be positive");
-    if (!actions && (!hor || !jump)) return fail(NPPSIM_E_ARG, "inputs are NULL");
-    if (!actions && !(input_ticks == 1 || input_ticks == n_ticks)) return fail(NPPSIM_E_ARG, "input_ticks must be 1 or n_ticks");
+    nppsim_input_stream_t sp;
+    memset(&sp, 0, sizeof(sp));
+    sp.repeat = 1;
+    if (in) sp = *in;
+    if (!in && !actions && (!hor || !jump)) return fail(NPPSIM_E_ARG, "inputs are NULL");
+    if (!in && !actions && !(input_ticks == 1 || input_ticks == n_ticks)) return fail(NPPSIM_E_ARG, "input_ticks must be 1 or n_ticks");
     const int block = STEP_BLOCK;
     const int grid = (st->n_envs + block - 1) / block;
     // shared-memory carve-out: room for the two blocks per SM the register file admits and not more -- the rest
@@ -303,8 +420,8 @@ int launch_step(const nppsim_state_t* st, const int8_t* hor, const int8_t* jump,
     (void)carveout_set;
     // kind_mask == 0: census unknown (older callers) -> the full kernel
     const bool basic = st->kind_mask != 0 && (st->kind_mask & ~NPP_BASIC_MASK) == 0 && !g_force_full;
-    if (basic) sim_basic::step_kernel<<<grid, block, STEP_SMEM, (cudaStream_t)stream>>>(*st, hor, jump, actions, input_ticks, n_ticks, tick_limit, stop_on_terminal, frames_executed);
-    else sim_full::step_kernel<<<grid, block, STEP_SMEM, (cudaStream_t)stream>>>(*st, hor, jump, actions, input_ticks, n_ticks, tick_limit, stop_on_terminal, frames_executed);
+    if (basic) sim_basic::step_kernel<<<grid, block, STEP_SMEM, (cudaStream_t)stream>>>(*st, hor, jump, actions, input_ticks, n_ticks, tick_limit, stop_on_terminal, frames_executed, sp);
+    else sim_full::step_kernel<<<grid, block, STEP_SMEM, (cudaStream_t)stream>>>(*st, hor, jump, actions, input_ticks, n_ticks, tick_limit, stop_on_terminal, frames_executed, sp);
     g_launches++;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_fail(e, "step_kernel launch");
@@ -396,6 +513,19 @@ int nppsim_observe(const nppsim_state_t* st, const uint8_t* path_dir, uint8_t* m
     return 0;
 }
 
+int nppsim_set_exit_positions(const nppsim_state_t* st, const uint8_t* mask, const double* switch_xy, const double* door_xy,
+                              int32_t* status, void* stream) {
+    g_err[0] = 0;
+    int rc = check_state(st);
+    if (rc) return rc;
+    if (!switch_xy || !door_xy) return fail(NPPSIM_E_ARG, "switch_xy / door_xy is NULL");
+    curriculum_kernel<<<(st->n_envs + 127) / 128, 128, 0, (cudaStream_t)stream>>>(*st, mask, switch_xy, door_xy, status);
+    g_launches++;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "curriculum_kernel launch");
+    return 0;
+}
+
 int nppsim_step(const nppsim_state_t* st, const int8_t* hor, const int8_t* jump, int32_t input_ticks, int32_t n_ticks,
                 const int32_t* tick_limit, int32_t stop_on_terminal, int32_t* frames_executed, void* stream) {
     g_err[0] = 0;
@@ -407,6 +537,30 @@ int nppsim_step_actions(const nppsim_state_t* st, const uint8_t* actions, int32_
     g_err[0] = 0;
     if (!actions) return fail(NPPSIM_E_ARG, "actions is NULL");
     return launch_step(st, nullptr, nullptr, actions, 1, n_ticks, nullptr, stop_on_terminal, frames_executed, stream);
+}
+
+int nppsim_step_stream(const nppsim_state_t* st, const nppsim_input_stream_t* in, int32_t n_ticks, int32_t stop_on_terminal,
+                       int32_t* frames_executed, void* stream) {
+    g_err[0] = 0;
+    int rc = check_stream(in);
+    if (rc) return rc;
+    return launch_step(st, nullptr, nullptr, nullptr, 1, n_ticks, nullptr, stop_on_terminal, frames_executed, stream, in);
+}
+
+int nppsim_replay_rows(const nppsim_state_t* st, const nppsim_input_stream_t* in, const int64_t* row_off, int32_t obs_tick,
+                       int32_t frame_skip, float* game_state, double* pos, uint8_t* flags, int32_t* frame, void* stream) {
+    g_err[0] = 0;
+    int rc = check_state(st);
+    if (rc) return rc;
+    rc = check_stream(in);
+    if (rc) return rc;
+    if (in->encoding != NPPSIM_STREAM_REPLAY_BYTES || in->repeat != 1) return fail(NPPSIM_E_ARG, "replay rows need a replay-byte stream with repeat 1");
+    if (!row_off || frame_skip < 1 || obs_tick < 1 || obs_tick % frame_skip != 0) return fail(NPPSIM_E_ARG, "bad row_off / frame_skip / obs_tick");
+    replay_rows_kernel<<<(st->n_envs + 127) / 128, 128, 0, (cudaStream_t)stream>>>(*st, *in, row_off, obs_tick, frame_skip, game_state, pos, flags, frame);
+    g_launches++;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "replay_rows_kernel launch");
+    return 0;
 }
 
 int nppsim_step_host(const nppsim_state_t* st, const uint8_t* actions_host, uint8_t* actions_dev, int32_t n_ticks,

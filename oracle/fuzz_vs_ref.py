@@ -49,8 +49,29 @@ def generated_map(category, seed):
     return list(map_gen.map_data())
 
 
+def curriculum_moves(rng, path_xy, T):
+    """Curriculum repositioning events for a trajectory whose un-moved ninja path is path_xy [T+1, 2]: the switch
+    (and then the door) are put ON the path the ninja is about to walk, so the moved entities are actually
+    touched; some events come mid-episode (the reference warns but still moves, intermediate_goal_manager.py:843-856)."""
+    def on_path(t_lo):
+        t = rng.randrange(min(t_lo, T), T + 1)
+        return float(path_xy[t, 0]) + rng.uniform(-8, 8), float(path_xy[t, 1]) + rng.uniform(-8, 8), t
+    sx, sy, ts = on_path(5)
+    dx, dy, _ = on_path(ts)
+    moves = [(0, sx, sy, dx, dy)]
+    if rng.random() < 0.5:
+        t = rng.choice((1, 3, 9, 10, 11, 40, 120))
+        if t < T:
+            sx, sy, ts = on_path(t)
+            dx, dy, _ = on_path(rng.choice((t, ts)))
+            moves.append((t, sx, sy, dx, dy))
+    return moves
+
+
 def job(args):
     kind, a, b, episodes, frames = args
+    curriculum = kind.endswith("+c")
+    kind = kind[:-2] if curriculum else kind
     try:
         if kind == "gen":
             md = generated_map(a, b)
@@ -63,8 +84,22 @@ def job(args):
         for ep in range(episodes):
             rng = random.Random(zlib.crc32(f"{name}:{ep}".encode()))
             hor, jump = random_inputs(rng, frames)
-            ref = refdump.run_trajectory(md, hor, jump)
-            orc = oracle.run_trajectory(md, hor, jump)
+            moves = ()
+            if curriculum:
+                base = oracle.run_trajectory(md, hor, jump)
+                moves = curriculum_moves(rng, base["nin_f"][:, :2], frames)
+            try:
+                ref = refdump.run_trajectory(md, hor, jump, moves=moves)
+            except RuntimeError:
+                if not curriculum:
+                    raise
+                try:                      # level without an exit switch: both sides must refuse
+                    oracle.run_trajectory(md, hor, jump, moves=moves)
+                    bad.append((name, ep, -1))
+                except RuntimeError:
+                    pass
+                continue
+            orc = oracle.run_trajectory(md, hor, jump, moves=moves)
             nframes += frames
             if not np.array_equal(ref["hash"], orc["hash"]):
                 t = int(np.argmax(ref["hash"] != orc["hash"]))
@@ -82,16 +117,17 @@ def main():
     ap.add_argument("--replay-maps", type=int, default=130)
     ap.add_argument("--procs", type=int, default=os.cpu_count())
     ap.add_argument("--seed-base", type=int, default=9000)
+    ap.add_argument("--curriculum", action="store_true", help="with curriculum exit switch / door repositioning events")
     a = ap.parse_args()
     refdump.import_reference()
     from nclone.map_generation.generator_configs import CATEGORIES  # noqa
     jobs = []
     for cat in CATEGORIES:
         for s in range(a.maps_per_category):
-            jobs.append(("gen", cat, a.seed_base + s, a.episodes, a.frames))
+            jobs.append(("gen" + ("+c" if a.curriculum else ""), cat, a.seed_base + s, a.episodes, a.frames))
     files = sorted(glob.glob(os.path.join(refdump.REF_ROOT, "bc_replays", "*.replay")))[:a.replay_maps]
     for f in files:
-        jobs.append(("replay", f, 0, a.episodes, a.frames))
+        jobs.append(("replay" + ("+c" if a.curriculum else ""), f, 0, a.episodes, a.frames))
     oracle.build()
     with mp.Pool(a.procs) as pool:
         res = pool.map(job, jobs, chunksize=1)

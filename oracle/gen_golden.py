@@ -29,7 +29,7 @@ import numpy as np
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from oracle import schema, refdump  # noqa: E402
-from oracle.fuzz_vs_ref import generated_map, random_inputs  # noqa: E402
+from oracle.fuzz_vs_ref import generated_map, random_inputs, curriculum_moves  # noqa: E402
 
 OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
 
@@ -55,8 +55,43 @@ def pack(trajs):
     return d
 
 
+def curriculum():
+    """tests/golden/curriculum.npz: random-action episodes in which the curriculum's
+    IntermediateGoalManager.apply_to_simulator (the reference's own code, see refdump.apply_curriculum) moves the
+    exit switch and door onto the ninja's path -- at load and, in half the episodes, again mid-episode.
+    Extra arrays: mv_off [n+1], mv [*, 5] = (tick before which the move is applied, sx, sy, dx, dy)."""
+    refdump.import_reference()
+    from nclone.map_generation.generator_configs import CATEGORIES  # noqa
+    files = sorted(glob.glob(os.path.join(refdump.REF_ROOT, "bc_replays", "*.replay")))
+    sources = [(f"gen/{cat}/{41000 + s}", generated_map(cat, 41000 + s)) for cat in CATEGORIES for s in range(2)]
+    sources += [(f"rand/{os.path.basename(f)[:-7]}", list(schema.parse_replay(open(f, "rb").read())[0])) for f in files[::13]]
+    trajs, touched = [], 0
+    for name, md in sources:
+        for ep in range(2):
+            rng = random.Random(zlib.crc32(f"{name}:{ep}".encode()))
+            hor, jump = random_inputs(rng, 300)
+            base = refdump.run_trajectory(md, hor, jump)
+            moves = curriculum_moves(rng, base["nin_f"][:, :2], 300)
+            try:
+                rec = refdump.run_trajectory(md, hor, jump, full=True, moves=moves)
+            except RuntimeError:
+                continue                      # level without an exit switch
+            touched += int(not np.array_equal(rec["hash"][1:], base["hash"][1:]) and (rec["ent_i"][-1][:, 2] == 0).any())
+            trajs.append(dict(name=f"{name}/{ep}", map_data=np.asarray(md, dtype=np.float64), hor=hor, jump=jump, rec=rec,
+                              moves=np.asarray(moves, dtype=np.float64)))
+    d = pack(trajs)
+    d["mv_off"] = np.cumsum([0] + [len(t["moves"]) for t in trajs]).astype(np.int64)
+    d["mv"] = np.concatenate([t["moves"] for t in trajs])
+    np.savez_compressed(os.path.join(OUT, "curriculum.npz"), **d)
+    won = int((d["final_nin_i"][:, 0] == 8).sum())
+    print(f"curriculum: {len(trajs)} episodes, {len(d['hor'])} frames, {touched} with an entity taken after a move, {won} won;",
+          os.path.getsize(os.path.join(OUT, "curriculum.npz")) // 1024, "KiB")
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
+    if "--curriculum-only" in sys.argv:
+        return curriculum()
     refdump.import_reference()
     # ---- bc_replays ---------------------------------------------------------
     files = sorted(glob.glob(os.path.join(refdump.REF_ROOT, "bc_replays", "*.replay")))
@@ -108,6 +143,7 @@ def main():
     print(f"generated: {len(trajs)} episodes, {len(d['hor'])} frames")
     for n in ("bc_replays.npz", "generated.npz"):
         print(n, os.path.getsize(os.path.join(OUT, n)) // 1024, "KiB")
+    curriculum()
 
 
 if __name__ == "__main__":

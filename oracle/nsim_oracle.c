@@ -1546,6 +1546,34 @@ int osim_fast_reset(OSim *S) {
     return 0;
 }
 
+/* IntermediateGoalManager.apply_to_simulator
+   (gym_environment/reward_calculation/intermediate_goal_manager.py:698-960): the curriculum moves the LAST
+   EntityExitSwitch of entity_dic[3] (reversed() scan, :725-729) and its parent door.  Returns -1 when the
+   level has no exit switch (the reference raises RuntimeError, :768-781). */
+int osim_apply_curriculum(OSim *S, double sx, double sy, double dx, double dy) {
+    int sw = -1;
+    for (int k = S->ndic - 1; k >= 0; k--) if (S->ents[S->dic_order[k]].kind == K_EXIT_SWITCH) { sw = S->dic_order[k]; break; }
+    if (sw < 0) return -1;
+    Ent *e = &S->ents[sw];
+    e->xpos = sx; e->ypos = sy;                                  /* :810-811 */
+    if (S->frame <= 10) e->active = 1;                           /* :843-845 */
+    int cx = clampi(ifloor(sx / 24), 0, 43), cy = clampi(ifloor(sy / 24), 0, 24);   /* :877-880 */
+    if (cx != e->cellx || cy != e->celly) {                      /* :881-894 */
+        iv_remove(&S->grid[e->cellx][e->celly], sw);
+        e->cellx = cx; e->celly = cy;
+        iv_push(&S->grid[cx][cy], sw);
+    }
+    Ent *d = &S->ents[e->parent];                                /* :928-960: the door is re-celled but never added */
+    d->xpos = dx; d->ypos = dy;
+    cx = clampi(ifloor(dx / 24), 0, 43); cy = clampi(ifloor(dy / 24), 0, 24);
+    if (cx != d->cellx || cy != d->celly) {
+        iv_remove(&S->grid[d->cellx][d->celly], e->parent);
+        iv_remove(&S->grid[cx][cy], e->parent);
+        d->cellx = cx; d->celly = cy;
+    }
+    return 0;
+}
+
 /* Simulator.tick: nsim.py:221-292 */
 void osim_tick(OSim *S, int hor_input, int jump_input) {
     Ninja *n = &S->ninja;

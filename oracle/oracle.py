@@ -42,6 +42,8 @@ def lib():
         L.osim_reset.argtypes = [C.c_void_p]; L.osim_reset.restype = C.c_int
         L.osim_fast_reset.argtypes = [C.c_void_p]; L.osim_fast_reset.restype = C.c_int
         L.osim_tick.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.osim_apply_curriculum.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_double]
+        L.osim_apply_curriculum.restype = C.c_int
         L.osim_num_entities.argtypes = [C.c_void_p]; L.osim_num_entities.restype = C.c_int
         L.osim_num_segments.argtypes = [C.c_void_p]; L.osim_num_segments.restype = C.c_int
         L.osim_events.argtypes = [C.c_void_p]; L.osim_events.restype = C.c_int
@@ -88,6 +90,11 @@ class OracleSim:
 
     def fast_reset(self):
         self.L.osim_fast_reset(self.h)
+
+    def apply_curriculum(self, switch_xy, door_xy):
+        """IntermediateGoalManager.apply_to_simulator (intermediate_goal_manager.py:698-960)."""
+        if self.L.osim_apply_curriculum(self.h, float(switch_xy[0]), float(switch_xy[1]), float(door_xy[0]), float(door_xy[1])):
+            raise RuntimeError("No EntityExitSwitch found in entity_dic[3]")
 
     def tick(self, hor, jump):
         self.L.osim_tick(self.h, int(hor), int(jump))
@@ -141,15 +148,26 @@ class OracleSim:
         return counts, present, segs, hor, ver
 
 
-def run_trajectory(map_data, hor, jump):
-    """Same return shape as refdump.run_trajectory (frame 0 = after load)."""
+def run_trajectory(map_data, hor, jump, moves=()):
+    """Same return shape as refdump.run_trajectory (frame 0 = after load).  moves: (t, sx, sy, dx, dy) tuples,
+    apply_curriculum before tick t (t = 0: right after load, i.e. before the frame-0 record)."""
     s = OracleSim()
     s.load(map_data)
     T = len(hor)
-    nf0, ni0, ef0, ei0 = s.state()
-    nf, ni, ef, ei = s.run(hor, jump)
-    NF = np.concatenate([nf0[None], nf]); NI = np.concatenate([ni0[None], ni])
-    EF = np.concatenate([ef0[None], ef]); EI = np.concatenate([ei0[None], ei])
+    cuts = sorted(set(int(m[0]) for m in moves if 0 < m[0] < T))
+    for m in moves:
+        if m[0] == 0:
+            s.apply_curriculum(m[1:3], m[3:5])
+    recs = [tuple(a[None] for a in s.state())]
+    t0 = 0
+    for t1 in cuts + [T]:
+        if t1 > t0:
+            recs.append(s.run(hor[t0:t1], jump[t0:t1]))
+        for m in moves:
+            if m[0] == t1 and t1 < T:
+                s.apply_curriculum(m[1:3], m[3:5])
+        t0 = t1
+    NF, NI, EF, EI = (np.concatenate([r[k] for r in recs]) for k in range(4))
     H = np.array([schema.state_hash(NF[t], NI[t], EF[t], EI[t]) for t in range(T + 1)], dtype=np.uint64)
     return {"nin_f": NF, "nin_i": NI, "ent_f": EF, "ent_i": EI, "hash": H}
 

@@ -98,11 +98,41 @@ def canonical(sim):
     return nf, ni, ef, ei
 
 
-def run_trajectory(map_data, hor, jump, full=False):
+_IGM = None
+
+
+def apply_curriculum(sim, switch_xy, door_xy):
+    """Run the reference's own IntermediateGoalManager.apply_to_simulator
+    (gym_environment/reward_calculation/intermediate_goal_manager.py:698-960) on `sim` with the given target
+    positions.  The module is loaded by path (its package __init__ chain needs gymnasium); `self` is a stand-in
+    that only answers the two position getters and the fields the method logs."""
+    global _IGM
+    if _IGM is None:
+        import importlib.util
+        import logging
+        p = os.path.join(REF_ROOT, "nclone", "gym_environment", "reward_calculation", "intermediate_goal_manager.py")
+        spec = importlib.util.spec_from_file_location("_ref_intermediate_goal_manager", p)
+        _IGM = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(_IGM)
+        _IGM.logger.setLevel(logging.CRITICAL)
+    from types import SimpleNamespace
+    fake = SimpleNamespace(
+        get_curriculum_switch_position=lambda: (switch_xy[0], switch_xy[1]),
+        get_curriculum_exit_position=lambda: (door_xy[0], door_xy[1]),
+        state=SimpleNamespace(unified_stage=0), config=SimpleNamespace(stage_distance_interval=100.0),
+        _spawn_to_switch_distance=0.0, _combined_distance=0.0)
+    _IGM.IntermediateGoalManager.apply_to_simulator(fake, sim)
+
+
+def run_trajectory(map_data, hor, jump, full=False, moves=()):
     """Tick the reference through (hor[t], jump[t]) and return per-frame records.
-    Frame 0 is the state right after load()."""
+    Frame 0 is the state right after load().  moves: (t, sx, sy, dx, dy) tuples -- the curriculum's
+    apply_to_simulator before tick t (t = 0: before the frame-0 record)."""
     sim = new_sim(map_data)
     T = len(hor)
+    for m in moves:
+        if m[0] == 0:
+            apply_curriculum(sim, m[1:3], m[3:5])
     nf0, ni0, ef0, ei0 = canonical(sim)
     NF = np.zeros((T + 1, schema.NF)); NI = np.zeros((T + 1, schema.NI), dtype=np.int64)
     H = np.zeros(T + 1, dtype=np.uint64)
@@ -112,6 +142,9 @@ def run_trajectory(map_data, hor, jump, full=False):
     if full:
         EFs.append(ef0); EIs.append(ei0)
     for t in range(T):
+        for m in moves:
+            if m[0] == t and t > 0:
+                apply_curriculum(sim, m[1:3], m[3:5])
         sim.tick(int(hor[t]), int(jump[t]))
         nf, ni, ef, ei = canonical(sim)
         NF[t + 1], NI[t + 1] = nf, ni

@@ -30,7 +30,10 @@ class Golden:
         f0, f1 = d["frame_off"][i], d["frame_off"][i + 1]
         i0, i1 = d["inp_off"][i], d["inp_off"][i + 1]
         e0, e1 = d["ent_off"][i], d["ent_off"][i + 1]
-        return dict(name=self.names[i], map_data=d["map_data"][m0:m1].astype(np.float64),
+        moves = ()
+        if "mv_off" in d:
+            moves = [tuple(r) for r in d["mv"][d["mv_off"][i]:d["mv_off"][i + 1]]]
+        return dict(name=self.names[i], moves=moves, map_data=d["map_data"][m0:m1].astype(np.float64),
                     hor=d["hor"][i0:i1], jump=d["jump"][i0:i1],
                     pv=d["pv"][f0:f1], state=d["state"][f0:f1], hash=d["hash"][f0:f1],
                     final_nin_f=d["final_nin_f"][i], final_nin_i=d["final_nin_i"][i],
@@ -45,3 +48,8 @@ def golden_replays():
 @pytest.fixture(scope="session")
 def golden_generated():
     return Golden(os.path.join(GOLDEN, "generated.npz"))
+
+
+@pytest.fixture(scope="session")
+def golden_curriculum():
+    return Golden(os.path.join(GOLDEN, "curriculum.npz"))

@@ -26,6 +26,16 @@ def _run_batch_vs_golden(G, idx):
     hor_d = torch.from_numpy(hor).cuda(); jump_d = torch.from_numpy(jump).cuda()
     bad = []
     frames = 0
+
+    def apply_moves(f):          # curriculum fixtures: apply_to_simulator before tick f for the envs that have one
+        hit = [(k, m) for k, t in enumerate(trajs) for m in t["moves"] if int(m[0]) == f]
+        if hit:
+            sxy = np.zeros((2, N)); dxy = np.zeros((2, N)); mask = np.zeros(N, dtype=np.uint8)
+            for k, m in hit:
+                sxy[:, k] = m[1:3]; dxy[:, k] = m[3:5]; mask[k] = 1
+            sim.set_exit_positions(sxy, dxy, mask)
+
+    apply_moves(0)
     recs = sim.canonical_state()
     for k in range(N):
         if schema.state_hash(*recs[k]) != trajs[k]["hash"][0]:
@@ -33,6 +43,8 @@ def _run_batch_vs_golden(G, idx):
     alive = np.ones(N, dtype=bool)
     for f in range(T):
         limit = (lens > f).astype(np.int32)
+        if f > 0:
+            apply_moves(f)
         sim.tick(hor_d[f], jump_d[f], n_ticks=1, tick_limit=limit)
         ids = np.nonzero((lens > f) & alive)[0]
         recs = sim.canonical_state(ids)
@@ -59,6 +71,30 @@ def test_generated_maps_random_actions_bit_exact(golden_generated):
     frames, bad, _, _ = _run_batch_vs_golden(golden_generated, range(len(golden_generated)))
     assert not bad, f"{len(bad)} episodes differ; first: {bad[:5]}"
     assert frames == 40800
+
+
+def test_curriculum_repositioning_bit_exact(golden_curriculum, golden_replays):
+    """SURVEY 8(b) "mutation from outside tick": nppsim_set_exit_positions against the reference's own
+    IntermediateGoalManager.apply_to_simulator (fixtures from the unmodified reference), every frame, full state."""
+    import torch
+    from nclone_b200 import BatchedSimulator
+    frames, bad, sim, trajs = _run_batch_vs_golden(golden_curriculum, range(len(golden_curriculum)))
+    assert not bad, f"{len(bad)} episodes differ; first: {bad[:5]}"
+    assert frames == 16800
+    # a level without an exit switch refuses, like the reference (RuntimeError)
+    md = golden_replays.traj(0)["map_data"].copy(); md[1235:] = 0
+    one = BatchedSimulator(1); one.load_maps([md])
+    with pytest.raises(RuntimeError):
+        one.set_exit_positions(torch.zeros(2, 1, dtype=torch.float64), torch.zeros(2, 1, dtype=torch.float64))
+    # reset restores the level's own positions
+    first = golden_curriculum.traj(0)
+    two = BatchedSimulator(1); two.load_maps([first["map_data"]])
+    before = two.canonical_state()
+    m = first["moves"][0]
+    two.set_exit_positions(np.array([[m[1]], [m[2]]]), np.array([[m[3]], [m[4]]]))
+    assert schema.state_hash(*two.canonical_state()[0]) == first["hash"][0]
+    two.reset()
+    assert schema.state_hash(*two.canonical_state()[0]) == schema.state_hash(*before[0])
 
 
 def test_first_replay_known_answer(golden_replays):
@@ -324,3 +360,68 @@ def test_observation_primitives_vs_reference():
             worst = max(worst, float(err.max()))
             assert err.max() <= 1.2e-7, (k, f, int(err.argmax()), st[k][err.argmax()], want[err.argmax()])
     assert worst <= 1.2e-7
+
+
+def _replay_rows_fixture():
+    import os
+    from conftest import Golden, GOLDEN
+    return dict(np.load(os.path.join(GOLDEN, "replay_rows.npz"))), Golden(os.path.join(GOLDEN, "bc_replays.npz"))
+
+
+def test_replay_dataset_rows_vs_reference():
+    """execute_replays (per-env input-byte streams + nppsim_replay_rows, everything in HBM) against
+    the reference's own ReplayExecutor loop (tests/golden/replay_rows.npz).  Positions, flags, actions, frames and
+    time_remaining bit-exact; the 40 ninja-state floats within one float32 ulp (tolerance 1.2e-7 * max(1, |x|), as
+    in test_observation_primitives_vs_reference: sqrt / atan2 differ from glibc's by <= 2 double ulp)."""
+    from nclone_b200 import execute_replays
+    d, G = _replay_rows_fixture()
+    inp_all, inp_off = G.d["input_bytes"], G.d["inp_off"]
+    replays = [(G.traj(int(i))["map_data"], inp_all[inp_off[i]:inp_off[i + 1]]) for i in d["idx"]]
+    for fs in (1, 4):
+        out = execute_replays(replays, frame_skip=fs)
+        assert np.array_equal(out["row_off"].cpu().numpy(), d[f"row_off_fs{fs}"])
+        assert np.array_equal(out["pos"].cpu().numpy().view(np.int64), d[f"pos_fs{fs}"].view(np.int64))
+        fl = d[f"flags_fs{fs}"]
+        assert np.array_equal(out["switch_activated"].cpu().numpy(), fl[:, 0].astype(bool))
+        assert np.array_equal(out["player_won"].cpu().numpy(), fl[:, 1].astype(bool))
+        assert np.array_equal(out["player_dead"].cpu().numpy(), fl[:, 2].astype(bool))
+        assert np.array_equal(out["action"].cpu().numpy(), fl[:, 3])
+        assert np.array_equal(out["frame"].cpu().numpy(), d[f"frame_fs{fs}"])
+        gs = out["game_state"].cpu().numpy(); want = d[f"game_state_fs{fs}"]
+        assert np.array_equal(gs[:, 40].view(np.int32), want[:, 40].view(np.int32))
+        err = np.abs(gs.astype(np.float64) - want) / np.maximum(1.0, np.abs(want))
+        assert err.max() <= 1.2e-7, (fs, np.unravel_index(err.argmax(), err.shape))
+        assert int(out["player_won"].sum()) > 0
+
+
+def test_checkpoint_replay_vs_reference():
+    """replay_to_checkpoint (reset + ragged per-env action streams, one launch) against the
+    reference's ActionReplayer(frame_skip=4).replay_to_checkpoint.  Every column bit-exact except entity `index`,
+    which keeps counting across reset() on the reference's re-used Simulator (entities.py:213-216)."""
+    import torch
+    from nclone_b200 import BatchedSimulator
+    d, G = _replay_rows_fixture()
+    trajs = [G.traj(int(i)) for i in d["idx"]]
+    N = len(trajs)
+    sim = BatchedSimulator(N)
+    sim.load_maps([t["map_data"] for t in trajs], np.arange(N))
+    rng = np.random.default_rng(3)
+    for _ in range(7):                                   # the envs have been used before the restore
+        sim.step(torch.from_numpy(rng.integers(0, 6, N).astype(np.uint8)).cuda(), 4, False)
+    seqs = [d["ck_actions"][d["ck_off"][k]:d["ck_off"][k + 1]] for k in range(N)]
+    x, y = sim.replay_to_checkpoint(seqs, frame_skip=4)
+    assert np.array_equal(np.stack([x.cpu().numpy(), y.cpu().numpy()], 1).view(np.int64), d["ck_pos"].view(np.int64))
+    assert np.array_equal(sim.frames_executed.cpu().numpy(), np.array([4 * len(q) for q in seqs]))
+    for k, (nf, ni, ef, ei) in enumerate(sim.canonical_state()):
+        e0, e1 = d["ck_ent_off"][k], d["ck_ent_off"][k + 1]
+        assert np.array_equal(nf.view(np.int64), d["ck_nin_f"][k].view(np.int64)) and np.array_equal(ni, d["ck_nin_i"][k]), k
+        assert np.array_equal(ef.view(np.int64), d["ck_ent_f"][e0:e1].view(np.int64)), k
+        keep = [c for c in range(ei.shape[1]) if c != 1]
+        assert np.array_equal(ei[:, keep], d["ck_ent_i"][e0:e1][:, keep]), k
+    # masked restore: only env 0 is touched
+    before = sim.canonical_state()
+    mask = np.zeros(N, dtype=np.uint8); mask[0] = 1
+    sim.replay_to_checkpoint(seqs, frame_skip=4, mask=mask)
+    after = sim.canonical_state()
+    for k in range(N):
+        assert schema.state_hash(*before[k]) == schema.state_hash(*after[k]), k

@@ -10,7 +10,7 @@ from oracle import oracle, schema
 
 
 def _check(traj):
-    rec = oracle.run_trajectory(traj["map_data"], traj["hor"], traj["jump"])
+    rec = oracle.run_trajectory(traj["map_data"], traj["hor"], traj["jump"], moves=traj["moves"])
     bad = np.nonzero(rec["hash"] != traj["hash"])[0]
     assert bad.size == 0, f"{traj['name']}: first differing frame {bad[0]} of {len(traj['hor'])}"
     assert np.array_equal(rec["nin_f"][:, :4].view(np.int64), traj["pv"].view(np.int64))
@@ -49,6 +49,20 @@ def test_oracle_bc_replays_bit_exact(golden_replays):
 def test_oracle_generated_bit_exact(golden_generated):
     frames = sum(_check(golden_generated.traj(i)) for i in range(len(golden_generated)))
     assert frames == 40800
+
+
+def test_oracle_curriculum_repositioning_bit_exact(golden_curriculum):
+    """the reference's IntermediateGoalManager.apply_to_simulator (run unmodified by
+    oracle/gen_golden.py) moves the exit switch / door at load and mid-episode; the restatement must follow."""
+    g = golden_curriculum
+    frames = sum(_check(g.traj(i)) for i in range(len(g)))
+    assert frames == 16800 and len(g) == 56
+    assert sum(len(g.traj(i)["moves"]) > 1 for i in range(len(g))) >= 10      # mid-episode moves are covered
+    s = oracle.OracleSim(); s.load(g.traj(0)["map_data"])
+    md = g.traj(0)["map_data"].copy(); md[1235:] = 0                          # a level without exit switch refuses
+    s2 = oracle.OracleSim(); s2.load(md)
+    with pytest.raises(RuntimeError):
+        s2.apply_curriculum((100.0, 100.0), (200.0, 200.0))
 
 
 def test_pow_is_libm_not_multiply():
@@ -101,3 +115,66 @@ def test_oracle_observation_primitives_match_reference():
             assert np.array_equal(s.action_mask(f % 4), d["mask"][f0 + f]), (src, i, f)
             frames += 1
     assert frames == len(d["mask"]) == 11327
+
+
+def _replay_rows_fixture():
+    import os
+    from conftest import Golden, GOLDEN
+    return dict(np.load(os.path.join(GOLDEN, "replay_rows.npz"))), Golden(os.path.join(GOLDEN, "bc_replays.npz"))
+
+
+def test_oracle_replay_rows_match_reference():
+    """the simulator-derived columns of ReplayExecutor._get_raw_observation, recorded from the
+    reference's own loop (oracle/gen_golden_replay_rows.py), against the restatement -- bit-exact (float32 rows
+    compared after the same float64 -> float32 rounding)."""
+    from nclone_b200.replay import decode_input_byte, INPUT_TO_ACTION
+    d, G = _replay_rows_fixture()
+    inp_all, inp_off = G.d["input_bytes"], G.d["inp_off"]
+    for fs in (1, 4):
+        off = d[f"row_off_fs{fs}"]
+        for k, i in enumerate(d["idx"]):
+            t = G.traj(int(i)); inp = inp_all[inp_off[i]:inp_off[i + 1]]
+            hor, jump = decode_input_byte(inp)
+            assert np.array_equal(hor, t["hor"]) and np.array_equal(jump, t["jump"])
+            s = oracle.OracleSim(); s.load(t["map_data"])
+            row = int(off[k])
+            for f, b in enumerate(inp):
+                s.tick(hor[f], jump[f])
+                if (f + 1) % fs:
+                    continue
+                nf, ni, ef, ei = s.state()
+                gs = np.append(s.ninja_state().astype(np.float32), max(0.0, (len(inp) - ni[schema.NINJA_I.index("frame")]) / len(inp))).astype(np.float32)
+                assert np.array_equal(gs.view(np.int32), d[f"game_state_fs{fs}"][row].view(np.int32)), (fs, i, f)
+                sw = [e for e in range(len(ei)) if ei[e, 0] == 4]
+                pos = [nf[0], nf[1], 0, 0, 0, 0]
+                act = 1
+                if sw:
+                    door = [e for e in range(len(ei)) if ei[e, 0] == 3][len(sw) - 1]     # parent of the last switch
+                    pos[2:] = [ef[sw[-1], 0], ef[sw[-1], 1], ef[door, 0], ef[door, 1]]
+                    act = int(not ei[sw[-1], 2])
+                assert np.array_equal(np.array(pos, dtype=np.float64).view(np.int64), d[f"pos_fs{fs}"][row].view(np.int64)), (fs, i, f)
+                assert list(d[f"flags_fs{fs}"][row]) == [act, int(ni[0] == 8), int(ni[0] in (6, 7)), INPUT_TO_ACTION[b & 7]], (fs, i, f)
+                assert d[f"frame_fs{fs}"][row] == f
+                row += 1
+            assert row == off[k + 1]
+
+
+def test_oracle_checkpoint_replay_matches_reference():
+    """ActionReplayer.replay_to_checkpoint (reset + frame_skip ticks per stored action) run by the
+    reference on re-used Simulators; the oracle's reset() keeps entity_counts the same way, so the whole record matches."""
+    from nclone_b200 import ACTION_TO_INPUTS
+    d, G = _replay_rows_fixture()
+    for k, i in enumerate(d["idx"]):
+        t = G.traj(int(i))
+        s = oracle.OracleSim(); s.load(t["map_data"])
+        for _ in range(5):
+            s.tick(1, 1)
+        s.reset()
+        for a in d["ck_actions"][d["ck_off"][k]:d["ck_off"][k + 1]]:
+            for _ in range(4):
+                s.tick(*ACTION_TO_INPUTS[a])
+        nf, ni, ef, ei = s.state()
+        e0, e1 = d["ck_ent_off"][k], d["ck_ent_off"][k + 1]
+        assert (nf[0], nf[1]) == tuple(d["ck_pos"][k])
+        assert np.array_equal(nf.view(np.int64), d["ck_nin_f"][k].view(np.int64)) and np.array_equal(ni, d["ck_nin_i"][k])
+        assert np.array_equal(ef.view(np.int64), d["ck_ent_f"][e0:e1].view(np.int64)) and np.array_equal(ei, d["ck_ent_i"][e0:e1])
