@@ -116,6 +116,8 @@ def cpu_baseline(arr, lens, threads, target_seconds, seed=99):
     n_steps = 500                                   # agent steps per env: several episodes each
     n_maps = int(min(len(arr), max(threads * 2, target_seconds * rate / (n_steps * FRAME_SKIP))))
     n_maps -= n_maps % threads if n_maps > threads else 0
+    # the level set is finite: once every level is in the sample, lengthen the rollouts instead (about target_seconds of work)
+    n_steps = int(min(20000, max(n_steps, target_seconds * rate / (n_maps * FRAME_SKIP))))
     acts = rng.integers(0, 6, size=(n_maps, n_steps)).astype(np.uint8)
     ticks, secs = oracle.baseline_run(arr[:n_maps], lens[:n_maps], acts, FRAME_SKIP, MAX_FRAMES, threads)
     return ticks / secs, f"{n_maps} envs (first {n_maps} levels of the workload) x {n_steps} agent steps = {ticks} ticks in {secs:.2f} s on {threads} threads"

@@ -12,4 +12,7 @@ def __getattr__(name):
     if name in ("parse_replay", "decode_input_byte", "execute_replays"):
         from . import replay
         return getattr(replay, name)
+    if name == "EnvView":
+        from .env_view import EnvView
+        return EnvView
     raise AttributeError(name)

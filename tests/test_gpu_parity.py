@@ -425,3 +425,42 @@ def test_checkpoint_replay_vs_reference():
     after = sim.canonical_state()
     for k in range(N):
         assert schema.state_hash(*before[k]) == schema.state_hash(*after[k]), k
+
+
+def test_env_view_mirrors_single_env_interface(golden_replays):
+    """EnvView = env i of a batch behind NPlayHeadless's scalar interface.  Env 3 of a batch is driven
+    through view.tick() with a replay's inputs and read through the facade getters; the other envs must not move."""
+    from nclone_b200 import BatchedSimulator, EnvView
+    idx = [0, 7, 14, 40, 77]
+    trajs = [golden_replays.traj(i) for i in idx]
+    sim = BatchedSimulator(len(idx))
+    sim.load_maps([t["map_data"] for t in trajs])
+    k = 3
+    t = trajs[k]
+    others = [schema.state_hash(*r) for r in sim.canonical_state()]
+    v = EnvView(sim, k, map_data=t["map_data"])
+    assert v.ninja_position() == (t["pv"][0, 0], t["pv"][0, 1]) and v.sim.frame == 0
+    assert not v.exit_switch_activated()
+    o = oracle.OracleSim(); o.load(t["map_data"])
+    for f in range(len(t["hor"])):
+        v.tick(int(t["hor"][f]), int(t["jump"][f])); o.tick(int(t["hor"][f]), int(t["jump"][f]))
+        assert v.ninja_position() == (t["pv"][f + 1, 0], t["pv"][f + 1, 1]), f
+        assert v.ninja_velocity() == (t["pv"][f + 1, 2], t["pv"][f + 1, 3]), f
+        assert v.sim.ninja.state == t["state"][f + 1] and v.sim.frame == f + 1
+        if f % 50 == 0:
+            assert v.get_action_mask() == [bool(b) for b in o.action_mask(0)]
+            assert np.abs(v.get_ninja_state() - o.ninja_state()).max() <= 1.2e-7
+    assert v.ninja_has_won() and v.exit_switch_activated() and not v.ninja_has_died()
+    nf, ni, ef, ei = o.state()
+    flat = [e for lst in v.sim.entity_dic.values() for e in lst]
+    assert len(flat) == len(ei)
+    for e, rf, ri in zip(flat, ef, ei):
+        assert (e.type, e.active, e.xpos, e.ypos, e.cell) == (ri[0], bool(ri[2]), rf[0], rf[1], (ri[3], ri[4]))
+    sw = [r for r in range(len(ei)) if ei[r, 0] == 4]
+    assert v.exit_switch_position() == (ef[sw[-1], 0], ef[sw[-1], 1])
+    assert len(v.sim.tile_dic) == 1100 and v.sim.tile_dic[(0, 0)] == 1
+    for j, r in enumerate(sim.canonical_state()):
+        if j != k:
+            assert schema.state_hash(*r) == others[j]
+    v.reset()
+    assert v.ninja_position() == (t["pv"][0, 0], t["pv"][0, 1]) and v.sim.frame == 0
