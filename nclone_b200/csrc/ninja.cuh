@@ -75,7 +75,7 @@ DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
         double dist_sq = dx * dx + dy * dy;
         if (dist_sq < 1e-16) return false;
         double dist = SQRT(dist_sq);
-        double depen_len = NINJA_RADIUS - dist * result;
+        double depen_len = NINJA_RADIUS - (result < 0 ? -dist : dist);     // dist * result, result = +-1: exact either way
         if (depen_len < 0.0000001) return false;
         double inv_dist = DIV(1.0, dist);
         double norm_dx = dx * inv_dist, norm_dy = dy * inv_dist;
@@ -109,6 +109,55 @@ DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
         if (need) need = depen(result, a, b);
     }
     unsigned todo;
+#ifndef NPP_COOP_LEGACY
+    // Cooperative service, uniform: every lane parks its own loop state in shared memory and takes over the served
+    // owner's, so the whole iteration (query + push) runs redundantly on all 32 lanes without a divergent section;
+    // a lone wedged ninja -- the kernel's critical path -- pays per iteration for one broadcast of (a, b, result) only.
+#define COOP_STATE(X) X(0, xpos) X(1, ypos) X(2, xspeed) X(3, yspeed) X(4, n.f[F_XCRUSH]) X(5, n.f[F_YCRUSH]) X(6, n.f[F_CRUSH_LEN]) \
+                      X(7, n.f[F_CEIL_NX]) X(8, n.f[F_CEIL_NY]) X(9, n.f[F_FLOOR_NX]) X(10, n.f[F_FLOOR_NY])
+    int ncoop = 0;
+    #pragma unroll 1
+    while ((todo = __ballot_sync(FULL_MASK, need)) != 0) {
+        const int lane = threadIdx.x & 31;
+        const int o = __ffs(todo) - 1;
+        const int ns = __shfl_sync(FULL_MASK, nseg, o);
+        const SegC g = seg_decode(lane < ns ? wp.lseg[o][lane] : 0u);
+        const bool pushed_own = pushed;
+#define COOP_PARK(k, v) coop_slot(wp, k, lane) = v;
+#define COOP_TAKE(k, v) v = coop_slot(wp, k, o);
+#define COOP_BACK(k, v) v = coop_slot(wp, k, lane);
+        COOP_STATE(COOP_PARK)
+        wp.seg[lane] = (uint32_t)n.i[I_CEILING_COUNT]; wp.seg[32 + lane] = (uint32_t)n.i[I_FLOOR_COUNT];
+        __syncwarp();
+        COOP_STATE(COOP_TAKE)
+        n.i[I_CEILING_COUNT] = (int)wp.seg[o]; n.i[I_FLOOR_COUNT] = (int)wp.seg[32 + o];
+        #pragma unroll 1
+        for (int it = 2; it < 32; it++) {
+            ncoop++;
+            double a = 0, b = 0; int result = 0;
+            if (ns < 0) {                                    // list overflow: the owner's literal walk, then broadcast
+                double ea = 0, eb = 0;
+                if (lane == o) result = closest_point_exact(c.cell_hdr, c.segs, gx1, gy1, gx2, gy2, xpos, ypos, ea, eb);
+                a = __shfl_sync(FULL_MASK, ea, o); b = __shfl_sync(FULL_MASK, eb, o); result = __shfl_sync(FULL_MASK, result, o);
+            } else {
+                result = warp_closest_uniform(wp, c, o, ns, g, gx1, gy1, gx2, gy2, xpos, ypos, a, b);
+            }
+            if (!depen(result, a, b)) break;                 // uniform: same inputs on every lane
+        }
+        __syncwarp();
+        if (lane != o) {
+            COOP_STATE(COOP_BACK)
+            n.i[I_CEILING_COUNT] = (int)wp.seg[lane]; n.i[I_FLOOR_COUNT] = (int)wp.seg[32 + lane];
+            pushed = pushed_own;
+        } else need = false;
+        __syncwarp();
+    }
+    if ((threadIdx.x & 31) == 0) wp.coop += ncoop;
+#undef COOP_STATE
+#undef COOP_PARK
+#undef COOP_TAKE
+#undef COOP_BACK
+#else
     #pragma unroll 1
     while ((todo = __ballot_sync(FULL_MASK, need)) != 0) {
         const int lane = threadIdx.x & 31;
@@ -140,6 +189,7 @@ DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
         }
         if (lane == o) need = false;
     }
+#endif
     PH_MARK(6)
     if (alive) { n.f[F_XPOS] = xpos; n.f[F_YPOS] = ypos; n.f[F_XSPEED] = xspeed; n.f[F_YSPEED] = yspeed; }
     return !pushed && __double_as_longlong(xpos) == __double_as_longlong(xin) && __double_as_longlong(ypos) == __double_as_longlong(yin);

@@ -454,6 +454,56 @@ DEV int warp_closest_point(WarpPool& wp, const Ctx& c, int o, int ns, const SegC
     return result;
 }
 
+// Uniform variant for the cooperative depenetration loop: (x, y) is the served owner's position, already held by
+// every lane, and the result (a, b, result) is returned to every lane, so that all 32 lanes can run the push
+// redundantly -- no divergent owner-only section, no broadcast of the position and of the continue flag per
+// iteration.  The minimum is usually decided by the high words alone (one redux + one ballot).
+DEV int warp_closest_uniform(WarpPool& wp, const Ctx& c, int o, int ns, const SegC& g, double gx1, double gy1, double gx2, double gy2,
+                             double x, double y, double& pa, double& pb) {
+    const int lane = threadIdx.x & 31;
+    const double inf = __longlong_as_double(0x7ff0000000000000LL);
+    double d2 = inf, a = 0, b = 0; int r = 0; bool ix = false, ok = false;
+    if (lane < ns) ok = closest_eval(g, x, y, d2, a, b, r, ix);
+    if (!ok) d2 = inf;
+    int result = 0;
+    if (__ballot_sync(FULL_MASK, ok && ix) == 0) {
+        const long long bits = __double_as_longlong(d2);
+        const unsigned long long key = (unsigned long long)(bits ^ ((bits >> 63) | (long long)0x8000000000000000ULL));   // monotone in d2
+        const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+        const unsigned mhi = __reduce_min_sync(FULL_MASK, hi);
+        unsigned cand = __ballot_sync(FULL_MASK, ok && hi == mhi);
+        if (cand & (cand - 1)) {                                             // several lanes share the high word: decide on the low one
+            const unsigned mlo = __reduce_min_sync(FULL_MASK, (ok && hi == mhi) ? lo : 0xffffffffu);
+            cand = __ballot_sync(FULL_MASK, ok && hi == mhi && lo == mlo);
+        }
+        if (cand) {                                                          // first minimum in list order (strict < scan, physics.py:170-176)
+            const int w = __ffs(cand) - 1;
+            pa = __shfl_sync(FULL_MASK, a, w); pb = __shfl_sync(FULL_MASK, b, w); result = __shfl_sync(FULL_MASK, r, w);
+        }
+        return result;
+    }
+    wp.res[lane] = d2; wp.ra[lane] = a; wp.rb[lane] = b; wp.aux[lane] = (uint8_t)(!ok ? 2 : ((r < 0 ? 1 : 0) | (ix ? 4 : 0)));
+    __syncwarp();
+    double fa = 0, fb = 0;
+    if (lane == o) {
+        double best = inf, ba = 0, bb = 0;
+        bool uncertain = false, bix = false;
+        #pragma unroll 1
+        for (int k = 0; k < ns; k++) {
+            int ax = wp.aux[k];
+            if (ax == 2) continue;
+            closest_fold(wp.res[k], wp.ra[k], wp.rb[k], (ax & 1) ? -1 : 1, (ax & 4) != 0, best, ba, bb, result, bix, uncertain);
+        }
+        if (uncertain) { double ea, eb; result = closest_point_exact(c.cell_hdr, c.segs, gx1, gy1, gx2, gy2, x, y, ea, eb); fa = ea; fb = eb; }
+        else { fa = ba; fb = bb; }
+    }
+    __syncwarp();
+    pa = __shfl_sync(FULL_MASK, fa, o); pb = __shfl_sync(FULL_MASK, fb, o);
+    return __shfl_sync(FULL_MASK, result, o);
+}
+// stash slots of the cooperative loop: 13 values per lane in the idle tails of the pool's result arrays
+DEV double& coop_slot(WarpPool& wp, int k, int l) { return k < 7 ? wp.res[32 * (k + 1) + l] : wp.ra[32 * (k - 6) + l]; }
+
 // ---- pooled wall test of post_collision (ninja.py:422-441) ----------------------------------------------------
 // Items evaluate the literal reference expression on cheap squares; the owner adds the terms to
 // wall_normal in list order.  `uncertain` when a term's squares were flagged inexact (table path needed).
