@@ -116,8 +116,13 @@ DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
 #define COOP_STATE(X) X(0, xpos) X(1, ypos) X(2, xspeed) X(3, yspeed) X(4, n.f[F_XCRUSH]) X(5, n.f[F_YCRUSH]) X(6, n.f[F_CRUSH_LEN]) \
                       X(7, n.f[F_CEIL_NX]) X(8, n.f[F_CEIL_NY]) X(9, n.f[F_FLOOR_NX]) X(10, n.f[F_FLOOR_NY])
     int ncoop = 0;
+    long long cacc[6] = {0, 0, 0, 0, 0, 0}, ct = 0;
+    (void)cacc; (void)ct;
     #pragma unroll 1
     while ((todo = __ballot_sync(FULL_MASK, need)) != 0) {
+#ifdef NPP_PROFILE
+        ct = clock64(); cacc[4]++;
+#endif
         const int lane = threadIdx.x & 31;
         const int o = __ffs(todo) - 1;
         const int ns = __shfl_sync(FULL_MASK, nseg, o);
@@ -131,18 +136,72 @@ DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
         __syncwarp();
         COOP_STATE(COOP_TAKE)
         n.i[I_CEILING_COUNT] = (int)wp.seg[o]; n.i[I_FLOOR_COUNT] = (int)wp.seg[32 + o];
+        COOP_T(cacc, 5, ct)
         #pragma unroll 1
         for (int it = 2; it < 32; it++) {
             ncoop++;
+#ifdef NPP_COOP_SPEC   // measured slower than the plain uniform loop (the broadcast of the push costs what the select saved); kept for A/B
+            // Speculative push: every lane pushes from ITS segment's closest point while the warp minimum is being
+            // found, then the winner's push is broadcast -- selection (two collectives and a vote) leaves the chain
+            // evaluate -> sqrt -> reciprocal -> position.  Same expressions on the same inputs as depen() above.
+            if (ns >= 0) {
+                const double inf = __longlong_as_double(0x7ff0000000000000LL);
+                double d2 = inf, ca = 0, cb = 0; int r = 1; bool ix = false, ok = false;
+                if (lane < ns) ok = closest_eval_nb(g, xpos, ypos, d2, ca, cb, r, ix);
+                COOP_T(cacc, 0, ct)
+                if (__ballot_sync(FULL_MASK, ok && ix) == 0) {
+                    const unsigned cand = warp_first_min(d2, ok);
+                    double sdx = xpos - ca, sdy = ypos - cb;
+                    if (fabs(sdx) <= 0.0000001) {                  // ninja.py:312-318 band-aid
+                        sdx = 0;
+                        if (xpos == 50.51197510492316 || xpos == 49.23232124849253) sdx = -0x1p-47;
+                        if (xpos == 49.153536108584795) sdx = 0x1p-47;
+                    }
+                    const double dist_sq = sdx * sdx + sdy * sdy;
+                    const double dist = SQRT(dist_sq);
+                    double depen_len = NINJA_RADIUS - (r < 0 ? -dist : dist);
+                    const bool go_own = !(dist_sq < 1e-16) && !(depen_len < 0.0000001);
+                    const double inv_dist = DIV(1.0, dist);
+                    double norm_dx = sdx * inv_dist, norm_dy = sdy * inv_dist;
+                    double nvx = xspeed, nvy = yspeed;
+                    if (xspeed * sdx + yspeed * sdy < 0) {
+                        const double cross_product = xspeed * sdy - yspeed * sdx;
+                        const double inv_dist_sq = inv_dist * inv_dist;
+                        nvx = cross_product * inv_dist_sq * sdy;
+                        nvy = cross_product * inv_dist_sq * (sdx == 0 ? 0.0 : -sdx);
+                    }
+                    int pack = (go_own ? 1 : 0) | (sdy >= -0.0001 ? 2 : 0);
+                    COOP_T(cacc, 2, ct)
+                    if (!cand) break;                              // result == 0: nothing within reach
+                    const int w = __ffs(cand) - 1;
+                    pack = __shfl_sync(FULL_MASK, pack, w);
+                    if (!(pack & 1)) break;
+                    norm_dx = __shfl_sync(FULL_MASK, norm_dx, w); norm_dy = __shfl_sync(FULL_MASK, norm_dy, w);
+                    depen_len = __shfl_sync(FULL_MASK, depen_len, w);
+                    xspeed = __shfl_sync(FULL_MASK, nvx, w); yspeed = __shfl_sync(FULL_MASK, nvy, w);
+                    const double depen_x = norm_dx * depen_len, depen_y = norm_dy * depen_len;
+                    pushed = true;
+                    xpos += depen_x; ypos += depen_y;
+                    n.f[F_XCRUSH] += depen_x; n.f[F_YCRUSH] += depen_y; n.f[F_CRUSH_LEN] += depen_len;
+                    if (pack & 2) { n.i[I_CEILING_COUNT] += 1; n.f[F_CEIL_NX] += norm_dx; n.f[F_CEIL_NY] += norm_dy; }
+                    else { n.i[I_FLOOR_COUNT] += 1; n.f[F_FLOOR_NX] += norm_dx; n.f[F_FLOOR_NY] += norm_dy; }
+                    COOP_T(cacc, 1, ct)
+                    continue;
+                }
+            }
+#endif
             double a = 0, b = 0; int result = 0;
             if (ns < 0) {                                    // list overflow: the owner's literal walk, then broadcast
                 double ea = 0, eb = 0;
                 if (lane == o) result = closest_point_exact(c.cell_hdr, c.segs, gx1, gy1, gx2, gy2, xpos, ypos, ea, eb);
                 a = __shfl_sync(FULL_MASK, ea, o); b = __shfl_sync(FULL_MASK, eb, o); result = __shfl_sync(FULL_MASK, result, o);
             } else {
-                result = warp_closest_uniform(wp, c, o, ns, g, gx1, gy1, gx2, gy2, xpos, ypos, a, b);
+                result = warp_closest_uniform(wp, c, o, ns, g, gx1, gy1, gx2, gy2, xpos, ypos, a, b, cacc, ct);
             }
-            if (!depen(result, a, b)) break;                 // uniform: same inputs on every lane
+            COOP_T(cacc, 1, ct)
+            const bool go = depen(result, a, b);             // uniform: same inputs on every lane
+            COOP_T(cacc, 2, ct)
+            if (!go) break;
         }
         __syncwarp();
         if (lane != o) {
@@ -151,8 +210,12 @@ DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
             pushed = pushed_own;
         } else need = false;
         __syncwarp();
+        COOP_T(cacc, 5, ct)
     }
     if ((threadIdx.x & 31) == 0) wp.coop += ncoop;
+#ifdef NPP_PROFILE
+    if ((threadIdx.x & 31) == 0 && ncoop) { for (int k = 0; k < 6; k++) if (k != 3) atomicAdd(&g_coop_cycles[k], (unsigned long long)cacc[k]); atomicAdd(&g_coop_cycles[3], (unsigned long long)ncoop); }
+#endif
 #undef COOP_STATE
 #undef COOP_PARK
 #undef COOP_TAKE

@@ -128,13 +128,18 @@ __global__ void __launch_bounds__(128) reset_kernel(nppsim_state_t st, const uin
 
 namespace {
 // Longest-first order for the next launch from the costs of this one (one block; nw <= 2^20 / 32).
-// Three classes by cost relative to the mean -- > 3x, > 1.5x, the rest -- placed in that order; inside a
+// Six classes by cost relative to the mean (sched_class), placed in that order; inside a
 // class the order is arbitrary (it only affects scheduling, never results).
+#define SCHED_NCLS 6
+__device__ __forceinline__ int sched_class(unsigned long long v, unsigned long long mean) {
+    // cost relative to the mean: > 24x, > 12x, > 6x, > 3x, > 1.5x, the rest
+    return v > 24 * mean ? 0 : (v > 12 * mean ? 1 : (v > 6 * mean ? 2 : (v > 3 * mean ? 3 : (2 * v > 3 * mean ? 4 : 5))));
+}
 __global__ void __launch_bounds__(1024) sched_kernel(int32_t* __restrict__ order, const uint32_t* __restrict__ cost, int nw) {
     __shared__ unsigned long long s_sum;
-    __shared__ int s_cnt[3], s_pos[3];
+    __shared__ int s_cnt[SCHED_NCLS], s_pos[SCHED_NCLS];
     const int lane = threadIdx.x & 31;
-    if (threadIdx.x == 0) { s_sum = 0; s_cnt[0] = s_cnt[1] = s_cnt[2] = 0; }
+    if (threadIdx.x == 0) { s_sum = 0; for (int k = 0; k < SCHED_NCLS; k++) s_cnt[k] = 0; }
     __syncthreads();
     unsigned long long loc = 0;
     for (int w = threadIdx.x; w < nw; w += blockDim.x) loc += cost[w];
@@ -147,20 +152,18 @@ __global__ void __launch_bounds__(1024) sched_kernel(int32_t* __restrict__ order
     // warp-aggregated counting / placement: one shared-memory atomic per warp and class
     for (int r = 0; r < rounds; r++) {
         const int w = r * blockDim.x + threadIdx.x;
-        const unsigned long long v = w < nw ? cost[w] : 0;
-        const int cls = w < nw ? (v > 3 * mean ? 0 : (2 * v > 3 * mean ? 1 : 2)) : 3;
+        const int cls = w < nw ? sched_class(cost[w], mean) : SCHED_NCLS;
 #pragma unroll
-        for (int k = 0; k < 3; k++) { unsigned m = __ballot_sync(0xffffffffu, cls == k); if (lane == 0 && m) atomicAdd(&s_cnt[k], __popc(m)); }
+        for (int k = 0; k < SCHED_NCLS; k++) { unsigned m = __ballot_sync(0xffffffffu, cls == k); if (lane == 0 && m) atomicAdd(&s_cnt[k], __popc(m)); }
     }
     __syncthreads();
-    if (threadIdx.x == 0) { s_pos[0] = 0; s_pos[1] = s_cnt[0]; s_pos[2] = s_cnt[0] + s_cnt[1]; }
+    if (threadIdx.x == 0) { int p = 0; for (int k = 0; k < SCHED_NCLS; k++) { s_pos[k] = p; p += s_cnt[k]; } }
     __syncthreads();
     for (int r = 0; r < rounds; r++) {
         const int w = r * blockDim.x + threadIdx.x;
-        const unsigned long long v = w < nw ? cost[w] : 0;
-        const int cls = w < nw ? (v > 3 * mean ? 0 : (2 * v > 3 * mean ? 1 : 2)) : 3;
+        const int cls = w < nw ? sched_class(cost[w], mean) : SCHED_NCLS;
 #pragma unroll
-        for (int k = 0; k < 3; k++) {
+        for (int k = 0; k < SCHED_NCLS; k++) {
             unsigned m = __ballot_sync(0xffffffffu, cls == k);
             int base = 0;
             if (lane == 0 && m) base = atomicAdd(&s_pos[k], __popc(m));
@@ -410,7 +413,8 @@ int launch_step(const nppsim_state_t* st, const int8_t* hor, const int8_t* jump,
     // shared-memory carve-out: room for the two blocks per SM the register file admits and not more -- the rest
     // of the 256 KB stays L1 for the level blobs (max-shared left 28 KB of L1: hit rate 40 % instead of 66 %)
     static const bool carveout_set = [] {
-        const int carve = (int)((2 * (STEP_SMEM + 1024) * 100 + 233471) / 233472) + 1;
+        const int resident = STEP_BLOCKS_PER_SM > 2 ? STEP_BLOCKS_PER_SM : 2;
+        const int carve = (int)((resident * (STEP_SMEM + 1024) * 100 + 233471) / 233472) + 1;
         cudaFuncSetAttribute(sim_basic::step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
         cudaFuncSetAttribute(sim_full::step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
         cudaFuncSetAttribute(sim_basic::step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)STEP_SMEM);
@@ -420,8 +424,8 @@ int launch_step(const nppsim_state_t* st, const int8_t* hor, const int8_t* jump,
     (void)carveout_set;
     // kind_mask == 0: census unknown (older callers) -> the full kernel
     const bool basic = st->kind_mask != 0 && (st->kind_mask & ~NPP_BASIC_MASK) == 0 && !g_force_full;
-    if (basic) sim_basic::step_kernel<<<grid, block, STEP_SMEM, (cudaStream_t)stream>>>(*st, hor, jump, actions, input_ticks, n_ticks, tick_limit, stop_on_terminal, frames_executed, sp);
-    else sim_full::step_kernel<<<grid, block, STEP_SMEM, (cudaStream_t)stream>>>(*st, hor, jump, actions, input_ticks, n_ticks, tick_limit, stop_on_terminal, frames_executed, sp);
+    auto kernel = basic ? sim_basic::step_kernel : sim_full::step_kernel;
+    kernel<<<grid, block, STEP_SMEM, (cudaStream_t)stream>>>(*st, hor, jump, actions, input_ticks, n_ticks, tick_limit, stop_on_terminal, frames_executed, sp);
     g_launches++;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_fail(e, "step_kernel launch");
@@ -455,6 +459,16 @@ int nppsim_debug_warp_cycles(unsigned long long* out, unsigned long long* phases
     if (out) cudaMemcpyFromSymbol(out, g_warp_cycles, sizeof(unsigned long long) * n);
     if (phases) cudaMemcpyFromSymbol(phases, g_warp_phase, sizeof(unsigned long long) * n * 4);
     if (reset) cudaMemset((void*)0, 0, 0);
+    return 0;
+}
+int nppsim_debug_warp_span(unsigned long long* out, int n) {
+    cudaDeviceSynchronize();
+    return (int)cudaMemcpyFromSymbol(out, g_warp_span, sizeof(unsigned long long) * n * 2);
+}
+int nppsim_debug_coop_cycles(unsigned long long* out8, int reset) {
+    cudaDeviceSynchronize();
+    if (out8) cudaMemcpyFromSymbol(out8, g_coop_cycles, sizeof(unsigned long long) * 8);
+    if (reset) { unsigned long long z[8] = {0}; cudaMemcpyToSymbol(g_coop_cycles, z, sizeof(z)); }
     return 0;
 }
 int nppsim_debug_phase_cycles(unsigned long long* out16, int reset) {

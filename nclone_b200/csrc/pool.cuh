@@ -16,7 +16,11 @@
 // NPP_PROFILE: per-warp cycle counters per phase (debug builds only; tools/phase_profile.py)
 __device__ unsigned long long g_phase_cycles[16];      // [0..10] cycles per phase, [11..14] event counters, [15] kernel cycles
 __device__ unsigned long long g_warp_cycles[1 << 16];      // per warp: kernel duration of the last launch
+__device__ unsigned long long g_warp_span[1 << 16][2];    // per warp: %globaltimer (ns) at start / end of the last launch
+DEV unsigned long long global_ns() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 __device__ unsigned long long g_warp_phase[1 << 16][4];   // per warp: cycles in entities / sweep / closest / post of the last launch
+__device__ unsigned long long g_coop_cycles[8];        // cooperative depenetration loop: [0] evaluate, [1] select, [2] push, [3] iterations, [4] services, [5] park/take/back
+#define COOP_T(acc, k, t) { long long _n = clock64(); (acc)[k] += _n - (t); (t) = _n; }
 #define PH_COUNT(k) atomicAdd(&g_phase_cycles[k], 1ULL)
 #define PH_T0 long long _q0 = clock64();
 #define PH_ACC(k) { long long _q1 = clock64(); if ((threadIdx.x & 31) == 0) atomicAdd(&g_phase_cycles[k], (unsigned long long)(_q1 - _q0)); _q0 = _q1; }
@@ -27,6 +31,7 @@ __device__ unsigned long long g_warp_phase[1 << 16][4];   // per warp: cycles in
 #define PH_MARK(k)
 #define PH_COUNT(k)
 #define PH_T0
+#define COOP_T(acc, k, t)
 #define PH_ACC(k)
 #endif
 
@@ -454,17 +459,64 @@ DEV int warp_closest_point(WarpPool& wp, const Ctx& c, int o, int ns, const SegC
     return result;
 }
 
+// closest_eval without the early AABB return: the bounds test only gates `ok` and stays off the dependency chain
+// (in the cooperative loop every lane owns one segment, so skipping the arithmetic would save nothing).
+DEV bool closest_eval_nb(const SegC& g, double x, double y, double& d2, double& a, double& b, int& r, bool& ix) {
+    const bool inb = !(g.bx1 < x - NINJA_RADIUS || g.bx0 > x + NINJA_RADIUS || g.by1 < y - NINJA_RADIUS || g.by0 > y + NINJA_RADIUS);
+    const double dx = x - g.x1, dy = y - g.y1;
+    bool back;
+    if (!g.arc) {                                                            // entities.py:43-59
+        double u = div_seglen(dx * g.px + dy * g.py, g.lensq);
+        if (0 > u) u = 0;
+        if (1 < u) u = 1;
+        a = g.x1 + u * g.px; b = g.y1 + u * g.py;
+        back = (dy * g.px - dx * g.py < 0);
+    } else {                                                                 // entities.py:127-157
+        back = false;
+        if (dx * g.px > 0 && dy * g.py > 0) {
+            double dist = SQRT(SQ(dx) + SQ(dy));
+            a = g.x1 + DIV(24.0 * dx, dist); b = g.y1 + DIV(24.0 * dy, dist);
+            back = (g.lensq != 0) ? (dist < 24.0) : (dist > 24.0);
+        } else if (dx * g.px > dy * g.py) { a = g.x1 + 24.0 * g.px; b = g.y1; }
+        else { a = g.x1; b = g.y1 + 24.0 * g.py; }
+    }
+    ix = false;
+    d2 = sq_flag(x - a, ix) + sq_flag(y - b, ix);
+    if (!back) d2 -= 0.1;
+    r = back ? -1 : 1;
+    return inb;
+}
+// First minimum of d2 over the lanes with ok set: ballot of the winner(s) -- 0 when no lane is ok, else the lowest
+// set bit is the reference's strict-< scan result (physics.py:170-176).  Usually one redux on the high words decides.
+DEV unsigned warp_first_min(double d2, bool ok) {
+    const long long bits = __double_as_longlong(d2);
+    const unsigned long long key = (unsigned long long)(bits ^ ((bits >> 63) | (long long)0x8000000000000000ULL));   // monotone in d2
+    const unsigned hi = ok ? (unsigned)(key >> 32) : 0xffffffffu, lo = (unsigned)key;
+    const unsigned mhi = __reduce_min_sync(FULL_MASK, hi);
+    unsigned cand = __ballot_sync(FULL_MASK, ok && hi == mhi);
+    if (cand & (cand - 1)) {
+        const unsigned mlo = __reduce_min_sync(FULL_MASK, (ok && hi == mhi) ? lo : 0xffffffffu);
+        cand = __ballot_sync(FULL_MASK, ok && hi == mhi && lo == mlo);
+    }
+    return cand;
+}
+
 // Uniform variant for the cooperative depenetration loop: (x, y) is the served owner's position, already held by
 // every lane, and the result (a, b, result) is returned to every lane, so that all 32 lanes can run the push
 // redundantly -- no divergent owner-only section, no broadcast of the position and of the continue flag per
 // iteration.  The minimum is usually decided by the high words alone (one redux + one ballot).
 DEV int warp_closest_uniform(WarpPool& wp, const Ctx& c, int o, int ns, const SegC& g, double gx1, double gy1, double gx2, double gy2,
-                             double x, double y, double& pa, double& pb) {
+                             double x, double y, double& pa, double& pb, long long* cacc, long long& ct) {
     const int lane = threadIdx.x & 31;
     const double inf = __longlong_as_double(0x7ff0000000000000LL);
     double d2 = inf, a = 0, b = 0; int r = 0; bool ix = false, ok = false;
+#ifdef NPP_COOP_EVAL_NB
+    if (lane < ns) ok = closest_eval_nb(g, x, y, d2, a, b, r, ix);
+#else
     if (lane < ns) ok = closest_eval(g, x, y, d2, a, b, r, ix);
+#endif
     if (!ok) d2 = inf;
+    COOP_T(cacc, 0, ct)
     int result = 0;
     if (__ballot_sync(FULL_MASK, ok && ix) == 0) {
         const long long bits = __double_as_longlong(d2);

@@ -62,3 +62,23 @@ n_ent = np.array([sim.maps[m].n_ent for m in sim.env_map_host])
 for o in order:
     envs = np.arange(o * 32, min(o * 32 + 32, n_envs))
     print(f"  warp {o}: total {w[o]:,.0f} entities/sweep/closest/post {d[o]} max n_ent in warp {n_ent[envs].max()}")
+
+# ---- timeline of the last launch: who ends the kernel?
+span = np.zeros((nw, 2), dtype=np.uint64)
+lib_.nppsim_debug_warp_span.argtypes = [C.c_void_p, C.c_int]
+lib_.nppsim_debug_warp_span(span.ctypes.data, nw)
+cost = sim.warp_cost.cpu().numpy().astype(np.int64)[:nw] - 1
+t0 = span[:, 0].min()
+st = (span[:, 0] - t0).astype(np.float64) / 1e3; en = (span[:, 1] - t0).astype(np.float64) / 1e3
+print(f"timeline (us from the first warp's start): kernel span {en.max():.1f}; all warps started by {st.max():.1f}; "
+      f"50% / 90% / 99% of warps finished by {np.percentile(en, 50):.1f} / {np.percentile(en, 90):.1f} / {np.percentile(en, 99):.1f}")
+busy = np.sort(en)
+for frac in (0.5, 0.75, 0.9, 0.95, 0.99):
+    t = np.percentile(en, 100 * frac); print(f"  resident warps at t={t:.0f} us: {int(((st <= t) & (en > t)).sum())} of {148 * 8} slots")
+print("  last finishers: (warp group, start us, end us, duration us, cooperative iterations)")
+for o in np.argsort(-en)[:12]:
+    print(f"    {o:6d} {st[o]:8.1f} {en[o]:8.1f} {en[o] - st[o]:8.1f} {cost[o]:6d}")
+long_ = np.argsort(-cost)[:12]
+print("  most cooperative iterations: (warp group, start us, end us, duration us, iterations)")
+for o in long_:
+    print(f"    {o:6d} {st[o]:8.1f} {en[o]:8.1f} {en[o] - st[o]:8.1f} {cost[o]:6d}")

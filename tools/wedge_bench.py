@@ -55,6 +55,19 @@ def main():
             torch.cuda.synchronize()
             if r >= 3:
                 base.append(e0.elapsed_time(e1) * 1000)
+        if hasattr(sim.L, "nppsim_debug_coop_cycles"):          # -DNPP_PROFILE build (NPPSIM_LIB=variants/profile.so)
+            import ctypes as C
+            out = (C.c_ulonglong * 8)()
+            ph = (C.c_ulonglong * 16)()
+            sim.L.nppsim_debug_coop_cycles(None, 1); sim.L.nppsim_debug_phase_cycles(None, 1)
+            restore(); sim.step(a, 4, False); torch.cuda.synchronize()
+            sim.L.nppsim_debug_coop_cycles(out, 0); sim.L.nppsim_debug_phase_cycles(ph, 0)
+            names = {0: "dyn_move", 1: "mines/boost", 2: "dyn_think", 3: "integrate+pre", 4: "substep residue", 5: "sweep", 6: "closest loop",
+                     7: "post residue", 8: "think", 9: "post gather+logical", 10: "post wall", 15: "kernel"}
+            print("  phase cycles (4 warps of the block add up; /4 for the wedge warp's share when the others idle at barriers):")
+            print("   ", ", ".join(f"{names[k]} {ph[k]:,}" for k in sorted(names)))
+            v = list(out); it = max(v[3], 1)
+            print(f"  per iteration (clock64): evaluate {v[0] / it:.0f}, select {v[1] / it:.0f}, push {v[2] / it:.0f}; park/take/back {v[5] / max(v[4], 1):.0f} per service, {v[4]} services, {v[3]} iterations")
         t, b = float(np.median(times)), float(np.median(base))
         print(f"wedge {k}: step {t:.1f} us (rest step {b:.1f} us), {coop} cooperative iterations of {d['cp_calls'][k]} closest-point calls"
               f" -> {(t - b) * sm_mhz / max(coop, 1):.0f} cycles per cooperative iteration at {sm_mhz:.0f} MHz")
