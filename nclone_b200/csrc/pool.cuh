@@ -25,7 +25,7 @@ __device__ unsigned long long g_coop_cycles[8];        // cooperative depenetrat
 #define PH_T0 long long _q0 = clock64();
 #define PH_ACC(k) { long long _q1 = clock64(); if ((threadIdx.x & 31) == 0) atomicAdd(&g_phase_cycles[k], (unsigned long long)(_q1 - _q0)); _q0 = _q1; }
 #define PH_BEGIN long long _ph_t = clock64();
-#define PH_MARK(k) { long long _t2 = clock64(); if ((threadIdx.x & 31) == (__ffs(__activemask()) - 1)) { atomicAdd(&g_phase_cycles[k], (unsigned long long)(_t2 - _ph_t)); int _w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; int _b = (k) <= 3 ? 0 : ((k) == 5 ? 1 : ((k) == 6 ? 2 : (((k) == 9 || (k) == 10) ? 3 : -1))); if (_b >= 0 && _w < (1 << 16)) g_warp_phase[_w][_b] += (unsigned long long)(_t2 - _ph_t); } _ph_t = _t2; }
+#define PH_MARK(k) { long long _t2 = clock64(); if ((threadIdx.x & 31) == (__ffs(__activemask()) - 1)) { atomicAdd(&g_phase_cycles[k], (unsigned long long)(_t2 - _ph_t)); int _w = wp.group; int _b = (k) <= 3 ? 0 : ((k) == 5 ? 1 : ((k) == 6 ? 2 : (((k) == 9 || (k) == 10) ? 3 : -1))); if (_b >= 0 && _w >= 0 && _w < (1 << 16)) g_warp_phase[_w][_b] += (unsigned long long)(_t2 - _ph_t); } _ph_t = _t2; }
 #else
 #define PH_BEGIN
 #define PH_MARK(k)
@@ -61,6 +61,7 @@ struct WarpPool {
     uint8_t own[POOL_CAP], aux[POOL_CAP];
     uint32_t lseg[32][POOL_LCAP];   // per-lane copy of the segments gathered for the current substep (ninja.py:282-285)
     int coop;                       // cooperative depenetration iterations this launch: the warp's cost for longest-first scheduling
+    int group;                      // the env group this warp works on (profile build: per-warp phase attribution)
 };
 
 // ---- gather: the segments of a query box, per lane, in SpatialSegmentIndex.query_region order -----------

@@ -79,6 +79,8 @@ print("  last finishers: (warp group, start us, end us, duration us, cooperative
 for o in np.argsort(-en)[:12]:
     print(f"    {o:6d} {st[o]:8.1f} {en[o]:8.1f} {en[o] - st[o]:8.1f} {cost[o]:6d}")
 long_ = np.argsort(-cost)[:12]
-print("  most cooperative iterations: (warp group, start us, end us, duration us, iterations)")
+print("  most cooperative iterations: (warp group, start us, end us, duration us, iterations; cycles in entities / sweep / closest-point loop / post_collision)")
 for o in long_:
-    print(f"    {o:6d} {st[o]:8.1f} {en[o]:8.1f} {en[o] - st[o]:8.1f} {cost[o]:6d}")
+    print(f"    {o:6d} {st[o]:8.1f} {en[o]:8.1f} {en[o] - st[o]:8.1f} {cost[o]:6d}   {d[o].astype(np.int64)}")
+quiet = np.nonzero(cost == 0)[0]
+print("  warps without cooperative iterations: mean cycles entities / sweep / closest / post:", d[quiet].mean(0).astype(np.int64), "duration us mean", (en - st)[quiet].mean())
