@@ -23,80 +23,95 @@ int cuda_fail(cudaError_t e, const char* what) {
 // mode 0: state right after Simulator.load / reset (nsim.py:62-76; Ninja.__init__ ninja.py:80-196; entity ctors)
 // mode 1: Simulator.fast_reset (nsim.py:78-140): only classes with reset_state() are restored, every
 //         entity (except exit doors) is re-appended to its cell in entity_dic order.
+// One lane owns one env for the test and the ninja record; the entity tables of the envs that do reset (about 1 % per
+// agent step) are then rewritten by the whole warp, entity id = lane, lane + 32, ... (a level has up to a few hundred
+// entities: a per-thread loop over them was 7 % of a step).
 __global__ void __launch_bounds__(128) reset_kernel(nppsim_state_t st, const uint8_t* mask, int mode, int auto_terminal, int max_frames,
                                                      unsigned long long* stats) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= st.n_envs) return;
-    if (mask && !mask[i]) return;
+    const int lane = threadIdx.x & 31;
     const size_t N = st.n_envs;
-    if (auto_terminal) {
+    bool need = i < st.n_envs && !(mask && !mask[i]);
+    if (need && auto_terminal) {
         int s = st.nin_i[I_STATE * N + i], fr = st.nin_i[I_FRAME * N + i];
         bool term = (s == 6 || s == 7 || s == 8), trunc = (max_frames > 0 && fr >= max_frames);
-        if (!term && !trunc) return;
-        if (stats) {
+        need = term || trunc;
+        if (need && stats) {
             atomicAdd(stats + 0, 1ULL);
             if (s == 8) atomicAdd(stats + 1, 1ULL); else if (term) atomicAdd(stats + 2, 1ULL); else atomicAdd(stats + 3, 1ULL);
         }
     }
-    const uint8_t* blob = st.map_blob + st.map_off[st.env_map[i]];
-    const NppMapHeader* h = reinterpret_cast<const NppMapHeader*>(blob);
-    const NppStaticEnt* ents = reinterpret_cast<const NppStaticEnt*>(blob + h->off_ents);
-    double* nf = st.nin_f + i; int32_t* ni = st.nin_i + i; int32_t* envi = st.env_i + i;
-    #pragma unroll 1
-    for (int f = 0; f < NPPSIM_NF; f++) nf[f * N] = 0.0;
-    #pragma unroll 1
-    for (int f = 0; f < NPPSIM_NI; f++) ni[f * N] = 0;
-    nf[F_XPOS * N] = h->spawn_x; nf[F_YPOS * N] = h->spawn_y;
-    nf[F_X_AT_ACTION * N] = h->spawn_x; nf[F_Y_AT_ACTION * N] = h->spawn_y;
-    nf[F_GRAVITY * N] = GRAVITY_FALL; nf[F_DRAG * N] = DRAG_REGULAR; nf[F_FRICTION * N] = FRICTION_GROUND;
-    nf[F_FNY * N] = -1; nf[F_CNY * N] = 1;
-    ni[I_JUMP_BUFFER * N] = -1; ni[I_FLOOR_BUFFER * N] = -1; ni[I_WALL_BUFFER * N] = -1; ni[I_LP_BUFFER * N] = -1;
-    envi[NPPSIM_ENV_STAMP * N] = h->n_ent;
-    envi[NPPSIM_ENV_EVENTS * N] = 0;
-    envi[NPPSIM_ENV_SWFRAME * N] = -1;
-    envi[NPPSIM_ENV_ORDER * N] = mode ? 1 : 0;
-    uint8_t* flag = st.ent_flag + i; double* dynf = st.dyn_f + i; int32_t* dyni = st.dyn_i + i;
-    int hot = 0;   // fast_reset keeps boost pads' is_touching_ninja (no reset_state())
-    #pragma unroll 1
-    for (uint32_t id = 0; id < h->n_ent; id++) {
-        const NppStaticEnt& e = ents[id];
-        int stamp = mode ? (int)id : (int)e.load_order;
-        uint8_t fl = FL_ACTIVE;
-        switch (e.kind) {
-        case NPP_K_MINE: fl |= e.p0; break;
-        case NPP_K_GOLD: break;
-        case NPP_K_BOOST: fl |= FL_IS_BOOST; if (mode) { fl |= flag[id * N] & FL_TOUCH; if (fl & FL_TOUCH) hot++; } break;
-        case NPP_K_DOOR_LOCKED: fl |= FL_CLOSED; break;
-        case NPP_K_DOOR_TRAP: break;                         // starts open (entity_door_trap.py:51-53)
-        case NPP_K_DOOR_REGULAR:
-            if (mode == 0) { fl |= FL_CLOSED; dyni[(e.dyn * 3 + 0) * N] = -1; dyni[(e.dyn * 3 + 1) * N] = stamp; dyni[(e.dyn * 3 + 2) * N] = 256; }
-            else fl |= flag[id * N] & FL_CLOSED;
-            break;
-        case NPP_K_EXIT:
-            dynf[(e.dyn * 4 + 0) * N] = e.x; dynf[(e.dyn * 4 + 1) * N] = e.y; dynf[(e.dyn * 4 + 2) * N] = 0; dynf[(e.dyn * 4 + 3) * N] = 0;
-            dyni[(e.dyn * 3 + 0) * N] = -1; dyni[(e.dyn * 3 + 1) * N] = stamp; dyni[(e.dyn * 3 + 2) * N] = e.cell;
-            break;
-        case NPP_K_EXIT_SWITCH:
-            dynf[(e.dyn * 4 + 0) * N] = e.x; dynf[(e.dyn * 4 + 1) * N] = e.y; dynf[(e.dyn * 4 + 2) * N] = 0; dynf[(e.dyn * 4 + 3) * N] = 0;
-            dyni[(e.dyn * 3 + 0) * N] = e.cell; dyni[(e.dyn * 3 + 1) * N] = stamp; dyni[(e.dyn * 3 + 2) * N] = 0;
-            break;
-        case NPP_K_DRONE_ZAP: case NPP_K_MINI_DRONE: case NPP_K_BOUNCE: case NPP_K_THWUMP: case NPP_K_DEATH_BALL: case NPP_K_SHWUMP:
-            if (mode == 0) {
-                bool drone = (e.kind == NPP_K_DRONE_ZAP || e.kind == NPP_K_MINI_DRONE);
-                if (drone) fl |= (uint8_t)(e.p0 << FL_ST_SHIFT);
-                dynf[(e.dyn * 4 + 0) * N] = e.x; dynf[(e.dyn * 4 + 1) * N] = e.y;
-                dynf[(e.dyn * 4 + 2) * N] = drone ? e.x : 0.0; dynf[(e.dyn * 4 + 3) * N] = drone ? e.y : 0.0;   // xtarget,ytarget | speeds | xdir,ydir
-                dyni[(e.dyn * 3 + 0) * N] = e.cell; dyni[(e.dyn * 3 + 2) * N] = 0;
-            } else {
-                fl = flag[id * N] | FL_ACTIVE;      // no reset_state(): position, speed, state and cell all persist
-            }
-            dyni[(e.dyn * 3 + 1) * N] = stamp;
-            break;
-        default: break;
-        }
-        flag[id * N] = fl;
+    unsigned todo = __ballot_sync(0xffffffffu, need);
+    if (!todo) return;
+    if (need) {
+        const NppMapHeader* h = reinterpret_cast<const NppMapHeader*>(st.map_blob + st.map_off[st.env_map[i]]);
+        double* nf = st.nin_f + i; int32_t* ni = st.nin_i + i; int32_t* envi = st.env_i + i;
+        #pragma unroll 1
+        for (int f = 0; f < NPPSIM_NF; f++) nf[f * N] = 0.0;
+        #pragma unroll 1
+        for (int f = 0; f < NPPSIM_NI; f++) ni[f * N] = 0;
+        nf[F_XPOS * N] = h->spawn_x; nf[F_YPOS * N] = h->spawn_y;
+        nf[F_X_AT_ACTION * N] = h->spawn_x; nf[F_Y_AT_ACTION * N] = h->spawn_y;
+        nf[F_GRAVITY * N] = GRAVITY_FALL; nf[F_DRAG * N] = DRAG_REGULAR; nf[F_FRICTION * N] = FRICTION_GROUND;
+        nf[F_FNY * N] = -1; nf[F_CNY * N] = 1;
+        ni[I_JUMP_BUFFER * N] = -1; ni[I_FLOOR_BUFFER * N] = -1; ni[I_WALL_BUFFER * N] = -1; ni[I_LP_BUFFER * N] = -1;
+        envi[NPPSIM_ENV_STAMP * N] = h->n_ent;
+        envi[NPPSIM_ENV_EVENTS * N] = 0;
+        envi[NPPSIM_ENV_SWFRAME * N] = -1;
+        envi[NPPSIM_ENV_ORDER * N] = mode ? 1 : 0;
     }
-    envi[NPPSIM_ENV_HOT * N] = hot;
+    #pragma unroll 1
+    for (; todo; todo &= todo - 1) {
+        const int e_i = __shfl_sync(0xffffffffu, i, __ffs(todo) - 1);        // the env whose entity tables the warp rewrites now
+        const uint8_t* blob = st.map_blob + st.map_off[st.env_map[e_i]];
+        const NppMapHeader* h = reinterpret_cast<const NppMapHeader*>(blob);
+        const NppStaticEnt* ents = reinterpret_cast<const NppStaticEnt*>(blob + h->off_ents);
+        uint8_t* flag = st.ent_flag + e_i; double* dynf = st.dyn_f + e_i; int32_t* dyni = st.dyn_i + e_i;
+        const uint32_t n_ent = h->n_ent;
+        int hot = 0;   // fast_reset keeps boost pads' is_touching_ninja (no reset_state())
+        #pragma unroll 1
+        for (uint32_t id = lane; id < n_ent; id += 32) {
+            const NppStaticEnt& e = ents[id];
+            int stamp = mode ? (int)id : (int)e.load_order;
+            uint8_t fl = FL_ACTIVE;
+            switch (e.kind) {
+            case NPP_K_MINE: fl |= e.p0; break;
+            case NPP_K_GOLD: break;
+            case NPP_K_BOOST: fl |= FL_IS_BOOST; if (mode) { fl |= flag[id * N] & FL_TOUCH; if (fl & FL_TOUCH) hot++; } break;
+            case NPP_K_DOOR_LOCKED: fl |= FL_CLOSED; break;
+            case NPP_K_DOOR_TRAP: break;                         // starts open (entity_door_trap.py:51-53)
+            case NPP_K_DOOR_REGULAR:
+                if (mode == 0) { fl |= FL_CLOSED; dyni[(e.dyn * 3 + 0) * N] = -1; dyni[(e.dyn * 3 + 1) * N] = stamp; dyni[(e.dyn * 3 + 2) * N] = 256; }
+                else fl |= flag[id * N] & FL_CLOSED;
+                break;
+            case NPP_K_EXIT:
+                dynf[(e.dyn * 4 + 0) * N] = e.x; dynf[(e.dyn * 4 + 1) * N] = e.y; dynf[(e.dyn * 4 + 2) * N] = 0; dynf[(e.dyn * 4 + 3) * N] = 0;
+                dyni[(e.dyn * 3 + 0) * N] = -1; dyni[(e.dyn * 3 + 1) * N] = stamp; dyni[(e.dyn * 3 + 2) * N] = e.cell;
+                break;
+            case NPP_K_EXIT_SWITCH:
+                dynf[(e.dyn * 4 + 0) * N] = e.x; dynf[(e.dyn * 4 + 1) * N] = e.y; dynf[(e.dyn * 4 + 2) * N] = 0; dynf[(e.dyn * 4 + 3) * N] = 0;
+                dyni[(e.dyn * 3 + 0) * N] = e.cell; dyni[(e.dyn * 3 + 1) * N] = stamp; dyni[(e.dyn * 3 + 2) * N] = 0;
+                break;
+            case NPP_K_DRONE_ZAP: case NPP_K_MINI_DRONE: case NPP_K_BOUNCE: case NPP_K_THWUMP: case NPP_K_DEATH_BALL: case NPP_K_SHWUMP:
+                if (mode == 0) {
+                    bool drone = (e.kind == NPP_K_DRONE_ZAP || e.kind == NPP_K_MINI_DRONE);
+                    if (drone) fl |= (uint8_t)(e.p0 << FL_ST_SHIFT);
+                    dynf[(e.dyn * 4 + 0) * N] = e.x; dynf[(e.dyn * 4 + 1) * N] = e.y;
+                    dynf[(e.dyn * 4 + 2) * N] = drone ? e.x : 0.0; dynf[(e.dyn * 4 + 3) * N] = drone ? e.y : 0.0;   // xtarget,ytarget | speeds | xdir,ydir
+                    dyni[(e.dyn * 3 + 0) * N] = e.cell; dyni[(e.dyn * 3 + 2) * N] = 0;
+                } else {
+                    fl = flag[id * N] | FL_ACTIVE;      // no reset_state(): position, speed, state and cell all persist
+                }
+                dyni[(e.dyn * 3 + 1) * N] = stamp;
+                break;
+            default: break;
+            }
+            flag[id * N] = fl;
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) hot += __shfl_xor_sync(0xffffffffu, hot, d);
+        if (lane == 0) st.env_i[NPPSIM_ENV_HOT * N + e_i] = hot;
+    }
 }
 
 }  // namespace
