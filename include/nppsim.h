@@ -203,6 +203,9 @@ int nppsim_observe(const nppsim_state_t* st, const uint8_t* path_dir, uint8_t* m
  * nppsim_sq_mode: 1 = exact pow emulation (default build), 0 = x*x. */
 int nppsim_debug_sq(const double* in_dev, double* out_dev, int32_t n, void* stream);
 int nppsim_sq_mode(void);
+/* Test hook: counts (into *mismatches, device uint64, not cleared) the i for which the kernels' shared-reciprocal double division
+ * div2(a1[i], a2[i], b[i]) differs in any bit from the device's own a1[i] / b[i], a2[i] / b[i]. */
+int nppsim_debug_div2(const double* a1_dev, const double* a2_dev, const double* b_dev, unsigned long long* mismatches_dev, int32_t n, void* stream);
 /* Test hook: non-zero forces every launch onto the full (all entity kinds) kernel; returns the previous setting. */
 int nppsim_debug_force_full_kernel(int on);
 

@@ -31,7 +31,7 @@ EXPORTS = (
     "nppsim_version", "nppsim_last_error", "nppsim_map_blob_bound", "nppsim_compile_map",
     "nppsim_reset", "nppsim_reset_terminal", "nppsim_step", "nppsim_step_actions", "nppsim_step_stream", "nppsim_replay_rows",
     "nppsim_step_host", "nppsim_launch_count",
-    "nppsim_observe", "nppsim_set_exit_positions", "nppsim_compile_maps_device", "nppsim_debug_sq", "nppsim_sq_mode", "nppsim_debug_force_full_kernel",
+    "nppsim_observe", "nppsim_set_exit_positions", "nppsim_compile_maps_device", "nppsim_debug_sq", "nppsim_debug_div2", "nppsim_sq_mode", "nppsim_debug_force_full_kernel",
 )
 
 
@@ -68,6 +68,7 @@ def lib():
     L.nppsim_observe.argtypes = [st, vp, vp, vp, vp]; L.nppsim_observe.restype = C.c_int
     L.nppsim_set_exit_positions.argtypes = [st, vp, vp, vp, vp, vp]; L.nppsim_set_exit_positions.restype = C.c_int
     L.nppsim_debug_sq.argtypes = [vp, vp, i32, vp]; L.nppsim_debug_sq.restype = C.c_int
+    L.nppsim_debug_div2.argtypes = [vp, vp, vp, vp, i32, vp]; L.nppsim_debug_div2.restype = C.c_int
     L.nppsim_sq_mode.restype = C.c_int
     L.nppsim_debug_force_full_kernel.argtypes = [i32]; L.nppsim_debug_force_full_kernel.restype = C.c_int
     _lib = L

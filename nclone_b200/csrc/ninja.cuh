@@ -147,7 +147,7 @@ DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
             if (ns >= 0) {
                 const double inf = __longlong_as_double(0x7ff0000000000000LL);
                 double d2 = inf, ca = 0, cb = 0; int r = 1; bool ix = false, ok = false;
-                if (lane < ns) ok = closest_eval_nb(g, xpos, ypos, d2, ca, cb, r, ix);
+                if (lane < ns) ok = closest_eval_nb(g, xpos, ypos, d2, ca, cb, r);
                 COOP_T(cacc, 0, ct)
                 if (__ballot_sync(FULL_MASK, ok && ix) == 0) {
                     const unsigned cand = warp_first_min(d2, ok);

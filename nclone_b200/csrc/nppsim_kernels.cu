@@ -388,6 +388,14 @@ __global__ void __launch_bounds__(128) curriculum_kernel(nppsim_state_t st, cons
     }
 }
 
+__global__ void div2_kernel(const double* a1, const double* a2, const double* b, unsigned long long* mismatches, int n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double q1, q2;
+    div2(a1[i], a2[i], b[i], q1, q2);
+    const double w1 = a1[i] / b[i], w2 = a2[i] / b[i];
+    if (__double_as_longlong(q1) != __double_as_longlong(w1) || __double_as_longlong(q2) != __double_as_longlong(w2)) atomicAdd(mismatches, 1ULL);
+}
 __global__ void sq_kernel(const double* in, double* out, int n) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = SQ(in[i]);
@@ -493,6 +501,16 @@ int nppsim_debug_phase_cycles(unsigned long long* out16, int reset) {
     return 0;
 }
 #endif
+
+int nppsim_debug_div2(const double* a1, const double* a2, const double* b, unsigned long long* mismatches, int32_t n, void* stream) {
+    g_err[0] = 0;
+    if (!a1 || !a2 || !b || !mismatches || n <= 0) return fail(NPPSIM_E_ARG, "bad arguments");
+    div2_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(a1, a2, b, mismatches, n);
+    g_launches++;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "div2_kernel launch");
+    return 0;
+}
 
 int nppsim_debug_sq(const double* in, double* out, int32_t n, void* stream) {
     g_err[0] = 0;

@@ -356,7 +356,9 @@ DEV bool closest_eval(const SegC& g, double x, double y, double& d2, double& a, 
         back = false;
         if (dx * g.px > 0 && dy * g.py > 0) {
             double dist = SQRT(SQ(dx) + SQ(dy));
-            a = g.x1 + DIV(24.0 * dx, dist); b = g.y1 + DIV(24.0 * dy, dist);
+            double qa, qb;
+            div2(24.0 * dx, 24.0 * dy, dist, qa, qb);
+            a = g.x1 + qa; b = g.y1 + qb;
             back = (g.lensq != 0) ? (dist < 24.0) : (dist > 24.0);
         } else if (dx * g.px > dy * g.py) { a = g.x1 + 24.0 * g.px; b = g.y1; }
         else { a = g.x1; b = g.y1 + 24.0 * g.py; }
@@ -462,7 +464,7 @@ DEV int warp_closest_point(WarpPool& wp, const Ctx& c, int o, int ns, const SegC
 
 // closest_eval without the early AABB return: the bounds test only gates `ok` and stays off the dependency chain
 // (in the cooperative loop every lane owns one segment, so skipping the arithmetic would save nothing).
-DEV bool closest_eval_nb(const SegC& g, double x, double y, double& d2, double& a, double& b, int& r, bool& ix) {
+DEV bool closest_eval_nb(const SegC& g, double x, double y, double& d2, double& a, double& b, int& r) {
     const bool inb = !(g.bx1 < x - NINJA_RADIUS || g.bx0 > x + NINJA_RADIUS || g.by1 < y - NINJA_RADIUS || g.by0 > y + NINJA_RADIUS);
     const double dx = x - g.x1, dy = y - g.y1;
     bool back;
@@ -476,13 +478,16 @@ DEV bool closest_eval_nb(const SegC& g, double x, double y, double& d2, double& 
         back = false;
         if (dx * g.px > 0 && dy * g.py > 0) {
             double dist = SQRT(SQ(dx) + SQ(dy));
-            a = g.x1 + DIV(24.0 * dx, dist); b = g.y1 + DIV(24.0 * dy, dist);
+            double qa, qb;
+            div2(24.0 * dx, 24.0 * dy, dist, qa, qb);
+            a = g.x1 + qa; b = g.y1 + qb;
             back = (g.lensq != 0) ? (dist < 24.0) : (dist > 24.0);
         } else if (dx * g.px > dy * g.py) { a = g.x1 + 24.0 * g.px; b = g.y1; }
         else { a = g.x1; b = g.y1 + 24.0 * g.py; }
     }
-    ix = false;
-    d2 = sq_flag(x - a, ix) + sq_flag(y - b, ix);
+    // exact squares (pow2_exact: one FMA test, the table path for the 3 % near a rounding midpoint): no "inexact" flag to
+    // resolve afterwards -- with one segment per lane a flagged lane costs less here than the owner's ordered re-fold
+    d2 = SQ(x - a) + SQ(y - b);
     if (!back) d2 -= 0.1;
     r = back ? -1 : 1;
     return inb;
@@ -511,8 +516,8 @@ DEV int warp_closest_uniform(WarpPool& wp, const Ctx& c, int o, int ns, const Se
     const int lane = threadIdx.x & 31;
     const double inf = __longlong_as_double(0x7ff0000000000000LL);
     double d2 = inf, a = 0, b = 0; int r = 0; bool ix = false, ok = false;
-#ifdef NPP_COOP_EVAL_NB
-    if (lane < ns) ok = closest_eval_nb(g, x, y, d2, a, b, r, ix);
+#ifdef NPP_COOP_EVAL_EXACT   // bounds test off the chain + exact squares instead of the flagged ones: measured 1-2 % slower
+    if (lane < ns) ok = closest_eval_nb(g, x, y, d2, a, b, r);
 #else
     if (lane < ns) ok = closest_eval(g, x, y, d2, a, b, r, ix);
 #endif

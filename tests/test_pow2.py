@@ -61,3 +61,36 @@ def test_device_sq_matches_python_pow():
     assert bad.size == 0, (x[bad[:5]], got[bad[:5]], ref[bad[:5]])
     assert np.array_equal(got[-17:].view(np.int64), want.view(np.int64))
     assert np.count_nonzero(ref != x[:-17] * x[:-17]) > 1000      # the emulation is doing real work
+
+
+@pytest.mark.gpu
+def test_device_div2_is_ieee_division():
+    """csrc/geom.cuh div2 (two quotients by one denominator off a single reciprocal refinement) must return the bits of
+    the device's own IEEE `/` for every input: 2^28 random triples over the kernels' working range (24*dx / dist),
+    over wide exponent ranges, and over the special values that must take the guarded fallback."""
+    import ctypes as C
+    import torch
+    from nclone_b200._lib import lib, check
+    L = lib()
+    g = torch.Generator(device="cuda"); g.manual_seed(5)
+    bad = torch.zeros(1, dtype=torch.int64, device="cuda")
+
+    def run(a1, a2, b):
+        check(L.nppsim_debug_div2(C.c_void_p(a1.data_ptr()), C.c_void_p(a2.data_ptr()), C.c_void_p(b.data_ptr()),
+                                  C.c_void_p(bad.data_ptr()), a1.numel(), None))
+    n = 1 << 24
+    for rep in range(8):
+        dx = (torch.rand(n, generator=g, device="cuda", dtype=torch.float64) - 0.5) * 96
+        dy = (torch.rand(n, generator=g, device="cuda", dtype=torch.float64) - 0.5) * 96
+        run(24.0 * dx, 24.0 * dy, torch.sqrt(dx * dx + dy * dy))
+    for rep in range(8):
+        e = lambda: torch.exp2((torch.rand(n, generator=g, device="cuda", dtype=torch.float64) - 0.5) * 600) * \
+            torch.where(torch.rand(n, generator=g, device="cuda") < 0.5, -1.0, 1.0).double() * (1 + torch.rand(n, generator=g, device="cuda", dtype=torch.float64))
+        run(e(), e(), e())
+    sp = torch.tensor([0.0, -0.0, 1.0, -1.0, 5e-324, 2.2e-308, 1e-300, 1e300, 1.7e308, float("inf"), -float("inf"), float("nan"), 3.0, 1e-160, 1e160],
+                      dtype=torch.float64, device="cuda")
+    k = sp.numel()
+    a1 = sp.repeat_interleave(k * k); a2 = sp.repeat(k).repeat_interleave(k); b = sp.repeat(k * k)
+    run(a1.contiguous(), a2.contiguous(), b.contiguous())
+    torch.cuda.synchronize()
+    assert int(bad.item()) == 0
