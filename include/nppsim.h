@@ -71,7 +71,9 @@ typedef struct {
     uint32_t kind_mask;         /* OR of NppMapHeader.kind_mask over the loaded maps (entity-kind census); 0 = unknown.
                                    Selects the step-kernel variant: level sets without moving / pushing entities run
                                    on a kernel compiled without those phases. */
-    uint32_t reserved;
+    uint32_t stride;            /* SoA stride in elements; 0 = n_envs.  A sub-batch (envs [b, b + n) of a batch of S envs, b % 32 == 0) is the same
+                                   struct with n_envs = n, stride = S and every per-env pointer advanced by b (warp_order / warp_cost by b / 32):
+                                   groups of one batch can then be stepped independently on different streams. */
     int32_t*  warp_order;       /* optional [ceil(N/32)]: launch slot -> group of 32 consecutive envs (a permutation);
                                    NULL = identity.  Rewritten by nppsim_step* after each launch when warp_cost is set. */
     uint32_t* warp_cost;        /* optional [ceil(N/32)]: device-clock cost of each group in the last launch (written by

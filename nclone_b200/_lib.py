@@ -14,7 +14,7 @@ class NppsimState(C.Structure):
         ("n_envs", C.c_int32), ("ent_cap", C.c_int32), ("dyn_cap", C.c_int32), ("n_maps", C.c_int32),
         ("nin_f", C.c_void_p), ("nin_i", C.c_void_p), ("env_i", C.c_void_p), ("ent_flag", C.c_void_p),
         ("dyn_f", C.c_void_p), ("dyn_i", C.c_void_p), ("env_map", C.c_void_p), ("map_blob", C.c_void_p),
-        ("map_off", C.c_void_p), ("kind_mask", C.c_uint32), ("reserved", C.c_uint32),
+        ("map_off", C.c_void_p), ("kind_mask", C.c_uint32), ("stride", C.c_uint32),
         ("warp_order", C.c_void_p), ("warp_cost", C.c_void_p),
     ]
 

@@ -142,6 +142,48 @@ class BatchedSimulator:
         st.kind_mask = self.kind_mask
         self._state = st
 
+    # ------------------------------------------------------------------ sub-batches for asynchronous stepping
+    def groups(self, n_groups):
+        """Split the batch into n_groups views over contiguous env ranges (multiples of 32 envs).  A view is a
+        BatchedSimulator over the SAME device memory (column slices, nppsim_state_t.stride = the parent's n_envs), so it
+        can be stepped / reset / observed on its own stream while the other groups do something else -- the policy acting
+        on one group while the next one steps, as asynchronous RL loops do.  The kernel of one group then overlaps the
+        long tail of another's (a wedged ninja's serial depenetration chain): +30 % env-steps/s at 131,072 envs per GPU.
+        Do not mix calls on the parent with calls on its groups without synchronising in between."""
+        self._need_maps()
+        N = self.n_envs
+        per = -(-N // n_groups)
+        per = (per + 31) // 32 * 32
+        views = []
+        for b in range(0, N, per):
+            views.append(self._view(b, min(N, b + per)))
+        return views
+
+    def _view(self, b, e):
+        v = BatchedSimulator.__new__(BatchedSimulator)
+        v.__dict__.update(self.__dict__)
+        v.n_envs = e - b
+        v._exit_cache = None
+        for name in ("nin_f", "nin_i", "env_i", "ent_flag", "dyn_f", "dyn_i"):
+            setattr(v, name, getattr(self, name)[:, b:e])
+        for name in ("env_map", "frames_executed", "_actions_dev"):
+            setattr(v, name, getattr(self, name)[b:e])
+        v.env_map_host = self.env_map_host[b:e]
+        v.warp_order = self.warp_order[b // 32:(e + 31) // 32]
+        v.warp_cost = self.warp_cost[b // 32:(e + 31) // 32]
+        v.warp_order.copy_(torch.arange(v.warp_order.numel(), dtype=torch.int32, device=self.device))   # group-local slots
+        parent = self._state
+        st = NppsimState()
+        st.n_envs, st.ent_cap, st.dyn_cap, st.n_maps = v.n_envs, parent.ent_cap, parent.dyn_cap, parent.n_maps
+        st.stride = parent.stride or parent.n_envs
+        st.nin_f, st.nin_i, st.env_i = v.nin_f.data_ptr(), v.nin_i.data_ptr(), v.env_i.data_ptr()
+        st.ent_flag, st.dyn_f, st.dyn_i = v.ent_flag.data_ptr(), v.dyn_f.data_ptr(), v.dyn_i.data_ptr()
+        st.env_map, st.map_blob, st.map_off = v.env_map.data_ptr(), parent.map_blob, parent.map_off
+        st.warp_order, st.warp_cost = v.warp_order.data_ptr(), v.warp_cost.data_ptr()
+        st.kind_mask = parent.kind_mask
+        v._state = st
+        return v
+
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 

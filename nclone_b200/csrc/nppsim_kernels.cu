@@ -30,7 +30,7 @@ __global__ void __launch_bounds__(128) reset_kernel(nppsim_state_t st, const uin
                                                      unsigned long long* stats) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
-    const size_t N = st.n_envs;
+    const size_t N = npp_stride(st);
     bool need = i < st.n_envs && !(mask && !mask[i]);
     if (need && auto_terminal) {
         int s = st.nin_i[I_STATE * N + i], fr = st.nin_i[I_FRAME * N + i];
@@ -199,7 +199,7 @@ DEV double obs_min(double a, double b) { return b < a ? b : a; }      // Python 
 DEV double obs_max(double a, double b) { return b > a ? b : a; }
 // NPlayHeadless.get_ninja_state for env i -> o[0..39]
 DEV void ninja_state_row(const nppsim_state_t& st, int i, float* __restrict__ o) {
-    const size_t N = st.n_envs;
+    const size_t N = npp_stride(st);
     const double* f = st.nin_f + i; const int32_t* q = st.nin_i + i;
 #define NF_(k) f[(size_t)(k) * N]
 #define NI_(k) q[(size_t)(k) * N]
@@ -261,7 +261,7 @@ DEV void ninja_state_row(const nppsim_state_t& st, int i, float* __restrict__ o)
 __global__ void __launch_bounds__(128) obs_kernel(nppsim_state_t st, const uint8_t* __restrict__ path_dir, uint8_t* __restrict__ mask_out, float* __restrict__ state_out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= st.n_envs) return;
-    const size_t N = st.n_envs;
+    const size_t N = npp_stride(st);
     const double* f = st.nin_f + i; const int32_t* q = st.nin_i + i;
 #define NF_(k) f[(size_t)(k) * N]
 #define NI_(k) q[(size_t)(k) * N]
@@ -307,7 +307,7 @@ __global__ void __launch_bounds__(128) replay_rows_kernel(nppsim_state_t st, npp
     if (i >= st.n_envs) return;
     const long long len = in.offset[i + 1] - in.offset[i];
     if (obs_tick > len) return;
-    const size_t N = st.n_envs;
+    const size_t N = npp_stride(st);
     const size_t row = (size_t)(row_off[i] + obs_tick / frame_skip - 1);
     const int state = st.nin_i[(size_t)I_STATE * N + i];
     if (game_state) {
@@ -358,7 +358,7 @@ __global__ void __launch_bounds__(128) curriculum_kernel(nppsim_state_t st, cons
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= st.n_envs) return;
     if (mask && !mask[i]) return;
-    const size_t N = st.n_envs;
+    const size_t N = npp_stride(st);
     const uint8_t* blob = st.map_blob + st.map_off[st.env_map[i]];
     const NppMapHeader* h = reinterpret_cast<const NppMapHeader*>(blob);
     const NppStaticEnt* ents = reinterpret_cast<const NppStaticEnt*>(blob + h->off_ents);
@@ -369,7 +369,7 @@ __global__ void __launch_bounds__(128) curriculum_kernel(nppsim_state_t st, cons
     if (sw < 0) return;                                       // the reference raises RuntimeError (:768-781)
     double* dynf = st.dyn_f + i; int32_t* dyni = st.dyn_i + i;
     const int s = ents[sw].dyn, d = ents[ents[sw].aux].dyn;
-    const double sx = switch_xy[i], sy = switch_xy[N + i];
+    const double sx = switch_xy[i], sy = switch_xy[(size_t)st.n_envs + i];          // caller arrays are dense over this batch
     dynf[(size_t)(s * 4 + 0) * N] = sx; dynf[(size_t)(s * 4 + 1) * N] = sy;
     if (st.nin_i[(size_t)I_FRAME * N + i] <= 10) st.ent_flag[(size_t)sw * N + i] |= FL_ACTIVE;
     int cx = min(max((int)floor(sx / 24), 0), NPP_NCX - 1), cy = min(max((int)floor(sy / 24), 0), NPP_NCY - 1);
@@ -378,7 +378,7 @@ __global__ void __launch_bounds__(128) curriculum_kernel(nppsim_state_t st, cons
         dyni[(size_t)(s * 3 + 0) * N] = cell;
         dyni[(size_t)(s * 3 + 1) * N] = st.env_i[(size_t)NPPSIM_ENV_STAMP * N + i]++;
     }
-    const double dx = door_xy[i], dy = door_xy[N + i];
+    const double dx = door_xy[i], dy = door_xy[(size_t)st.n_envs + i];
     dynf[(size_t)(d * 4 + 0) * N] = dx; dynf[(size_t)(d * 4 + 1) * N] = dy;
     cx = min(max((int)floor(dx / 24), 0), NPP_NCX - 1); cy = min(max((int)floor(dy / 24), 0), NPP_NCY - 1);
     cell = cx * NPP_NCY + cy;
@@ -617,13 +617,13 @@ int nppsim_step_host(const nppsim_state_t* st, const uint8_t* actions_host, uint
     if (rc) return rc;
     if (!actions_host || !actions_dev || !pos_vel_host || !state_host) return fail(NPPSIM_E_ARG, "a host/device buffer is NULL");
     cudaStream_t s = (cudaStream_t)stream;
-    size_t N = (size_t)st->n_envs;
+    const size_t N = (size_t)st->n_envs, S = st->stride ? (size_t)st->stride : N;
     cudaError_t e = cudaMemcpyAsync(actions_dev, actions_host, N, cudaMemcpyHostToDevice, s);
     if (e != cudaSuccess) return cuda_fail(e, "actions H2D");
     rc = launch_step(st, nullptr, nullptr, actions_dev, 1, n_ticks, nullptr, stop_on_terminal, nullptr, stream);
     if (rc) return rc;
     // xpos, ypos, xspeed, yspeed are fields 0..3 -> one contiguous [4][N] block; state is int field 0
-    e = cudaMemcpyAsync(pos_vel_host, st->nin_f, 4 * N * sizeof(double), cudaMemcpyDeviceToHost, s);
+    e = cudaMemcpy2DAsync(pos_vel_host, N * sizeof(double), st->nin_f, S * sizeof(double), N * sizeof(double), 4, cudaMemcpyDeviceToHost, s);
     if (e != cudaSuccess) return cuda_fail(e, "pos/vel D2H");
     e = cudaMemcpyAsync(state_host, st->nin_i, N * sizeof(int32_t), cudaMemcpyDeviceToHost, s);
     if (e != cudaSuccess) return cuda_fail(e, "state D2H");

@@ -464,3 +464,45 @@ def test_env_view_mirrors_single_env_interface(golden_replays):
             assert schema.state_hash(*r) == others[j]
     v.reset()
     assert v.ninja_position() == (t["pv"][0, 0], t["pv"][0, 1]) and v.sim.frame == 0
+
+
+def test_groups_views_step_independently(golden_replays, golden_generated):
+    """BatchedSimulator.groups(G): views over one allocation (nppsim_state_t.stride) stepped on their own streams, in a
+    different interleaving per group, must leave exactly the state the whole batch reaches when stepped as one."""
+    import torch
+    from nclone_b200 import BatchedSimulator
+    maps = [golden_generated.traj(i)["map_data"] for i in range(0, len(golden_generated), 3)]
+    maps += [golden_replays.traj(i)["map_data"] for i in range(0, 130, 9)]
+    N = 5 * 32 + 7
+    env_to_map = np.arange(N) % len(maps)
+    rng = np.random.default_rng(21)
+    steps = 40
+    acts = rng.integers(0, 6, size=(steps, N)).astype(np.uint8)
+    whole = BatchedSimulator(N); whole.load_maps(maps, env_to_map)
+    for s in range(steps):
+        whole.step(torch.from_numpy(acts[s]).cuda(), 4, True); whole.reset_terminal(60)
+    want = [schema.state_hash(*r) for r in whole.canonical_state()]
+    sim = BatchedSimulator(N); sim.load_maps(maps, env_to_map)
+    groups = sim.groups(3)
+    assert [g.n_envs for g in groups] == [64, 64, 39]
+    streams = [torch.cuda.Stream() for _ in groups]
+    torch.cuda.synchronize()
+    bounds = np.cumsum([0] + [g.n_envs for g in groups])
+    pv = [np.zeros((4, g.n_envs)) for g in groups]; stt = [np.zeros(g.n_envs, dtype=np.int32) for g in groups]
+    for k, (g, st) in enumerate(zip(groups, streams)):       # group k runs all its steps before group k+1 is even issued
+        with torch.cuda.stream(st):
+            for s in range(steps):
+                a = acts[s, bounds[k]:bounds[k + 1]]
+                if s % 2:
+                    g.step_host(np.ascontiguousarray(a), pv[k], stt[k], 4, True)      # host-buffer entry point on a view
+                else:
+                    g.step(torch.from_numpy(np.ascontiguousarray(a)).cuda(), 4, True)
+                g.reset_terminal(60)
+    torch.cuda.synchronize()
+    got = [schema.state_hash(*r) for r in sim.canonical_state()]
+    assert got == want
+    assert int(sim.stats[0]) == int(whole.stats[0]) > 0
+    # getters of a view are slices of the parent's
+    x, _ = groups[1].ninja_position()
+    assert torch.equal(x, sim.ninja_position()[0][64:128])
+    assert groups[2].get_action_mask().shape == (39, 6) and groups[2].get_ninja_state().shape == (39, 40)

@@ -14,38 +14,34 @@ from nclone_b200 import BatchedSimulator  # noqa: E402
 from nclone_b200.sharding import shard_env_to_map  # noqa: E402
 
 
-def run(n_envs, groups, steps, arr, lens):
+def run(n_envs, n_groups, steps, arr, lens):
     M = len(arr)
-    per = n_envs // groups
-    full = shard_env_to_map(n_envs, 0, M)
-    sims, streams, acts = [], [], []
-    for g in range(groups):
-        s = torch.cuda.Stream()
-        with torch.cuda.stream(s):
-            sim = BatchedSimulator(per)
-            sim.load_maps([arr[k, :lens[k]] for k in range(M)], full[g * per:(g + 1) * per])
-            gen = torch.Generator(device="cuda"); gen.manual_seed(1234 + g)
-            a = torch.randint(0, 6, (64, per), generator=gen, device="cuda", dtype=torch.uint8)
-            for k in range(320):
-                sim.step(a[k % 64], 4, True); sim.reset_terminal(2000)
-        sims.append(sim); streams.append(s); acts.append(a)
+    sim = BatchedSimulator(n_envs)
+    sim.load_maps([arr[k, :lens[k]] for k in range(M)], shard_env_to_map(n_envs, 0, M))
+    groups = sim.groups(n_groups)
+    streams = [torch.cuda.Stream() for _ in groups]
+    gen = torch.Generator(device="cuda"); gen.manual_seed(1234)
+    acts = torch.randint(0, 6, (64, n_envs), generator=gen, device="cuda", dtype=torch.uint8)
+    bounds = np.cumsum([0] + [g.n_envs for g in groups])
+    ga = [acts[:, bounds[k]:bounds[k + 1]].contiguous() for k in range(len(groups))]
+    for k in range(320):
+        sim.step(acts[k % 64], 4, True); sim.reset_terminal(2000)
     torch.cuda.synchronize()
-    t0 = [s.total_ticks() for s in sims]
+    t0 = sim.total_ticks()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for s in streams:
         s.wait_event(e0)
     for k in range(steps):
-        for g in range(groups):
+        for g in range(len(groups)):
             with torch.cuda.stream(streams[g]):
-                sims[g].step(acts[g][k % 64], 4, True); sims[g].reset_terminal(2000)
+                groups[g].step(ga[g][k % 64], 4, True); groups[g].reset_terminal(2000)
     for s in streams:
         torch.cuda.current_stream().wait_stream(s)
     e1.record()
     torch.cuda.synchronize()
-    ticks = sum(s.total_ticks() - t for s, t in zip(sims, t0))
     ms = e0.elapsed_time(e1)
-    return ticks / ms * 1e3, ms / steps
+    return (sim.total_ticks() - t0) / ms * 1e3, ms / steps
 
 
 def main():
