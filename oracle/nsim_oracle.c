@@ -360,12 +360,20 @@ static double sweep_circle_vs_tiles(OSim *S, double xpos_old, double ypos_old, d
     return shortest;
 }
 /* physics.py:131-180.  segs==NULL: gather first (death balls). */
+#ifdef OSIM_STATS
+int osim_last_winner;
+long osim_stat_pred[4];
+long osim_stat_arc[3];    /* calls 2..31: [0] an arc in the gathered list, [1] an arc inside the query box, [2] the winner is an arc */   /* calls 2..31 of loops that reach call 3+: [0] total, [1] winner == winner two calls back, [2] == previous winner, [3] neither */
+#endif
 static int get_single_closest_point(OSim *S, double xpos, double ypos, double radius, IVec *segs, double *pa, double *pb) {
     if (!segs) {
         query_region(S, xpos - radius, ypos - radius, xpos + radius, ypos + radius, &S->tmp_segs);
         segs = &S->tmp_segs;
     }
     double shortest = INFINITY; int result = 0;
+#ifdef OSIM_STATS
+    extern int osim_last_winner; osim_last_winner = -1;
+#endif
     double qx0 = xpos - radius, qy0 = ypos - radius, qx1 = xpos + radius, qy1 = ypos + radius;
     for (int k = 0; k < segs->n; k++) {
         const Seg *s = &S->segs[segs->v[k]];
@@ -374,7 +382,11 @@ static int get_single_closest_point(OSim *S, double xpos, double ypos, double ra
         seg_closest_point(s, xpos, ypos, &back, &a, &b);
         double d2 = SQ(xpos - a) + SQ(ypos - b);
         if (!back) d2 -= 0.1;
-        if (d2 < shortest) { shortest = d2; *pa = a; *pb = b; result = back ? -1 : 1; }
+        if (d2 < shortest) { shortest = d2; *pa = a; *pb = b; result = back ? -1 : 1;
+#ifdef OSIM_STATS
+            osim_last_winner = k;
+#endif
+        }
     }
     return result;
 }
@@ -509,6 +521,10 @@ static void ninja_collide_vs_objects(OSim *S) {      /* ninja.py:224-267 */
 }
 #ifdef OSIM_STATS   /* tools/iter_stats.py only: depenetration-loop statistics (not thread safe) */
 long osim_stat_iters[34], osim_stat_nseg[64], osim_stat_calls;
+long osim_stat_period[5][34];
+long osim_stat_traj[34];        /* [k]: full-length loops whose position at call k first matched the previous full-length loop's (same env, same call index); 33: none */
+static double osim_prev_x[32], osim_prev_y[32]; static int osim_prev_valid;   /* one env at a time (tools/iter_stats.py) */
+void osim_stat_new_env(void) { osim_prev_valid = 0; }   /* [p][k]: full-length (32-call) loops whose position first repeated with period p at call k; p = 0: never */
 #define STAT_ITERS(k, ns) do { osim_stat_iters[(k)]++; osim_stat_nseg[(ns) < 63 ? (ns) : 63]++; osim_stat_calls += (k); } while (0)
 #else
 #define STAT_ITERS(k, ns) do { } while (0)
@@ -526,10 +542,30 @@ static void ninja_collide_vs_tiles(OSim *S) {        /* ninja.py:269-379 */
     for (int k = 0; k < S->tmp_segs.n; k++) iv_push(&segments, S->tmp_segs.v[k]);
     double xpos = n->xpos, ypos = n->ypos, xspeed = n->xspeed, yspeed = n->yspeed;
     int cp_calls = 0;
+#ifdef OSIM_STATS
+    double hx[32], hy[32]; int per_p = 0, per_k = 0;
+#endif
     for (int it = 0; it < 32; it++) {
         double a, b;
+#ifdef OSIM_STATS
+        hx[it] = xpos; hy[it] = ypos;
+        static int w1, w2;
+        for (int p = 1; p <= 4 && !per_p; p++)
+            if (it >= p && memcmp(&hx[it - p], &xpos, 8) == 0 && memcmp(&hy[it - p], &ypos, 8) == 0) { per_p = p; per_k = it; }
+#endif
         int result = get_single_closest_point(S, xpos, ypos, NINJA_RADIUS, &segments, &a, &b);
         cp_calls++;
+#ifdef OSIM_STATS
+        if (it >= 2) {
+            int any = 0, inb = 0;
+            for (int k = 0; k < segments.n; k++) { const Seg *sg = &S->segs[segments.v[k]]; if (sg->kind) { any = 1;
+                if (!(sg->b[2] < xpos - 10 || sg->b[0] > xpos + 10 || sg->b[3] < ypos - 10 || sg->b[1] > ypos + 10)) inb = 1; } }
+            osim_stat_arc[0] += any; osim_stat_arc[1] += inb;
+            if (osim_last_winner >= 0 && S->segs[segments.v[osim_last_winner]].kind) osim_stat_arc[2]++;
+        }
+        if (it >= 2) { osim_stat_pred[0]++; if (osim_last_winner == w2) osim_stat_pred[1]++; else if (osim_last_winner == w1) osim_stat_pred[2]++; else osim_stat_pred[3]++; }
+        w2 = w1; w1 = osim_last_winner;
+#endif
         if (result == 0) break;
         dx = xpos - a; dy = ypos - b;
         if (fabs(dx) <= 0.0000001) {                 /* ninja.py:312-318 band-aid */
@@ -560,6 +596,15 @@ static void ninja_collide_vs_tiles(OSim *S) {        /* ninja.py:269-379 */
         else { n->floor_count += 1; n->floor_normal_x += norm_dx; n->floor_normal_y += norm_dy; }
     }
     STAT_ITERS(cp_calls, segments.n);
+#ifdef OSIM_STATS
+    if (cp_calls == 32) {
+        osim_stat_period[per_p][per_k]++;
+        int k = 33;
+        if (osim_prev_valid) for (int j = 0; j < 32; j++) if (memcmp(&hx[j], &osim_prev_x[j], 8) == 0 && memcmp(&hy[j], &osim_prev_y[j], 8) == 0) { k = j; break; }
+        osim_stat_traj[k]++;
+        memcpy(osim_prev_x, hx, sizeof hx); memcpy(osim_prev_y, hy, sizeof hy); osim_prev_valid = 1;
+    }
+#endif
     (void)cp_calls;
     n->xpos = xpos; n->ypos = ypos; n->xspeed = xspeed; n->yspeed = yspeed;
     free(segments.v);

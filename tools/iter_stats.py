@@ -24,7 +24,7 @@ per_map = []
 nf = np.zeros(31); ni = np.zeros(27, dtype=np.int64)
 heavy = []
 for m in range(n_maps):
-    S = C.c_void_p(L.osim_create())
+    S = C.c_void_p(L.osim_create()); L.osim_stat_new_env()
     md = np.ascontiguousarray(arr[m, :lens[m]])
     L.osim_load(S, md.ctypes.data_as(dp), len(md))
     frames = 0; c0 = calls.value; ticks = 0
@@ -53,3 +53,13 @@ print("entities per map: mean %.1f max %d" % (pm[:, 1].mean(), pm[:, 1].max()))
 print("corr(calls/tick, n_ent) = %.3f" % np.corrcoef(pm[:, 0], pm[:, 1])[0, 1])
 print("heavy ticks (>40 closest-point calls):", len(heavy), "of", int(it.sum() / 4))
 for h in heavy[:20]: print("  map %d frame %d calls %d pos (%.6f, %.6f) v (%.4f, %.4f) state %d" % h)
+per = np.array(list((C.c_long * (5 * 34)).in_dll(L, "osim_stat_period"))).reshape(5, 34)
+print("full-length (32-call) loops:", int(per.sum()), " never periodic (p <= 4):", int(per[0].sum()))
+for p in range(1, 5):
+    if per[p].sum(): print(f"  period {p}: {int(per[p].sum())}  first repeat at call k: " + str({k: int(v) for k, v in enumerate(per[p]) if v}))
+tr = np.array(list((C.c_long * 34).in_dll(L, "osim_stat_traj")))
+print("full-length loops whose trajectory rejoins the previous full-length loop's of the env at call k:", {k: int(v) for k, v in enumerate(tr) if v}, "(33 = never)")
+pr = list((C.c_long * 4).in_dll(L, "osim_stat_pred"))
+print("calls 2..31: total %d, winner == winner two calls back %d (%.3f), else == previous winner %d, neither %d" % (pr[0], pr[1], pr[1] / max(pr[0], 1), pr[2], pr[3]))
+ar = list((C.c_long * 3).in_dll(L, "osim_stat_arc"))
+print("calls 2..31 with an arc in the list %d, inside the query box %d, arc wins %d" % tuple(ar))
