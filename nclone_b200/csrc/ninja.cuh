@@ -63,37 +63,51 @@ DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
     // segments are gathered once, around the post-sweep position (ninja.py:282-285)
     const double gx1 = xpos - NINJA_RADIUS, gy1 = ypos - NINJA_RADIUS, gx2 = xpos + NINJA_RADIUS, gy2 = ypos + NINJA_RADIUS;
     double xspeed = n.f[F_XSPEED], yspeed = n.f[F_YSPEED];
-    // One depenetration push (ninja.py:303-379) from the closest point (a, b); false = the loop ends here.
-    auto depen = [&](int result, double a, double b) -> bool {
-        if (result == 0) return false;
-        dx = xpos - a; dy = ypos - b;
-        if (fabs(dx) <= 0.0000001) {                  // ninja.py:312-318 band-aid
-            dx = 0;
-            if (xpos == 50.51197510492316 || xpos == 49.23232124849253) dx = -0x1p-47;
-            if (xpos == 49.153536108584795) dx = 0x1p-47;
+    // One depenetration push (ninja.py:303-379) from the closest point (a, b), in two parts: push_eval is a pure function of
+    // (result, a, b) and the position -- the dependent chain of a wedged ninja -- and push_commit applies it.  The split lets the
+    // cooperative loop evaluate the push from a PREDICTED winner while the warp minimum is still being found (below).
+    struct Push { bool go; double dx, dy, inv_dist, norm_dx, norm_dy, depen_len; };
+    auto push_eval = [&](int result, double a, double b) -> Push {
+        Push t; t.go = false; t.dx = 0; t.dy = 0; t.inv_dist = 0; t.norm_dx = 0; t.norm_dy = 0; t.depen_len = 0;
+        if (result == 0) return t;
+        double ex = xpos - a; const double ey = ypos - b;
+        if (fabs(ex) <= 0.0000001) {                  // ninja.py:312-318 band-aid
+            ex = 0;
+            if (xpos == 50.51197510492316 || xpos == 49.23232124849253) ex = -0x1p-47;
+            if (xpos == 49.153536108584795) ex = 0x1p-47;
         }
-        double dist_sq = dx * dx + dy * dy;
-        if (dist_sq < 1e-16) return false;
-        double dist = SQRT(dist_sq);
-        double depen_len = NINJA_RADIUS - (result < 0 ? -dist : dist);     // dist * result, result = +-1: exact either way
-        if (depen_len < 0.0000001) return false;
-        double inv_dist = DIV(1.0, dist);
-        double norm_dx = dx * inv_dist, norm_dy = dy * inv_dist;
-        double depen_x = norm_dx * depen_len, depen_y = norm_dy * depen_len;
+        t.dx = ex; t.dy = ey;
+        const double dist_sq = ex * ex + ey * ey;
+        if (dist_sq < 1e-16) return t;
+        const double dist = SQRT(dist_sq);
+        t.depen_len = NINJA_RADIUS - (result < 0 ? -dist : dist);     // dist * result, result = +-1: exact either way
+        if (t.depen_len < 0.0000001) return t;
+        t.inv_dist = DIV(1.0, dist);
+        t.norm_dx = ex * t.inv_dist; t.norm_dy = ey * t.inv_dist;
+        t.go = true;
+        return t;
+    };
+    auto push_commit = [&](const Push& t) {
+        dx = t.dx; dy = t.dy;
+        const double depen_x = t.norm_dx * t.depen_len, depen_y = t.norm_dy * t.depen_len;
         pushed = true;
         xpos += depen_x; ypos += depen_y;
-        n.f[F_XCRUSH] += depen_x; n.f[F_YCRUSH] += depen_y; n.f[F_CRUSH_LEN] += depen_len;
-        double dot_product = xspeed * dx + yspeed * dy;
+        n.f[F_XCRUSH] += depen_x; n.f[F_YCRUSH] += depen_y; n.f[F_CRUSH_LEN] += t.depen_len;
+        const double dot_product = xspeed * dx + yspeed * dy;
         if (dot_product < 0) {
-            double cross_product = xspeed * dy - yspeed * dx;
-            double inv_dist_sq = inv_dist * inv_dist;
+            const double cross_product = xspeed * dy - yspeed * dx;
+            const double inv_dist_sq = t.inv_dist * t.inv_dist;
             xspeed = cross_product * inv_dist_sq * dy;
             // dx == 0 only via the band-aid's `dx = 0` (a Python int): -(int 0) is 0, not -0.0
             yspeed = cross_product * inv_dist_sq * (dx == 0 ? 0.0 : -dx);
         }
-        if (dy >= -0.0001) { n.i[I_CEILING_COUNT] += 1; n.f[F_CEIL_NX] += norm_dx; n.f[F_CEIL_NY] += norm_dy; }
-        else { n.i[I_FLOOR_COUNT] += 1; n.f[F_FLOOR_NX] += norm_dx; n.f[F_FLOOR_NY] += norm_dy; }
-        return true;
+        if (dy >= -0.0001) { n.i[I_CEILING_COUNT] += 1; n.f[F_CEIL_NX] += t.norm_dx; n.f[F_CEIL_NY] += t.norm_dy; }
+        else { n.i[I_FLOOR_COUNT] += 1; n.f[F_FLOOR_NX] += t.norm_dx; n.f[F_FLOOR_NY] += t.norm_dy; }
+    };
+    auto depen = [&](int result, double a, double b) -> bool {
+        const Push t = push_eval(result, a, b);
+        if (t.go) push_commit(t);
+        return t.go;
     };
     // Iteration 0 is pooled over the warp (and caches each lane's gathered list); iteration 1 runs per
     // lane on the cached list (5 % of substeps need it, i.e. most warps); iterations 2..31 are rare per
@@ -137,6 +151,7 @@ DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
         COOP_STATE(COOP_TAKE)
         n.i[I_CEILING_COUNT] = (int)wp.seg[o]; n.i[I_FLOOR_COUNT] = (int)wp.seg[32 + o];
         COOP_T(cacc, 5, ct)
+        int w1 = -1, w2 = -1;                                // winning lanes of the last two calls (-1: unknown)
         #pragma unroll 1
         for (int it = 2; it < 32; it++) {
             ncoop++;
@@ -190,15 +205,69 @@ DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
                 }
             }
 #endif
-            double a = 0, b = 0; int result = 0;
+            double a = 0, b = 0; int result = 0, w = -1;
             if (ns < 0) {                                    // list overflow: the owner's literal walk, then broadcast
                 double ea = 0, eb = 0;
                 if (lane == o) result = closest_point_exact(c.cell_hdr, c.segs, gx1, gy1, gx2, gy2, xpos, ypos, ea, eb);
                 a = __shfl_sync(FULL_MASK, ea, o); b = __shfl_sync(FULL_MASK, eb, o); result = __shfl_sync(FULL_MASK, result, o);
-            } else {
-                result = warp_closest_uniform(wp, c, o, ns, g, gx1, gy1, gx2, gy2, xpos, ypos, a, b, cacc, ct);
+            }
+#ifndef NPP_COOP_NOPRED
+            // Winner prediction.  A wedged ninja is pushed out of two segments in turn, so the closest segment of this call is
+            // the one of two calls back in 96 % of the calls (tools/iter_stats.py).  Every lane takes the predicted lane's
+            // closest point and evaluates the push from it while the warp minimum (redux + ballot) is in flight; the push is
+            // committed only once the real winner turned out to be the predicted lane (else it is re-evaluated from the real
+            // one): the selection leaves the dependent chain evaluate -> select -> push, nothing else changes.
+            else if (w2 >= 0) {
+                const double inf = __longlong_as_double(0x7ff0000000000000LL);
+                double d2 = inf, ea = 0, eb = 0; int er = 0; bool ix = false, ok = false;
+                if (lane < ns) ok = closest_eval(g, xpos, ypos, d2, ea, eb, er, ix);
+                if (!ok) { d2 = inf; er = 0; ix = false; }
+                const double sa = __shfl_sync(FULL_MASK, ea, w2), sb = __shfl_sync(FULL_MASK, eb, w2);
+                const int scode = __shfl_sync(FULL_MASK, (er & 3) | (ix ? 4 : 0), w2);
+                const int sr = (scode & 3) == 3 ? -1 : (scode & 3);
+                COOP_T(cacc, 0, ct)
+                // The speculative push, flat: push_eval's expressions without its early returns.
+                Push t;
+                t.dx = xpos - sa; t.dy = ypos - sb;
+                if (fabs(t.dx) <= 0.0000001) {                // ninja.py:312-318 band-aid
+                    t.dx = 0;
+                    if (xpos == 50.51197510492316 || xpos == 49.23232124849253) t.dx = -0x1p-47;
+                    if (xpos == 49.153536108584795) t.dx = 0x1p-47;
+                }
+                const double dist_sq = t.dx * t.dx + t.dy * t.dy;
+                const double dist = SQRT(dist_sq);
+                // The prediction holds iff no other lane can beat the predicted one in the reference's strict-< scan: it has the
+                // same closest point and side (then it does not matter which of the two wins), or a larger d2 (or the same d2 later
+                // in the list) -- beyond closest_fold's guard band when one of the two squares was flagged inexact.  ONE vote,
+                // issued behind the square root and read after the push.
+                const double sd = __shfl_sync(FULL_MASK, d2, w2);
+                const bool same = er == sr && __double_as_longlong(ea) == __double_as_longlong(sa) && __double_as_longlong(eb) == __double_as_longlong(sb);
+                const bool loses = (ix || (scode & 4)) ? (d2 > sd + 1e-10) : (d2 > sd || (d2 == sd && lane > w2));
+                const unsigned bad = __ballot_sync(FULL_MASK, ok && lane != w2 && !same && !loses);
+                t.depen_len = NINJA_RADIUS - (sr < 0 ? -dist : dist);
+                t.inv_dist = DIV(1.0, dist);
+                t.norm_dx = t.dx * t.inv_dist; t.norm_dy = t.dy * t.inv_dist;
+                t.go = sr != 0 && !(dist_sq < 1e-16) && !(t.depen_len < 0.0000001);
+                COOP_T(cacc, 2, ct)
+                w = w2;
+                if (bad) {                                   // mispredicted (or a flagged square): the full selection, the push again
+                    result = warp_select_uniform(wp, c, o, ns, ok, d2, ea, eb, er, ix, gx1, gy1, gx2, gy2, xpos, ypos, a, b, w);
+                    t = push_eval(result, a, b);
+                    // the ordered fold names no lane: keep predicting when it confirmed the predicted lane's point
+                    if (w < 0 && result == sr && __double_as_longlong(a) == __double_as_longlong(sa) && __double_as_longlong(b) == __double_as_longlong(sb)) w = w2;
+                }
+                COOP_T(cacc, 1, ct)
+                w2 = w1; w1 = w;
+                if (!t.go) break;
+                push_commit(t);
+                continue;
+            }
+#endif
+            else {
+                result = warp_closest_uniform(wp, c, o, ns, g, gx1, gy1, gx2, gy2, xpos, ypos, a, b, w, cacc, ct);
             }
             COOP_T(cacc, 1, ct)
+            w2 = w1; w1 = w;
             const bool go = depen(result, a, b);             // uniform: same inputs on every lane
             COOP_T(cacc, 2, ct)
             if (!go) break;

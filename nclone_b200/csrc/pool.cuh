@@ -507,39 +507,13 @@ DEV unsigned warp_first_min(double d2, bool ok) {
     return cand;
 }
 
-// Uniform variant for the cooperative depenetration loop: (x, y) is the served owner's position, already held by
-// every lane, and the result (a, b, result) is returned to every lane, so that all 32 lanes can run the push
-// redundantly -- no divergent owner-only section, no broadcast of the position and of the continue flag per
-// iteration.  The minimum is usually decided by the high words alone (one redux + one ballot).
-DEV int warp_closest_uniform(WarpPool& wp, const Ctx& c, int o, int ns, const SegC& g, double gx1, double gy1, double gx2, double gy2,
-                             double x, double y, double& pa, double& pb, long long* cacc, long long& ct) {
+// Ordered fold of the 32 lanes' evaluated segments by the owner lane (a square was flagged inexact: the guard-banded
+// strict-< scan of closest_fold, the literal walk when that is uncertain too), result broadcast to every lane.
+DEV int coop_ordered_fold(WarpPool& wp, const Ctx& c, int o, int ns, bool ok, double d2, double a, double b, int r, bool ix,
+                          double gx1, double gy1, double gx2, double gy2, double x, double y, double& pa, double& pb) {
     const int lane = threadIdx.x & 31;
     const double inf = __longlong_as_double(0x7ff0000000000000LL);
-    double d2 = inf, a = 0, b = 0; int r = 0; bool ix = false, ok = false;
-#ifdef NPP_COOP_EVAL_EXACT   // bounds test off the chain + exact squares instead of the flagged ones: measured 1-2 % slower
-    if (lane < ns) ok = closest_eval_nb(g, x, y, d2, a, b, r);
-#else
-    if (lane < ns) ok = closest_eval(g, x, y, d2, a, b, r, ix);
-#endif
-    if (!ok) d2 = inf;
-    COOP_T(cacc, 0, ct)
     int result = 0;
-    if (__ballot_sync(FULL_MASK, ok && ix) == 0) {
-        const long long bits = __double_as_longlong(d2);
-        const unsigned long long key = (unsigned long long)(bits ^ ((bits >> 63) | (long long)0x8000000000000000ULL));   // monotone in d2
-        const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
-        const unsigned mhi = __reduce_min_sync(FULL_MASK, hi);
-        unsigned cand = __ballot_sync(FULL_MASK, ok && hi == mhi);
-        if (cand & (cand - 1)) {                                             // several lanes share the high word: decide on the low one
-            const unsigned mlo = __reduce_min_sync(FULL_MASK, (ok && hi == mhi) ? lo : 0xffffffffu);
-            cand = __ballot_sync(FULL_MASK, ok && hi == mhi && lo == mlo);
-        }
-        if (cand) {                                                          // first minimum in list order (strict < scan, physics.py:170-176)
-            const int w = __ffs(cand) - 1;
-            pa = __shfl_sync(FULL_MASK, a, w); pb = __shfl_sync(FULL_MASK, b, w); result = __shfl_sync(FULL_MASK, r, w);
-        }
-        return result;
-    }
     wp.res[lane] = d2; wp.ra[lane] = a; wp.rb[lane] = b; wp.aux[lane] = (uint8_t)(!ok ? 2 : ((r < 0 ? 1 : 0) | (ix ? 4 : 0)));
     __syncwarp();
     double fa = 0, fb = 0;
@@ -558,6 +532,50 @@ DEV int warp_closest_uniform(WarpPool& wp, const Ctx& c, int o, int ns, const Se
     __syncwarp();
     pa = __shfl_sync(FULL_MASK, fa, o); pb = __shfl_sync(FULL_MASK, fb, o);
     return __shfl_sync(FULL_MASK, result, o);
+}
+// Selection half of the uniform query: from every lane's evaluated segment (ok, d2, a, b, r, ix) to the reference's strict-<
+// scan result on every lane; `win` = the winning lane (-1: none, or decided by the ordered fold).
+DEV int warp_select_uniform(WarpPool& wp, const Ctx& c, int o, int ns, bool ok, double d2, double a, double b, int r, bool ix,
+                            double gx1, double gy1, double gx2, double gy2, double x, double y, double& pa, double& pb, int& win) {
+    win = -1;
+    int result = 0;
+    if (__ballot_sync(FULL_MASK, ok && ix) == 0) {
+        const long long bits = __double_as_longlong(d2);
+        const unsigned long long key = (unsigned long long)(bits ^ ((bits >> 63) | (long long)0x8000000000000000ULL));   // monotone in d2
+        const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+        const unsigned mhi = __reduce_min_sync(FULL_MASK, hi);
+        unsigned cand = __ballot_sync(FULL_MASK, ok && hi == mhi);
+        if (cand & (cand - 1)) {                                             // several lanes share the high word: decide on the low one
+            const unsigned mlo = __reduce_min_sync(FULL_MASK, (ok && hi == mhi) ? lo : 0xffffffffu);
+            cand = __ballot_sync(FULL_MASK, ok && hi == mhi && lo == mlo);
+        }
+        if (cand) {                                                          // first minimum in list order (strict < scan, physics.py:170-176)
+            const int w = __ffs(cand) - 1;
+            win = w;
+            pa = __shfl_sync(FULL_MASK, a, w); pb = __shfl_sync(FULL_MASK, b, w); result = __shfl_sync(FULL_MASK, r, w);
+        }
+        return result;
+    }
+    return coop_ordered_fold(wp, c, o, ns, ok, d2, a, b, r, ix, gx1, gy1, gx2, gy2, x, y, pa, pb);
+}
+// Uniform variant for the cooperative depenetration loop: (x, y) is the served owner's position, already held by
+// every lane, and the result (a, b, result) is returned to every lane, so that all 32 lanes can run the push
+// redundantly -- no divergent owner-only section, no broadcast of the position and of the continue flag per
+// iteration.  The minimum is usually decided by the high words alone (one redux + one ballot).
+DEV int warp_closest_uniform(WarpPool& wp, const Ctx& c, int o, int ns, const SegC& g, double gx1, double gy1, double gx2, double gy2,
+                             double x, double y, double& pa, double& pb, int& win, long long* cacc, long long& ct) {
+    const int lane = threadIdx.x & 31;
+    win = -1;
+    const double inf = __longlong_as_double(0x7ff0000000000000LL);
+    double d2 = inf, a = 0, b = 0; int r = 0; bool ix = false, ok = false;
+#ifdef NPP_COOP_EVAL_EXACT   // bounds test off the chain + exact squares instead of the flagged ones: measured 1-2 % slower
+    if (lane < ns) ok = closest_eval_nb(g, x, y, d2, a, b, r);
+#else
+    if (lane < ns) ok = closest_eval(g, x, y, d2, a, b, r, ix);
+#endif
+    if (!ok) d2 = inf;
+    COOP_T(cacc, 0, ct)
+    return warp_select_uniform(wp, c, o, ns, ok, d2, a, b, r, ix, gx1, gy1, gx2, gy2, x, y, pa, pb, win);
 }
 // stash slots of the cooperative loop: 13 values per lane in the idle tails of the pool's result arrays
 DEV double& coop_slot(WarpPool& wp, int k, int l) { return k < 7 ? wp.res[32 * (k + 1) + l] : wp.ra[32 * (k - 6) + l]; }
