@@ -1,10 +1,13 @@
 """CUDA path (through the C ABI of include/nppsim.h) against the reference's own outputs
 (tests/golden, produced by the unmodified reference) and against the oracle.
 Bar: bit-exact -- every double compared by bit pattern, every int by value."""
+import os
+
 import numpy as np
 import pytest
 
 pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 from oracle import oracle, schema  # noqa: E402  (checker only)
 
@@ -267,6 +270,42 @@ def test_large_random_rollout_vs_oracle(golden_replays):
             badi = np.nonzero((gi != ni).any(1))[0]
             assert badf.size == 0 and badi.size == 0, (st, badf[:5], badi[:5], env_to_map[badf[:5]])
         sim.reset_terminal(2000)
+
+
+def test_wedged_ninja_cooperative_loop_vs_oracle():
+    """The kernel's critical path: a ninja wedged into a corner runs all 32 depenetration iterations of every substep
+    (ninja.py:303-379) through the warp-cooperative loop with winner prediction.  bench_data/wedges.npz holds three
+    levels + action prefixes that end in such a state (one against an arc, two against line segments); each is
+    continued with every Discrete(6) action held for 30 agent steps.  Full ninja record against the oracle after
+    every agent step, and the loop must actually have been taken."""
+    import torch
+    from nclone_b200 import BatchedSimulator
+    d = np.load(os.path.join(ROOT, "bench_data", "wedges.npz"))
+    K = len(d["lens"])
+    maps = [d["maps"][k, :d["lens"][k]] for k in range(K)]
+    pre = [d["acts"][d["act_off"][k]:d["act_off"][k + 1]] for k in range(K)]
+    env_to_map = np.repeat(np.arange(K), 6)
+    N = len(env_to_map)
+    steps = max(len(p) for p in pre) + 30
+    actions = np.zeros((steps, N), dtype=np.uint8)
+    for e in range(N):
+        p = pre[env_to_map[e]]
+        actions[:len(p), e] = p
+        actions[len(p):, e] = e % 6
+    sim = BatchedSimulator(N)
+    sim.load_maps(maps, env_to_map)
+    ref = _oracle_rollout(maps, env_to_map, actions, 4, 2000, 1)
+    most = 0
+    for st in range(steps):
+        sim.step(torch.from_numpy(actions[st]).cuda(), 4, True)
+        most = max(most, int(sim.warp_cost[0].item()) - 1)
+        _, nf, ni = ref[st]
+        gf = sim.nin_f.cpu().numpy().T; gi = sim.nin_i.cpu().numpy().T.astype(np.int64)
+        badf = np.nonzero((gf.view(np.int64) != nf.view(np.int64)).any(1))[0]
+        badi = np.nonzero((gi != ni).any(1))[0]
+        assert badf.size == 0 and badi.size == 0, (st, badf[:5], badi[:5])
+        sim.reset_terminal(2000)
+    assert most >= 1000, most      # several envs of the warp wedged in the same agent step (>= 354 iterations each)
 
 
 def test_basic_variant_vs_oracle_and_full_kernel():
