@@ -214,9 +214,11 @@ DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
 #ifndef NPP_COOP_NOPRED
             // Winner prediction.  A wedged ninja is pushed out of two segments in turn, so the closest segment of this call is
             // the one of two calls back in 96 % of the calls (tools/iter_stats.py).  Every lane takes the predicted lane's
-            // closest point and evaluates the push from it while the warp minimum (redux + ballot) is in flight; the push is
-            // committed only once the real winner turned out to be the predicted lane (else it is re-evaluated from the real
-            // one): the selection leaves the dependent chain evaluate -> select -> push, nothing else changes.
+            // closest point (two shuffles) and evaluates the push from it; ONE vote, issued behind the push's square root,
+            // checks that no other lane can win the reference's strict-< scan.  The push is committed only after the vote; on a
+            // miss the full selection (redux + ballots, ordered fold for flagged squares) runs and the push is evaluated again
+            // from the real winner.  The selection's dependent collectives leave the chain evaluate -> select -> push; results
+            // are those of the unpredicted loop by construction (profiles/r01_d_step_kernel.md).
             else if (w2 >= 0) {
                 const double inf = __longlong_as_double(0x7ff0000000000000LL);
                 double d2 = inf, ea = 0, eb = 0; int er = 0; bool ix = false, ok = false;
