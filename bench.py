@@ -35,6 +35,7 @@ WORKLOADS = {
     "c2": ("first_replay", 4096, "configs[1]: 4,096 envs on one level (exit + switch only), random Discrete(6)"),
     "c3": ("simplest_with_mines", 65536, "configs[2]: 65,536 envs/GPU over 4,096 distinct generated simplest_with_mines levels (x16), random Discrete(6)"),
     "c4": ("locked_doors", 131072, "configs[3]: 131,072 envs/GPU over 2,048 distinct generated levels with a locked door (x64), random Discrete(6)"),
+    "c5": ("bc_replays", 65536, "configs[4] throughput form (SURVEY 8(d) config 5): the 130 bc_replays levels (all 16 entity kinds, full kernel) replicated to 65,536 envs/GPU, random Discrete(6)"),
 }
 
 
@@ -43,6 +44,14 @@ def load_maps(fixture):
         g = np.load(os.path.join(ROOT, "tests", "golden", "bc_replays.npz"))
         md = g["map_data"][g["map_off"][0]:g["map_off"][1]].astype(np.float64)
         return md[None, :].copy(), np.array([len(md)], dtype=np.int32)
+    if fixture == "bc_replays":
+        g = np.load(os.path.join(ROOT, "tests", "golden", "bc_replays.npz"))
+        off = g["map_off"]
+        lens = np.diff(off).astype(np.int32)
+        arr = np.zeros((len(lens), int(lens.max())), dtype=np.float64)
+        for k in range(len(lens)):
+            arr[k, :lens[k]] = g["map_data"][off[k]:off[k + 1]]
+        return arr, lens
     d = np.load(os.path.join(ROOT, "bench_data", fixture + ".npz"))
     arr = d["ints"].astype(np.float64)
     arr[d["frac_row"], d["frac_col"]] = d["frac_val"]
@@ -164,6 +173,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-flush", action="store_true", help="do not flush L2 between timed steps")
     ap.add_argument("--async-groups", type=int, default=4, help="also time the batch stepped as this many independent groups on separate streams (0: skip)")
+    ap.add_argument("--placement", default="scattered", choices=["scattered", "adjacent"], help="caller's env -> level assignment: replicas of a level n_levels envs apart, or consecutive")
     ap.add_argument("--spread", type=int, default=300, help="untimed agent steps run first so envs sit at mixed episode phases")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -192,7 +202,7 @@ def main():
     M = len(arr)
     # shard: every rank owns its own env batch (weak scaling); ranks use different level rotations and seeds
     from nclone_b200.sharding import shard_env_to_map, reduce_rollout
-    env_to_map = shard_env_to_map(n_envs, rank, M)
+    env_to_map = shard_env_to_map(n_envs, rank, M, adjacent=(args.placement == "adjacent"))
     sim = BatchedSimulator(n_envs, device=dev)
     sim.load_maps([arr[k, :lens[k]] for k in range(M)], env_to_map)
 

@@ -13,8 +13,10 @@
  *   - every function returns 0 on success, <0 for an argument / map error (NPPSIM_E_*),
  *     >0 for a CUDA runtime error code; nppsim_last_error() describes the last failure
  *     on the calling thread;
- *   - launches are asynchronous on the given cudaStream_t (passed as void*); the library
- *     keeps no global mutable state, so one instance per device / stream is safe.
+ *   - launches are asynchronous on the given cudaStream_t (passed as void*); the library keeps
+ *     no simulation state of its own -- the only process-wide variables are the atomic launch
+ *     counter behind nppsim_launch_count() and per-device one-time kernel attributes -- so one
+ *     instance per device / stream is safe.
  */
 #ifndef NPPSIM_H
 #define NPPSIM_H
@@ -208,8 +210,7 @@ int nppsim_sq_mode(void);
 /* Test hook: counts (into *mismatches, device uint64, not cleared) the i for which the kernels' shared-reciprocal double division
  * div2(a1[i], a2[i], b[i]) differs in any bit from the device's own a1[i] / b[i], a2[i] / b[i]. */
 int nppsim_debug_div2(const double* a1_dev, const double* a2_dev, const double* b_dev, unsigned long long* mismatches_dev, int32_t n, void* stream);
-/* Test hook: non-zero forces every launch onto the full (all entity kinds) kernel; returns the previous setting. */
-int nppsim_debug_force_full_kernel(int on);
+/* (To run a basic level set on the full kernel -- the variant cross-check of the tests -- pass kind_mask = 0, "census unknown".) */
 
 /* Kernel launch count since library load (bench.py's gpu_launches claim). */
 int64_t nppsim_launch_count(void);

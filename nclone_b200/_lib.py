@@ -31,7 +31,7 @@ EXPORTS = (
     "nppsim_version", "nppsim_last_error", "nppsim_map_blob_bound", "nppsim_compile_map",
     "nppsim_reset", "nppsim_reset_terminal", "nppsim_step", "nppsim_step_actions", "nppsim_step_stream", "nppsim_replay_rows",
     "nppsim_step_host", "nppsim_launch_count",
-    "nppsim_observe", "nppsim_set_exit_positions", "nppsim_compile_maps_device", "nppsim_debug_sq", "nppsim_debug_div2", "nppsim_sq_mode", "nppsim_debug_force_full_kernel",
+    "nppsim_observe", "nppsim_set_exit_positions", "nppsim_compile_maps_device", "nppsim_debug_sq", "nppsim_debug_div2", "nppsim_sq_mode",
 )
 
 
@@ -41,11 +41,12 @@ def lib():
         return _lib
     path = os.environ.get("NPPSIM_LIB") or _build.LIB      # NPPSIM_LIB: A/B testing of kernel builds
     if path == _build.LIB and _build.needs_build():
-        try:
+        # Sources newer than the library: rebuild, and fail loudly if that does not work -- a stale binary must never
+        # pass for the code on disk.  Only a box without nvcc (the library then comes prebuilt with the snapshot) loads as is.
+        if _build.have_nvcc():
             _build.build()
-        except Exception:
-            if not os.path.exists(path):
-                raise
+        elif not os.path.exists(path):
+            raise RuntimeError("libnppsim.so is missing and there is no nvcc to build it")
     L = C.CDLL(path)
     vp, i32, i64 = C.c_void_p, C.c_int32, C.c_int64
     L.nppsim_version.restype = C.c_int
@@ -70,7 +71,6 @@ def lib():
     L.nppsim_debug_sq.argtypes = [vp, vp, i32, vp]; L.nppsim_debug_sq.restype = C.c_int
     L.nppsim_debug_div2.argtypes = [vp, vp, vp, vp, i32, vp]; L.nppsim_debug_div2.restype = C.c_int
     L.nppsim_sq_mode.restype = C.c_int
-    L.nppsim_debug_force_full_kernel.argtypes = [i32]; L.nppsim_debug_force_full_kernel.restype = C.c_int
     _lib = L
     return L
 

@@ -184,6 +184,12 @@ class BatchedSimulator:
         v._state = st
         return v
 
+    def force_full_kernel(self, on=True):
+        """Test hook: run this batch on the full (all entity kinds) step kernel whatever its level set holds, by
+        declaring the kind census unknown (nppsim_state_t.kind_mask = 0)."""
+        self._need_maps()
+        self._state.kind_mask = 0 if on else self.kind_mask
+
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 

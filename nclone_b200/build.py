@@ -26,6 +26,10 @@ def nvcc_path():
     return p
 
 
+def have_nvcc():
+    return bool(shutil.which("nvcc")) or os.path.exists("/usr/local/cuda/bin/nvcc")
+
+
 def needs_build():
     if not os.path.exists(LIB):
         return True

@@ -24,6 +24,7 @@
 //     order) is a rank computed per draft in parallel.
 #include <cuda_runtime.h>
 #include <atomic>
+#include <mutex>
 #include <cstdio>
 
 #include "map_blob.h"
@@ -452,13 +453,13 @@ __global__ void __launch_bounds__(MC_THREADS) compile_maps_kernel(const double* 
     }
 }
 
-thread_local char g_err[256] = "";
-
 }  // namespace
+
+extern thread_local char g_nppsim_err[256];       // nppsim_kernels.cu
+namespace { char (&g_err)[256] = g_nppsim_err; }
 
 extern std::atomic<long long> g_nppsim_launches;
 
-extern "C" const char* nppsim_compile_device_error(void) { return g_err; }
 
 extern "C" int nppsim_compile_maps_device(const double* map_data, int64_t row_stride, const int32_t* map_len, int32_t default_len,
                                           int32_t n_maps, uint8_t* blobs, int64_t blob_stride, int64_t* map_off, int32_t* status,
@@ -470,13 +471,24 @@ extern "C" int nppsim_compile_maps_device(const double* map_data, int64_t row_st
         return NPPSIM_E_ARG;
     }
     if (row_stride < 1235) { snprintf(g_err, sizeof(g_err), "row_stride shorter than 1235 values"); return NPPSIM_E_ARG; }
-    static const bool attr_set = [] {
-        cudaFuncSetAttribute(compile_maps_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Shared));
-        pack_tables_kernel<<<1, 64>>>();          // legacy stream: ordered before any later launch on a blocking stream; synchronise for the rest
-        cudaDeviceSynchronize();
-        return true;
-    }();
-    (void)attr_set;
+    // one-time setup PER DEVICE (function attributes and the __device__ tile table belong to the current device's context)
+    {
+        static std::mutex init_mu;
+        static bool init_done[64] = {false};
+        int dev = 0;
+        cudaError_t ie = cudaGetDevice(&dev);
+        std::lock_guard<std::mutex> lock(init_mu);
+        if (ie == cudaSuccess && (dev < 0 || dev >= 64 || !init_done[dev])) {
+            ie = cudaFuncSetAttribute(compile_maps_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Shared));
+            if (ie == cudaSuccess) {
+                pack_tables_kernel<<<1, 64>>>();      // legacy stream: ordered before any later launch on a blocking stream; synchronise for the rest
+                ie = cudaGetLastError();
+            }
+            if (ie == cudaSuccess) ie = cudaDeviceSynchronize();
+            if (ie == cudaSuccess && dev >= 0 && dev < 64) init_done[dev] = true;
+        }
+        if (ie != cudaSuccess) { snprintf(g_err, sizeof(g_err), "device compiler setup: %s", cudaGetErrorString(ie)); return (int)ie > 0 ? (int)ie : 1; }
+    }
     cudaStream_t s = (cudaStream_t)stream;
     cudaError_t e = cudaMemsetAsync(summary, 0, 4 * sizeof(int32_t), s);
     if (e == cudaSuccess) {

@@ -20,6 +20,7 @@
 #include "tile_tables.h"
 #include "../../include/nppsim.h"
 
+extern thread_local char g_nppsim_err[256];       // nppsim_kernels.cu: the buffer behind nppsim_last_error()
 namespace {
 
 struct Box { int x0, y0, x1, y1; };
@@ -49,12 +50,11 @@ struct Draft {               // entity in creation order
     NppDoor door; bool has_door;
 };
 
-thread_local char g_err[256] = "";
+char (&g_err)[256] = g_nppsim_err;
 int fail(int code, const char* msg) { std::snprintf(g_err, sizeof(g_err), "%s", msg); return code; }
 
 }  // namespace
 
-extern "C" const char* nppsim_compile_error(void) { return g_err; }
 
 extern "C" int64_t nppsim_map_blob_bound(int32_t map_len) {
     int64_t max_ent = map_len > 1230 ? (map_len - 1230) / 5 * 2 + 2 : 2;
@@ -195,7 +195,8 @@ extern "C" int nppsim_compile_map(const double* m, int32_t len, uint8_t* out, in
             if (index + 9 < len) index += (m[index + 7] != 0 && m[index + 8] == 0 && m[index + 9] == 0) ? 10 : 9;
             else index += 9;
         } else index += 5;
-        if (drafts.size() > 60000) return fail(NPPSIM_E_CAPACITY, "more than 60000 entities");
+        // NppStaticEnt.dyn / .aux are int16 and the kernels index ent_flag with 32-bit (id * stride): 32767 entities is the format's limit
+        if (drafts.size() > 32767) return fail(NPPSIM_E_CAPACITY, "more than 32767 entities");
     }
     // entity_dic order: keys 1..28 ascending, creation order inside a key (nsim.py:190-192)
     std::vector<int> order;

@@ -4,14 +4,16 @@
 
 #include <atomic>
 #include <cstring>
+#include <mutex>
 
 std::atomic<long long> g_nppsim_launches{0};     // shared with map_compile_device.cu
 
+thread_local char g_nppsim_err[256] = "";         // nppsim_last_error(): one buffer for all three translation units
+
 namespace {
 
-thread_local char g_err[256] = "";
+char (&g_err)[256] = g_nppsim_err;
 std::atomic<long long>& g_launches = g_nppsim_launches;
-bool g_force_full = false;     // test hook: run every level set on the full kernel
 
 int fail(int code, const char* msg) { snprintf(g_err, sizeof(g_err), "%s", msg); return code; }
 int cuda_fail(cudaError_t e, const char* what) {
@@ -120,6 +122,8 @@ __global__ void __launch_bounds__(128) reset_kernel(nppsim_state_t st, const uin
 #ifndef STEP_BLOCK
 #define STEP_BLOCK 128
 #endif
+// __launch_bounds__ minimum: 1 leaves the register budget to ptxas (254-255 per thread, so TWO 128-thread blocks are resident
+// per SM); 3 / 4 cap it at 168 / 128 registers and spill the ninja record (measured -14 % / -20 %)
 #ifndef STEP_BLOCKS_PER_SM
 #define STEP_BLOCKS_PER_SM 1
 #endif
@@ -408,6 +412,7 @@ int check_state(const nppsim_state_t* st) {
         return fail(NPPSIM_E_ARG, "a required state pointer is NULL");
     if ((st->ent_cap > 0 && !st->ent_flag) || (st->dyn_cap > 0 && (!st->dyn_f || !st->dyn_i)))
         return fail(NPPSIM_E_ARG, "entity buffers missing for a non-zero capacity");
+    if (st->stride != 0 && st->stride < (uint32_t)st->n_envs) return fail(NPPSIM_E_ARG, "stride must be 0 or >= n_envs");
     return 0;
 }
 
@@ -435,18 +440,26 @@ int launch_step(const nppsim_state_t* st, const int8_t* hor, const int8_t* jump,
     const int grid = (st->n_envs + block - 1) / block;
     // shared-memory carve-out: room for the two blocks per SM the register file admits and not more -- the rest
     // of the 256 KB stays L1 for the level blobs (max-shared left 28 KB of L1: hit rate 40 % instead of 66 %)
-    static const bool carveout_set = [] {
-        const int resident = STEP_BLOCKS_PER_SM > 2 ? STEP_BLOCKS_PER_SM : 2;
-        const int carve = (int)((resident * (STEP_SMEM + 1024) * 100 + 233471) / 233472) + 1;
-        cudaFuncSetAttribute(sim_basic::step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
-        cudaFuncSetAttribute(sim_full::step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
-        cudaFuncSetAttribute(sim_basic::step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)STEP_SMEM);
-        cudaFuncSetAttribute(sim_full::step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)STEP_SMEM);
-        return true;
-    }();
-    (void)carveout_set;
+    // (function attributes belong to the current device's context: set once per device, results checked)
+    {
+        static std::mutex init_mu;
+        static bool init_done[64] = {false};
+        int dev = 0;
+        cudaError_t ie = cudaGetDevice(&dev);
+        std::lock_guard<std::mutex> lock(init_mu);
+        if (ie == cudaSuccess && (dev < 0 || dev >= 64 || !init_done[dev])) {
+            const int resident = STEP_BLOCKS_PER_SM > 2 ? STEP_BLOCKS_PER_SM : 2;
+            const int carve = (int)((resident * (STEP_SMEM + 1024) * 100 + 233471) / 233472) + 1;
+            ie = cudaFuncSetAttribute(sim_basic::step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+            if (ie == cudaSuccess) ie = cudaFuncSetAttribute(sim_full::step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+            if (ie == cudaSuccess) ie = cudaFuncSetAttribute(sim_basic::step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)STEP_SMEM);
+            if (ie == cudaSuccess) ie = cudaFuncSetAttribute(sim_full::step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)STEP_SMEM);
+            if (ie == cudaSuccess && dev >= 0 && dev < 64) init_done[dev] = true;
+        }
+        if (ie != cudaSuccess) return cuda_fail(ie, "step kernel attributes");
+    }
     // kind_mask == 0: census unknown (older callers) -> the full kernel
-    const bool basic = st->kind_mask != 0 && (st->kind_mask & ~NPP_BASIC_MASK) == 0 && !g_force_full;
+    const bool basic = st->kind_mask != 0 && (st->kind_mask & ~NPP_BASIC_MASK) == 0;
     auto kernel = basic ? sim_basic::step_kernel : sim_full::step_kernel;
     kernel<<<grid, block, STEP_SMEM, (cudaStream_t)stream>>>(*st, hor, jump, actions, input_ticks, n_ticks, tick_limit, stop_on_terminal, frames_executed, sp);
     g_launches++;
@@ -466,22 +479,14 @@ int launch_step(const nppsim_state_t* st, const int8_t* hor, const int8_t* jump,
 extern "C" {
 
 int nppsim_version(void) { return NPPSIM_VERSION; }
-const char* nppsim_compile_error(void);
-const char* nppsim_compile_device_error(void);
-const char* nppsim_last_error(void) {
-    if (g_err[0]) return g_err;
-    const char* d = nppsim_compile_device_error();
-    return d[0] ? d : nppsim_compile_error();
-}
+const char* nppsim_last_error(void) { return g_nppsim_err; }
 int64_t nppsim_launch_count(void) { return (int64_t)g_launches.load(); }
 int nppsim_sq_mode(void) { return NPP_SQ_MODE; }
-int nppsim_debug_force_full_kernel(int on) { int was = g_force_full; g_force_full = on != 0; return was; }
 #ifdef NPP_PROFILE
 int nppsim_debug_warp_cycles(unsigned long long* out, unsigned long long* phases, int n, int reset) {
     cudaDeviceSynchronize();
     if (out) cudaMemcpyFromSymbol(out, g_warp_cycles, sizeof(unsigned long long) * n);
     if (phases) cudaMemcpyFromSymbol(phases, g_warp_phase, sizeof(unsigned long long) * n * 4);
-    if (reset) cudaMemset((void*)0, 0, 0);
     return 0;
 }
 int nppsim_debug_warp_span(unsigned long long* out, int n) {

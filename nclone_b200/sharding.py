@@ -11,10 +11,15 @@ def shard_env_range(total_envs, rank, world):
     return lo, lo + base + (1 if rank < rem else 0)
 
 
-def shard_env_to_map(envs_per_rank, rank, n_maps, stride=977):
+def shard_env_to_map(envs_per_rank, rank, n_maps, stride=977, adjacent=False):
     """Weak scaling: every rank owns `envs_per_rank` envs; level assignment is rotated per rank so
-    ranks do not all touch the same levels in the same order."""
-    return (np.arange(envs_per_rank, dtype=np.int64) + rank * stride) % n_maps
+    ranks do not all touch the same levels in the same order.  Default: env i -> level i % n_maps (the replicas
+    of a level are n_maps envs apart); adjacent=True: the replicas of a level are consecutive envs."""
+    e = np.arange(envs_per_rank, dtype=np.int64)
+    if adjacent:
+        reps = max(1, -(-int(envs_per_rank) // int(n_maps)))
+        return (e // reps + rank * stride) % n_maps
+    return (e + rank * stride) % n_maps
 
 
 def reduce_rollout(elapsed_ms, work, stats, dist=None):

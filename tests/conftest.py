@@ -53,3 +53,10 @@ def golden_generated():
 @pytest.fixture(scope="session")
 def golden_curriculum():
     return Golden(os.path.join(GOLDEN, "curriculum.npz"))
+
+
+@pytest.fixture(scope="session")
+def golden_doors():
+    """Synthesised regular-door / trap-door / shove-thwump levels and the reference's own scenario maps
+    (oracle/gen_golden_doors.py, outputs of the unmodified reference)."""
+    return Golden(os.path.join(GOLDEN, "doors.npz"))

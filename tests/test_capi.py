@@ -100,6 +100,29 @@ def test_map_compiler_edge_cases():
     assert t.n_ent == 0 and (t.tiles.reshape(44, 25)[1:17, 1] == 0).all()
 
 
+def test_map_compiler_capacity_is_an_error_not_truncation():
+    """include/nppsim.h: "capacity exceeded: an error at load, never truncation".  NppStaticEnt.dyn / .aux are int16, so a
+    level with more than 32,767 entities must be refused (NPPSIM_E_CAPACITY), not wrapped to negative slot numbers."""
+    n = 32768
+    md = np.zeros(1235 + 5 * n); md[1231] = 22; md[1232] = 22
+    rec = md[1235:].reshape(n, 5)
+    rec[:, 0] = 17; rec[:, 1] = 40 + (np.arange(n) % 100); rec[:, 2] = 40 + (np.arange(n) // 100 % 60)     # bounce blocks: one slot each
+    with pytest.raises(ValueError, match=r"\(-3\).*entities"):
+        compile_map(md)
+    t = MapTables(compile_map(md[:1235 + 5 * 32767]))
+    assert t.n_ent == 32767 and t.n_dyn == 32767 and int(t.ents["dyn"].min()) == 0 and int(t.ents["dyn"].max()) == 32766
+
+
+def test_state_stride_is_validated():
+    L = lib()
+    st = NppsimState()
+    st.n_envs, st.stride = 64, 32
+    for name in ("nin_f", "nin_i", "env_i", "env_map", "map_blob", "map_off"):
+        setattr(st, name, 0x1000)                       # never dereferenced: check_state runs before any launch
+    assert L.nppsim_reset(C.byref(st), None, 0, None) == -1
+    assert b"stride" in L.nppsim_last_error()
+
+
 def test_no_cpu_fallback():
     import torch
     if torch.cuda.is_available():

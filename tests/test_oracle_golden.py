@@ -65,6 +65,19 @@ def test_oracle_curriculum_repositioning_bit_exact(golden_curriculum):
         s2.apply_curriculum((100.0, 100.0), (200.0, 200.0))
 
 
+def test_oracle_doors_and_scenario_maps_bit_exact(golden_doors):
+    """Rows no reference replay exercises: regular doors (entity_door_regular.py:38-63, type-5 records injected into real
+    levels, on the ninja's path and across drone / thwump paths), trap doors, shove thwumps; plus the reference's 17
+    test_maps, 5 official maps and 8 bc_replays_tmp replays.  Fixtures: the unmodified reference (oracle/gen_golden_doors.py)."""
+    g = golden_doors
+    frames = sum(_check(g.traj(i)) for i in range(len(g)))
+    assert frames == 52396 and len(g) == 163
+    st = dict(zip((str(n) for n in g.d["stats_names"]), (int(v) for v in g.d["stats"])))
+    assert st["door_reclosed"] >= 20 and st["trap_closed"] >= 10 and st["shwump_activated"] >= 10 and st["door_on_mover_path"] >= 20
+    groups = {n.split("/")[0] for n in g.names}
+    assert groups == {"door5", "trap8", "shwump28", "testmap", "official", "tmp"}
+
+
 def test_pow_is_libm_not_multiply():
     """H1: x**2 is libm pow; the oracle must not have folded it to x*x."""
     import ctypes as C

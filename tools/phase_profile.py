@@ -5,7 +5,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from nclone_b200 import build as b
-lib = os.path.join(ROOT, "variants", "profile.so")
+lib = next((a.split("=", 1)[1] for a in sys.argv[1:] if a.startswith("--lib=")), os.path.join(ROOT, "variants", "profile.so"))
 os.makedirs(os.path.dirname(lib), exist_ok=True)
 if not os.path.exists(lib) or "--rebuild" in sys.argv:
     cmd = [b.nvcc_path()] + b.NVCC_FLAGS + ["-DNPP_PROFILE", "-o", lib] + [os.path.join(b.CSRC, s) for s in b.SOURCES]
@@ -16,7 +16,7 @@ import bench
 from nclone_b200 import BatchedSimulator
 from nclone_b200._lib import lib as L
 n_envs = int(sys.argv[1]) if len(sys.argv) > 1 and sys.argv[1].isdigit() else 65536
-fixture = next((a for a in sys.argv[1:] if a in ("simplest_with_mines", "locked_doors")), "simplest_with_mines")
+fixture = next((a for a in sys.argv[1:] if a in ("simplest_with_mines", "locked_doors", "bc_replays", "first_replay")), "simplest_with_mines")
 arr, lens = bench.load_maps(fixture)
 sim = BatchedSimulator(n_envs)
 sim.load_maps([arr[k, :lens[k]] for k in range(len(arr))], np.arange(n_envs) % len(arr))

@@ -1,0 +1,20 @@
+#!/bin/bash
+# round 2, GPU call 1: parity of the per-lane depenetration loop, A/B against the cooperative loop, first numbers for sim_full (c5)
+mkdir -p gpurun_out/r02
+O=gpurun_out/r02
+nvidia-smi --query-gpu=name,clocks.max.sm --format=csv,noheader > $O/gpu.txt
+echo "== parity (lane.so)" ; NPPSIM_LIB=$PWD/variants/lane.so timeout 600 python -m pytest tests/test_gpu_parity.py -x -q -m gpu > $O/parity_lane.log 2>&1; tail -3 $O/parity_lane.log
+summ() { python -c "
+import sys, json
+l = json.loads(sys.stdin.read().strip().split('\n')[-1])
+print('$1', 'value %.1fM e2e %.1fM step_kernel %.3f ms reset %.3f ms' % (l['value'] / 1e6, l['e2e']['value'] / 1e6, l['kernel_ms']['step_kernel'], l['kernel_ms']['reset_kernel']))"; }
+for so in base lane; do
+  echo "== wedge $so"; NPPSIM_LIB=$PWD/variants/$so.so timeout 300 python tools/wedge_bench.py 30 2>&1 | grep wedge
+  for cfg in "c3 65536 scattered" "c3 65536 adjacent" "c3 131072 scattered" "c4 131072 scattered" "c4 131072 adjacent" "c5 65536 scattered" "c2 4096 scattered"; do
+    set -- $cfg
+    NPPSIM_LIB=$PWD/variants/$so.so timeout 600 python bench.py --workload $1 --envs $2 --placement $3 --steps 40 --warmup 5 --no-cpu-baseline --async-groups 0 2>$O/err_${so}_$1_$2_$3.log | tail -1 > $O/bench_${so}_$1_$2_$3.json
+    summ "$so $1 $2 $3" < $O/bench_${so}_$1_$2_$3.json
+  done
+done
+echo "== phase profile c5 (sim_full)"; timeout 600 python tools/phase_profile.py 65536 bc_replays --lib=$PWD/variants/base_prof.so > $O/phase_c5_base.txt 2>&1; head -20 $O/phase_c5_base.txt
+echo "== phase profile c3 lane"; timeout 600 python tools/phase_profile.py 65536 --lib=$PWD/variants/lane_prof.so > $O/phase_c3_lane.txt 2>&1; head -40 $O/phase_c3_lane.txt
