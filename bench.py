@@ -231,6 +231,7 @@ def main():
     torch.cuda.synchronize(dev)
     ticks0 = sim.total_ticks()
     launches0 = sim.launch_count()
+    handoffs0 = sim.handoff_count()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
           for _ in range(args.steps)]
     for s in range(args.steps):
@@ -245,6 +246,8 @@ def main():
     if world > 1:
         dist.barrier()
     launches = sim.launch_count() - launches0
+    handoff_info = {"enabled": sim.handoff is not None, "mid_launch_per_step": (sim.handoff_count() - handoffs0) / args.steps,
+                    "solo_start_queue": sim.solo_queue_length(), "status": sim.handoff_status()}
     step_ms = np.array([e[0].elapsed_time(e[1]) for e in ev]); reset_ms = np.array([e[1].elapsed_time(e[2]) for e in ev])
     elapsed_ms = float(step_ms.sum() + reset_ms.sum())
     ticks = sim.total_ticks() - ticks0
@@ -351,7 +354,7 @@ def main():
         "kernel_ms": {"step_kernel": float(step_ms.mean()), "reset_kernel": float(reset_ms.mean())},
         "agent_steps_per_s": value / FRAME_SKIP,
         "episode_stats": {"episodes": int(stats[0]), "wins": int(stats[1]), "deaths": int(stats[2]), "truncations": int(stats[3])},
-        "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
+        "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks, "handoff": handoff_info,
     }
     if grp_ms > 0:
         line["async_groups"] = {"groups": args.async_groups, "value": grp_ticks_all / (grp_ms / 1000.0), "unit": "env-steps/s",

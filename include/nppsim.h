@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define NPPSIM_VERSION 100
+#define NPPSIM_VERSION 101
 
 #define NPPSIM_E_ARG      (-1)
 #define NPPSIM_E_MAP      (-2)   /* malformed map_data (the reference raises KeyError/IndexError/ValueError) */
@@ -45,7 +45,9 @@ extern "C" {
 #define NPPSIM_ENV_SWFRAME  3   /* sim.frame at which the exit switch was taken, -1 if not yet */
 #define NPPSIM_ENV_ORDER    4   /* 0: grid lists in creation order (load/reset); 1: entity_dic order (fast_reset) */
 #define NPPSIM_ENV_TICKS   5   /* ticks executed since load_maps (wraps at 2^31), for throughput accounting */
-#define NPPSIM_NENV 6
+#define NPPSIM_ENV_WEDGE   6   /* == the tag of a handoff queue (nppsim_state_t.handoff): the env is among that queue's initial
+                                  entries and starts the next launch on a solo warp; written only between launches */
+#define NPPSIM_NENV 7
 
 #define NPPSIM_EV_EXIT_SWITCH 1  /* entity_exit_switch.py:128-129 -> gym_env.invalidate_switch_cache() */
 #define NPPSIM_EV_LOCKED_DOOR 2  /* entity_door_locked.py:66-67 */
@@ -80,7 +82,25 @@ typedef struct {
                                    NULL = identity.  Rewritten by nppsim_step* after each launch when warp_cost is set. */
     uint32_t* warp_cost;        /* optional [ceil(N/32)]: device-clock cost of each group in the last launch (written by
                                    the step kernel), the key of the longest-first order */
+    const int32_t* ext_of;      /* optional [N]: state column i holds the caller's env ext_of[i] (a permutation).  The engine
+                                   may keep envs in any order -- BatchedSimulator puts the envs of a level next to each other, so
+                                   that the lanes of a warp walk the same level tables and run the same entity loops -- while
+                                   EVERY per-env array that crosses this interface (actions, hor / jump rows, tick_limit,
+                                   frames_executed, masks, stream offsets, row_off, switch_xy / door_xy, status, observation
+                                   outputs, nppsim_step_host's block) stays in the caller's env order.  NULL = identity. */
+    int32_t*  handoff;          /* optional [NPPSIM_HANDOFF_WORDS]: queue through which envs whose ninja is wedged in a corner (all
+                                   32 depenetration iterations of every substep, ninja.py:303-379) leave their home lane and run
+                                   their ticks alone on "solo" warps at the front of the grid -- from the start of a launch when
+                                   their previous tick was wedged, else from the end of their first wedged tick.  The caller
+                                   zero-initialises it once and sets word [6] to a non-zero tag unique among the queues used
+                                   on the same env arrays (sub-batches: one queue each); the library maintains the rest.
+                                   NULL: every env stays in its home lane.  Results are identical either way. */
 } nppsim_state_t;
+#define NPPSIM_HANDOFF_CAP   4096
+#define NPPSIM_HANDOFF_HDR   8      /* [0] entries reserved, [1] tickets taken, [2] regular blocks finished (per launch); [3] error
+                                       bits, [4] mid-launch handoffs so far (both sticky); [5] length of the next launch's list;
+                                       [6] tag (caller); [7] initial entries of the current launch */
+#define NPPSIM_HANDOFF_WORDS (NPPSIM_HANDOFF_HDR + 2 * NPPSIM_HANDOFF_CAP)
 
 /* Per-env input streams for nppsim_step_stream: env i owns data[offset[i] .. offset[i+1]) -- ragged, no padding. */
 #define NPPSIM_STREAM_ACTIONS      0   /* Discrete(6) actions, ACTION_TO_INPUTS (action_replayer.py:30-37); > 5 -> NOOP (:236-240) */
@@ -187,13 +207,19 @@ int nppsim_step_stream(const nppsim_state_t* st, const nppsim_input_stream_t* in
 int nppsim_replay_rows(const nppsim_state_t* st, const nppsim_input_stream_t* in, const int64_t* row_off, int32_t obs_tick,
                        int32_t frame_skip, float* game_state, double* pos, uint8_t* flags, int32_t* frame, void* stream);
 
-/* nppsim_step_host: the call a host-resident caller makes (one NppEnvironment.step worth of
- * physics for the batch): copies `actions_host` [N] to `actions_dev`, runs nppsim_step_actions,
- * and copies back ninja (xpos, ypos, xspeed, yspeed) [4][N] doubles and the state byte [N]
- * into host buffers, then synchronises the stream. */
+/* nppsim_step_host: the call a host-resident caller makes (one NppEnvironment.step worth of physics -- and, with
+ * with_obs != 0, of the observations the wrapper pulls every step, base_environment.py:2822, 3107 -- for the batch):
+ * copies `actions_host` [N] to `actions_dev`, runs nppsim_step_actions, packs the results in the CALLER's env order into
+ * `staging_dev` and copies that block to `out_host` with ONE device-to-host copy, then synchronises the stream.
+ * Block layout (nppsim_host_block_bytes(N, with_obs) bytes; staging_dev 8-byte aligned, out_host pinned for speed):
+ *   [0, 32N)      f64 [4][N]   ninja xpos, ypos, xspeed, yspeed
+ *   [32N, 36N)    i32 [N]      ninja state
+ *   [36N, 196N)   f32 [N][40]  NPlayHeadless.get_ninja_state (nplay_headless.py:735-917)        -- with_obs only
+ *   [196N, 202N)  u8  [N][6]   Ninja.get_valid_action_mask (ninja.py:628-839), no path hints      -- with_obs only */
+int64_t nppsim_host_block_bytes(int32_t n_envs, int32_t with_obs);
 int nppsim_step_host(const nppsim_state_t* st, const uint8_t* actions_host, uint8_t* actions_dev,
-                     int32_t n_ticks, int32_t stop_on_terminal, double* pos_vel_host, int32_t* state_host,
-                     void* stream);
+                     int32_t n_ticks, int32_t stop_on_terminal, uint8_t* staging_dev, uint8_t* out_host,
+                     int32_t with_obs, void* stream);
 
 /* nppsim_observe: the two per-step observation primitives the env wrapper calls.
  *   ninja_state_out  optional device float32 [N][40]: NPlayHeadless.get_ninja_state (nplay_headless.py:735-917);

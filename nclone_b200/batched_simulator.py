@@ -17,10 +17,21 @@ from .map_compile import compile_map, content_key, MapTables
 
 
 class BatchedSimulator:
-    def __init__(self, n_envs, device="cuda:0"):
+    def __init__(self, n_envs, device="cuda:0", handoff=None, placement="level"):
+        """handoff: run wedged envs on solo warps (nppsim_state_t.handoff; identical results, shorter step kernel).
+        Default: on for batches of at least 1,024 envs.
+        placement: "level" (default) keeps the envs of one level in consecutive state columns, whatever order the caller
+        numbers them in -- the lanes of a warp then read the same level tables and run the same entity loops -- and
+        every per-env array of this API stays in the caller's order (nppsim_state_t.ext_of); "caller": columns = env ids."""
         if not torch.cuda.is_available():
             raise RuntimeError("BatchedSimulator needs a CUDA device (there is no CPU fallback)")
         self.n_envs = int(n_envs)
+        self.use_handoff = (int(n_envs) >= 1024) if handoff is None else bool(handoff)
+        if placement not in ("level", "caller"):
+            raise ValueError("placement must be 'level' or 'caller'")
+        self.placement = placement
+        self.slot_env = None        # numpy [N]: caller env id of state column s (None: identity)
+        self._slot_of = None        # device int64 [N]: state column of caller env e
         self.device = torch.device(device)
         self.L = lib()
         self.maps = []          # MapTables per distinct level
@@ -63,7 +74,7 @@ class BatchedSimulator:
         self.map_blob = torch.from_numpy(host_blob).to(dev)
         self.map_off = torch.from_numpy(offs).to(dev)
         self.env_map_host = remap[env_to_map].astype(np.int32)
-        self.env_map = torch.from_numpy(self.env_map_host).to(dev)
+        self._place(self.env_map_host)
         kind_mask = 0
         for t in self.maps:
             kind_mask |= t.kind_mask           # entity-kind census of the level set -> step-kernel variant
@@ -110,34 +121,70 @@ class BatchedSimulator:
         self._blob_stride = stride
         self.maps = _DeviceMaps(self.map_blob, stride, M)
         self._keys = {}
-        self.env_map = env_map
         self.env_map_host = env_map.cpu().numpy()
+        self._place(self.env_map_host)
         self._alloc_state(M, ent_cap, dyn_cap, kind_mask)
         self.reset()
+
+    def _place(self, env_map_host):
+        """State-column order (placement='level'): envs sorted by level, stable, unless that is the caller's order anyway
+        or no two envs share a level.  Sets env_map (device, column order), slot_env / _slot_of / ext_of."""
+        N, dev = self.n_envs, self.device
+        order = None
+        if self.placement == "level" and N > 1:
+            o = np.argsort(env_map_host, kind="stable")
+            if not np.array_equal(o, np.arange(N)) and len(np.unique(env_map_host)) < N:
+                order = o
+        if order is None:
+            self.slot_env, self._slot_of, self.ext_of = None, None, None
+            self.env_map = torch.from_numpy(np.ascontiguousarray(env_map_host)).to(dev)
+        else:
+            self.slot_env = order.astype(np.int64)
+            inv = np.empty(N, dtype=np.int64); inv[order] = np.arange(N)
+            self._slot_of = torch.from_numpy(inv).to(dev)
+            self.ext_of = torch.from_numpy(order.astype(np.int32)).to(dev)
+            self.env_map = torch.from_numpy(np.ascontiguousarray(env_map_host[order])).to(dev)
+
+    # state tensors in the CALLER's env order (copies when the engine keeps another column order; the raw column-order
+    # tensors are _nin_f ... _dyn_i)
+    def _ext(self, t):
+        return t if self._slot_of is None else t[..., self._slot_of]
+
+    nin_f = property(lambda self: self._ext(self._nin_f))
+    nin_i = property(lambda self: self._ext(self._nin_i))
+    env_i = property(lambda self: self._ext(self._env_i))
+    ent_flag = property(lambda self: self._ext(self._ent_flag))
+    dyn_f = property(lambda self: self._ext(self._dyn_f))
+    dyn_i = property(lambda self: self._ext(self._dyn_i))
+    frames_executed = property(lambda self: self._frames_executed)         # written by the kernels in caller order
 
     def _alloc_state(self, n_blobs, ent_cap, dyn_cap, kind_mask):
         N, dev = self.n_envs, self.device
         self._exit_cache = None
         self.ent_cap = max(1, int(ent_cap))
         self.dyn_cap = max(1, int(dyn_cap))
-        self.nin_f = torch.zeros((FD.NF, N), dtype=torch.float64, device=dev)
-        self.nin_i = torch.zeros((FD.NI, N), dtype=torch.int32, device=dev)
-        self.env_i = torch.zeros((FD.NENV, N), dtype=torch.int32, device=dev)
-        self.ent_flag = torch.zeros((self.ent_cap, N), dtype=torch.uint8, device=dev)
-        self.dyn_f = torch.zeros((self.dyn_cap * 4, N), dtype=torch.float64, device=dev)
-        self.dyn_i = torch.zeros((self.dyn_cap * 3, N), dtype=torch.int32, device=dev)
-        self.frames_executed = torch.zeros(N, dtype=torch.int32, device=dev)
+        self._nin_f = torch.zeros((FD.NF, N), dtype=torch.float64, device=dev)
+        self._nin_i = torch.zeros((FD.NI, N), dtype=torch.int32, device=dev)
+        self._env_i = torch.zeros((FD.NENV, N), dtype=torch.int32, device=dev)
+        self._ent_flag = torch.zeros((self.ent_cap, N), dtype=torch.uint8, device=dev)
+        self._dyn_f = torch.zeros((self.dyn_cap * 4, N), dtype=torch.float64, device=dev)
+        self._dyn_i = torch.zeros((self.dyn_cap * 3, N), dtype=torch.int32, device=dev)
+        self._frames_executed = torch.zeros(N, dtype=torch.int32, device=dev)
         self._actions_dev = torch.zeros(N, dtype=torch.uint8, device=dev)
+        self._staging = torch.zeros(int(self.L.nppsim_host_block_bytes(N, 1)) + 8, dtype=torch.uint8, device=dev)
         self.stats = torch.zeros(4, dtype=torch.int64, device=dev)
         st = NppsimState()
         st.n_envs, st.ent_cap, st.dyn_cap, st.n_maps = N, self.ent_cap, self.dyn_cap, int(n_blobs)
-        st.nin_f, st.nin_i, st.env_i = self.nin_f.data_ptr(), self.nin_i.data_ptr(), self.env_i.data_ptr()
-        st.ent_flag, st.dyn_f, st.dyn_i = self.ent_flag.data_ptr(), self.dyn_f.data_ptr(), self.dyn_i.data_ptr()
+        st.nin_f, st.nin_i, st.env_i = self._nin_f.data_ptr(), self._nin_i.data_ptr(), self._env_i.data_ptr()
+        st.ent_flag, st.dyn_f, st.dyn_i = self._ent_flag.data_ptr(), self._dyn_f.data_ptr(), self._dyn_i.data_ptr()
         st.env_map, st.map_blob, st.map_off = self.env_map.data_ptr(), self.map_blob.data_ptr(), self.map_off.data_ptr()
+        st.ext_of = self.ext_of.data_ptr() if self.ext_of is not None else None
         nw = (N + 31) // 32
         self.warp_order = torch.arange(nw, dtype=torch.int32, device=dev)      # longest-first launch order (csrc/sim_variant.inc)
         self.warp_cost = torch.zeros(nw, dtype=torch.int32, device=dev)
         st.warp_order, st.warp_cost = self.warp_order.data_ptr(), self.warp_cost.data_ptr()
+        self.handoff = self._new_handoff() if self.use_handoff else None
+        st.handoff = self.handoff.data_ptr() if self.handoff is not None else None
         self.kind_mask = int(kind_mask)
         st.kind_mask = self.kind_mask
         self._state = st
@@ -159,16 +206,22 @@ class BatchedSimulator:
             views.append(self._view(b, min(N, b + per)))
         return views
 
+    env_ids = None      # on a group view: the parent's env ids of the view's envs 0..n-1 (numpy)
+
     def _view(self, b, e):
         v = BatchedSimulator.__new__(BatchedSimulator)
         v.__dict__.update(self.__dict__)
         v.n_envs = e - b
         v._exit_cache = None
-        for name in ("nin_f", "nin_i", "env_i", "ent_flag", "dyn_f", "dyn_i"):
+        # a view is a range of state COLUMNS; its own env numbering is the column order (no permutation inside a view)
+        for name in ("_nin_f", "_nin_i", "_env_i", "_ent_flag", "_dyn_f", "_dyn_i"):
             setattr(v, name, getattr(self, name)[:, b:e])
-        for name in ("env_map", "frames_executed", "_actions_dev"):
+        for name in ("env_map", "_frames_executed", "_actions_dev"):
             setattr(v, name, getattr(self, name)[b:e])
-        v.env_map_host = self.env_map_host[b:e]
+        v._staging = torch.zeros(int(self.L.nppsim_host_block_bytes(e - b, 1)) + 8, dtype=torch.uint8, device=self.device)
+        v.env_ids = (self.slot_env if self.slot_env is not None else np.arange(self.n_envs))[b:e]
+        v.env_map_host = self.env_map_host[v.env_ids]
+        v.slot_env, v._slot_of, v.ext_of = None, None, None
         v.warp_order = self.warp_order[b // 32:(e + 31) // 32]
         v.warp_cost = self.warp_cost[b // 32:(e + 31) // 32]
         v.warp_order.copy_(torch.arange(v.warp_order.numel(), dtype=torch.int32, device=self.device))   # group-local slots
@@ -176,13 +229,24 @@ class BatchedSimulator:
         st = NppsimState()
         st.n_envs, st.ent_cap, st.dyn_cap, st.n_maps = v.n_envs, parent.ent_cap, parent.dyn_cap, parent.n_maps
         st.stride = parent.stride or parent.n_envs
-        st.nin_f, st.nin_i, st.env_i = v.nin_f.data_ptr(), v.nin_i.data_ptr(), v.env_i.data_ptr()
-        st.ent_flag, st.dyn_f, st.dyn_i = v.ent_flag.data_ptr(), v.dyn_f.data_ptr(), v.dyn_i.data_ptr()
+        st.nin_f, st.nin_i, st.env_i = v._nin_f.data_ptr(), v._nin_i.data_ptr(), v._env_i.data_ptr()
+        st.ent_flag, st.dyn_f, st.dyn_i = v._ent_flag.data_ptr(), v._dyn_f.data_ptr(), v._dyn_i.data_ptr()
         st.env_map, st.map_blob, st.map_off = v.env_map.data_ptr(), parent.map_blob, parent.map_off
         st.warp_order, st.warp_cost = v.warp_order.data_ptr(), v.warp_cost.data_ptr()
+        v.handoff = self._new_handoff() if self.use_handoff else None   # one queue per concurrently stepped state
+        st.handoff = v.handoff.data_ptr() if v.handoff is not None else None
         st.kind_mask = parent.kind_mask
         v._state = st
         return v
+
+    _handoff_tags = 0
+
+    def _new_handoff(self):
+        """A zeroed handoff queue (nppsim_state_t.handoff) with a tag no other queue of this process carries."""
+        BatchedSimulator._handoff_tags += 1
+        q = torch.zeros(FD.HANDOFF_WORDS, dtype=torch.int32, device=self.device)
+        q[6] = BatchedSimulator._handoff_tags
+        return q
 
     def force_full_kernel(self, on=True):
         """Test hook: run this batch on the full (all entity kinds) step kernel whatever its level set holds, by
@@ -246,7 +310,7 @@ class BatchedSimulator:
             raise RuntimeError(f"No EntityExitSwitch found in entity_dic[3] (env {bad})")
 
     def total_ticks(self):
-        return int(self.env_i[FD.ENV_TICKS].to(torch.int64).sum().item())
+        return int(self._env_i[FD.ENV_TICKS].to(torch.int64).sum().item())
 
     # ------------------------------------------------------------------ Simulator.tick (nsim.py:221-292)
     def _dev_i8(self, x):
@@ -276,7 +340,7 @@ class BatchedSimulator:
         with torch.cuda.device(self.device):
             check(self.L.nppsim_step(C.byref(self._state), C.c_void_p(hor.data_ptr()), C.c_void_p(jump.data_ptr()),
                                      input_ticks, int(n_ticks), lim, int(bool(stop_on_terminal)),
-                                     C.c_void_p(self.frames_executed.data_ptr()), self._stream()))
+                                     C.c_void_p(self._frames_executed.data_ptr()), self._stream()))
         return self.frames_executed
 
     def step(self, actions, frame_skip=4, stop_on_terminal=True):
@@ -289,7 +353,7 @@ class BatchedSimulator:
         a = a.contiguous()
         with torch.cuda.device(self.device):
             check(self.L.nppsim_step_actions(C.byref(self._state), C.c_void_p(a.data_ptr()), int(frame_skip),
-                                             int(bool(stop_on_terminal)), C.c_void_p(self.frames_executed.data_ptr()),
+                                             int(bool(stop_on_terminal)), C.c_void_p(self._frames_executed.data_ptr()),
                                              self._stream()))
         return self.frames_executed
 
@@ -321,7 +385,7 @@ class BatchedSimulator:
         stream.start_tick = int(start_tick)
         with torch.cuda.device(self.device):
             check(self.L.nppsim_step_stream(C.byref(self._state), C.byref(stream), int(n_ticks), int(bool(stop_on_terminal)),
-                                            C.c_void_p(self.frames_executed.data_ptr()), self._stream()))
+                                            C.c_void_p(self._frames_executed.data_ptr()), self._stream()))
         return self.frames_executed
 
     def replay_to_checkpoint(self, action_sequences, frame_skip=1, mask=None):
@@ -340,22 +404,42 @@ class BatchedSimulator:
             self.step_stream(sp, total)
         return self.ninja_position()
 
-    def step_host(self, actions_host, pos_vel_host, state_host, frame_skip=4, stop_on_terminal=True):
-        """Host-buffer entry point (nppsim_step_host): numpy uint8 actions in, pos/vel [4,N] f64 and
-        state [N] i32 out; copies are part of the call and the stream is synchronised on return."""
+    def host_block(self, with_obs=False):
+        """Pinned host block for step_host and numpy views into it: {"pos_vel": f64 [4, N], "state": i32 [N]} and, with
+        observations, {"ninja_state": f32 [N, 40], "action_mask": u8 [N, 6]} (layout: include/nppsim.h)."""
+        N = self.n_envs
+        block = torch.zeros(int(self.L.nppsim_host_block_bytes(N, int(bool(with_obs)))), dtype=torch.uint8).pin_memory()
+        raw = block.numpy()
+        views = {"pos_vel": raw[:32 * N].view(np.float64).reshape(4, N), "state": raw[32 * N:36 * N].view(np.int32)}
+        if with_obs:
+            views["ninja_state"] = raw[36 * N:196 * N].view(np.float32).reshape(N, 40)
+            views["action_mask"] = raw[196 * N:202 * N].reshape(N, 6)
+        return block, views
+
+    def step_host(self, actions_host, block, frame_skip=4, stop_on_terminal=True, with_obs=False):
+        """Host-buffer entry point (nppsim_step_host): numpy uint8 actions [N] in, `block` (host_block()) out -- ninja
+        position / velocity / state and optionally the per-step observations, all in the caller's env order; copies are
+        part of the call and the stream is synchronised on return."""
         self._need_maps()
+        a = np.asarray(actions_host)
+        if a.dtype != np.uint8 or a.shape != (self.n_envs,) or not a.flags["C_CONTIGUOUS"]:
+            raise ValueError("actions_host must be a contiguous uint8 array with one action per env")
+        need = int(self.L.nppsim_host_block_bytes(self.n_envs, int(bool(with_obs))))
+        if block.dtype != torch.uint8 or block.device.type != "cpu" or block.numel() < need or not block.is_contiguous():
+            raise ValueError(f"block must be a contiguous CPU uint8 tensor of at least {need} bytes (host_block())")
+        stg = self._staging.data_ptr()
+        stg += (-stg) % 8
         with torch.cuda.device(self.device):
-            check(self.L.nppsim_step_host(C.byref(self._state), C.c_void_p(actions_host.ctypes.data),
-                                          C.c_void_p(self._actions_dev.data_ptr()), int(frame_skip),
-                                          int(bool(stop_on_terminal)), C.c_void_p(pos_vel_host.ctypes.data),
-                                          C.c_void_p(state_host.ctypes.data), self._stream()))
+            check(self.L.nppsim_step_host(C.byref(self._state), C.c_void_p(a.ctypes.data), C.c_void_p(self._actions_dev.data_ptr()),
+                                          int(frame_skip), int(bool(stop_on_terminal)), C.c_void_p(stg),
+                                          C.c_void_p(block.data_ptr()), int(bool(with_obs)), self._stream()))
 
     # ------------------------------------------------------------------ NPlayHeadless getters, batched
     def _f(self, name):
-        return self.nin_f[FD.F[name]]
+        return self._ext(self._nin_f[FD.F[name]])
 
     def _i(self, name):
-        return self.nin_i[FD.I[name]]
+        return self._ext(self._nin_i[FD.I[name]])
 
     # ------------------------------------------------------------------ observation primitives (SURVEY 8(f) f1)
     def get_action_mask(self, path_direction=None):
@@ -383,10 +467,10 @@ class BatchedSimulator:
         return out
 
     def ninja_position(self):            # nplay_headless.py:415-416
-        return self.nin_f[0], self.nin_f[1]
+        return self._f("xpos"), self._f("ypos")
 
     def ninja_velocity(self):            # :418-419
-        return self.nin_f[2], self.nin_f[3]
+        return self._f("xspeed"), self._f("yspeed")
 
     def ninja_velocity_old(self):        # :421-423
         return self._f("xspeed_old"), self._f("yspeed_old")
@@ -425,13 +509,17 @@ class BatchedSimulator:
     def events(self, clear=True):
         """Per-env NPPSIM_EV_* bits raised since the last clear (replaces the reference's
         sim.gym_env.invalidate_switch_cache() callback, entity_exit_switch.py:128-129)."""
-        ev = self.env_i[FD.ENV_EVENTS].clone()
+        ev = self._ext(self._env_i[FD.ENV_EVENTS]).clone()
         if clear:
-            self.env_i[FD.ENV_EVENTS].zero_()
+            self._env_i[FD.ENV_EVENTS].zero_()
         return ev
 
     def switch_frame(self):
-        return self.env_i[FD.ENV_SWFRAME]
+        return self._ext(self._env_i[FD.ENV_SWFRAME])
+
+    def _cols(self):
+        """State column of every env, in the caller's env order (device int64 [N])."""
+        return self._slot_of if self._slot_of is not None else torch.arange(self.n_envs, device=self.device)
 
     def _exit_slots(self):
         """Per env: entity id / dyn slot of the LAST exit switch in entity_dic[3]
@@ -452,14 +540,13 @@ class BatchedSimulator:
 
     def exit_switch_activated(self):     # nplay_headless.py:566-575 (no switch -> True)
         sw_id, _, _ = self._exit_slots()
-        ar = torch.arange(self.n_envs, device=self.device)
-        fl = self.ent_flag[sw_id.clamp(min=0), ar]
+        fl = self._ent_flag[sw_id.clamp(min=0), self._cols()]
         return (sw_id < 0) | ((fl & FD.FL_ACTIVE) == 0)
 
     def _slot_xy(self, slot):
-        ar = torch.arange(self.n_envs, device=self.device)
+        ar = self._cols()
         s = slot.clamp(min=0)
-        x = self.dyn_f[s * 4, ar]; y = self.dyn_f[s * 4 + 1, ar]
+        x = self._dyn_f[s * 4, ar]; y = self._dyn_f[s * 4 + 1, ar]
         zero = torch.zeros_like(x)
         return torch.where(slot >= 0, x, zero), torch.where(slot >= 0, y, zero)
 
@@ -477,18 +564,30 @@ class BatchedSimulator:
         self._need_maps()
         torch.cuda.synchronize(self.device)
         ids = np.arange(self.n_envs) if env_ids is None else np.asarray(env_ids)
-        tid = torch.from_numpy(ids).to(self.device)
-        nf = self.nin_f[:, tid].cpu().numpy().T.copy()
-        ni = self.nin_i[:, tid].cpu().numpy().T.astype(np.int64)
-        fl = self.ent_flag[:, tid].cpu().numpy()
-        df = self.dyn_f[:, tid].cpu().numpy()
-        di = self.dyn_i[:, tid].cpu().numpy()
-        order = self.env_i[FD.ENV_ORDER][tid].cpu().numpy()
+        tid = self._cols()[torch.from_numpy(ids.astype(np.int64)).to(self.device)]
+        nf = self._nin_f[:, tid].cpu().numpy().T.copy()
+        ni = self._nin_i[:, tid].cpu().numpy().T.astype(np.int64)
+        fl = self._ent_flag[:, tid].cpu().numpy()
+        df = self._dyn_f[:, tid].cpu().numpy()
+        di = self._dyn_i[:, tid].cpu().numpy()
+        order = self._env_i[FD.ENV_ORDER][tid].cpu().numpy()
         out = []
         for k, env in enumerate(ids):
             t = self.maps[self.env_map_host[env]]
             out.append((nf[k], ni[k]) + _entity_rows(t, fl[:, k], df[:, k], di[:, k], int(order[k])))
         return out
+
+    def handoff_status(self):
+        """Sticky error bits of the handoff queue (0 = fine; 1 = a solo warp gave up waiting)."""
+        return 0 if self.handoff is None else int(self.handoff[3].item())
+
+    def handoff_count(self):
+        """Envs that left their home lane for a solo warp in the middle of a launch since load_maps (0 without a queue)."""
+        return 0 if self.handoff is None else int(self.handoff[4].item())
+
+    def solo_queue_length(self):
+        """Envs that will start the next launch on a solo warp (their last tick was wedged)."""
+        return 0 if self.handoff is None else int(self.handoff[7].item())
 
     def launch_count(self):
         return int(self.L.nppsim_launch_count())

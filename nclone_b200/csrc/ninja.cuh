@@ -50,7 +50,7 @@ DEV void ninja_collide_vs_objects(Nin& n, Ctx& c, double gx, double gy) {   // n
 
 // ninja.py:269-379, warp-synchronous: every lane of the warp calls this; `alive` lanes collide.
 // Returns true when the substep changed nothing (position bit-identical, no depenetration push).
-DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) {
+DEV bool ninja_collide_vs_tiles(Nin& n, Ctx& c, WarpPool& wp, bool alive) {
     const double xin = n.f[F_XPOS], yin = n.f[F_YPOS];
     bool pushed = false;
     double dx = n.f[F_XPOS] - n.f[F_XPOS_OLD], dy = n.f[F_YPOS] - n.f[F_YPOS_OLD];
@@ -152,8 +152,9 @@ DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
         n.i[I_CEILING_COUNT] = (int)wp.seg[o]; n.i[I_FLOOR_COUNT] = (int)wp.seg[32 + o];
         COOP_T(cacc, 5, ct)
         int w1 = -1, w2 = -1;                                // winning lanes of the last two calls (-1: unknown)
+        int it;
         #pragma unroll 1
-        for (int it = 2; it < 32; it++) {
+        for (it = 2; it < 32; it++) {
             ncoop++;
 #ifdef NPP_COOP_SPEC   // measured slower than the plain uniform loop (the broadcast of the push costs what the select saved); kept for A/B
             // Speculative push: every lane pushes from ITS segment's closest point while the warp minimum is being
@@ -275,6 +276,7 @@ DEV bool ninja_collide_vs_tiles(Nin& n, const Ctx& c, WarpPool& wp, bool alive) 
             if (!go) break;
         }
         __syncwarp();
+        if (it == 32 && lane == o) c.wedged = 1;             // all 32 iterations used: a wedged ninja (handoff, sim_variant.inc)
         if (lane != o) {
             COOP_STATE(COOP_BACK)
             n.i[I_CEILING_COUNT] = (int)wp.seg[lane]; n.i[I_FLOOR_COUNT] = (int)wp.seg[32 + lane];
@@ -562,6 +564,7 @@ DEV void sim_tick(Nin& n, Ctx& c, WarpPool& wp, bool run, int hor_input, int jum
     double gx = 0, gy = 0;
     PH_BEGIN
     if (run) {
+        c.wedged = 0;
         n.i[I_FRAME] += 1;
         GI(c, I_HOR_INPUT) = hor_input; GI(c, I_JUMP_INPUT) = jump_input;
         GF(c, F_X_AT_ACTION) = n.f[F_XPOS]; GF(c, F_Y_AT_ACTION) = n.f[F_YPOS];   // ninja.py:841-847

@@ -2,6 +2,7 @@
 // Device code lives in geom.cuh / entities.cuh / ninja.cuh; see geom.cuh for the design notes.
 #include "pool.cuh"
 
+#include <algorithm>
 #include <atomic>
 #include <cstring>
 #include <mutex>
@@ -33,7 +34,7 @@ __global__ void __launch_bounds__(128) reset_kernel(nppsim_state_t st, const uin
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
     const size_t N = npp_stride(st);
-    bool need = i < st.n_envs && !(mask && !mask[i]);
+    bool need = i < st.n_envs && !(mask && !mask[npp_ext(st, i)]);
     if (need && auto_terminal) {
         int s = st.nin_i[I_STATE * N + i], fr = st.nin_i[I_FRAME * N + i];
         bool term = (s == 6 || s == 7 || s == 8), trunc = (max_frames > 0 && fr >= max_frames);
@@ -60,7 +61,7 @@ __global__ void __launch_bounds__(128) reset_kernel(nppsim_state_t st, const uin
         envi[NPPSIM_ENV_STAMP * N] = h->n_ent;
         envi[NPPSIM_ENV_EVENTS * N] = 0;
         envi[NPPSIM_ENV_SWFRAME * N] = -1;
-        envi[NPPSIM_ENV_ORDER * N] = mode ? 1 : 0;
+        envi[NPPSIM_ENV_ORDER * N] = mode ? 1 : 0;           // (NPPSIM_ENV_WEDGE stays: it belongs to the handoff queue)
     }
     #pragma unroll 1
     for (; todo; todo &= todo - 1) {
@@ -154,8 +155,27 @@ __device__ __forceinline__ int sched_class(unsigned long long v, unsigned long l
     // cost relative to the mean: > 24x, > 12x, > 6x, > 3x, > 1.5x, the rest
     return v > 24 * mean ? 0 : (v > 12 * mean ? 1 : (v > 6 * mean ? 2 : (v > 3 * mean ? 3 : (2 * v > 3 * mean ? 4 : 5))));
 }
-__global__ void __launch_bounds__(1024) sched_kernel(int32_t* __restrict__ order, const uint32_t* __restrict__ cost, int nw) {
+__global__ void __launch_bounds__(1024) sched_kernel(int32_t* __restrict__ order, const uint32_t* __restrict__ cost, int nw, int32_t* __restrict__ handoff,
+                                                     int32_t* __restrict__ wedge_mark, int solo_limit) {
     __shared__ unsigned long long s_sum;
+    if (handoff) {
+        // Handoff queue between two launches (sim_variant.inc): the envs the finished launch appended to `next` become the
+        // initial entries of the following one and get this queue's mark; the previous initial entries lose theirs.
+        int32_t* cur = handoff + NPPSIM_HANDOFF_HDR; int32_t* next = cur + NPPSIM_HANDOFF_CAP;
+        // (at most solo_limit envs start on solo warps: on levels where a large share of the ninjas is wedged the chains are the
+        // bulk of the work, not its tail, and a warp per env would only take slots from the regular warps)
+        const int tag = handoff[6], n_old = min(handoff[7], NPPSIM_HANDOFF_CAP), n_new = min(min(handoff[5], NPPSIM_HANDOFF_CAP), solo_limit);
+        for (int k = threadIdx.x; k < n_old; k += blockDim.x) { const int v = cur[k]; if (v > 0 && wedge_mark[v - 1] == tag) wedge_mark[v - 1] = 0; }
+        __syncthreads();
+        for (int k = threadIdx.x; k < NPPSIM_HANDOFF_CAP; k += blockDim.x) {
+            const int v = k < n_new ? next[k] : 0;
+            cur[k] = v; next[k] = 0;
+            if (v > 0) wedge_mark[v - 1] = tag;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) { handoff[0] = n_new; handoff[1] = n_new; handoff[2] = 0; handoff[5] = 0; handoff[7] = n_new; }
+    }
+    if (!order || !cost) return;
     __shared__ int s_cnt[SCHED_NCLS], s_pos[SCHED_NCLS];
     const int lane = threadIdx.x & 31;
     if (threadIdx.x == 0) { s_sum = 0; for (int k = 0; k < SCHED_NCLS; k++) s_cnt[k] = 0; }
@@ -262,9 +282,11 @@ DEV void ninja_state_row(const nppsim_state_t& st, int i, float* __restrict__ o)
 #undef NI_
 }
 
-__global__ void __launch_bounds__(128) obs_kernel(nppsim_state_t st, const uint8_t* __restrict__ path_dir, uint8_t* __restrict__ mask_out, float* __restrict__ state_out) {
+__global__ void __launch_bounds__(128) obs_kernel(nppsim_state_t st, const uint8_t* __restrict__ path_dir, uint8_t* __restrict__ mask_out, float* __restrict__ state_out,
+                                                  double* __restrict__ pos_vel_out, int32_t* __restrict__ ninja_state_out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= st.n_envs) return;
+    const int x = npp_ext(st, i);                               // outputs (and path_dir) are in the caller's env order
     const size_t N = npp_stride(st);
     const double* f = st.nin_f + i; const int32_t* q = st.nin_i + i;
 #define NF_(k) f[(size_t)(k) * N]
@@ -287,15 +309,20 @@ __global__ void __launch_bounds__(128) obs_kernel(nppsim_state_t st, const uint8
                 else if (wall_normal < 0) { if (!would_trigger_wall_slide) m[2] = false; }
             }
         }
-        const int pd = path_dir ? path_dir[i] : 0;
+        const int pd = path_dir ? path_dir[x] : 0;
         if (pd == 1) { m[2] = false; m[3] = false; m[4] = false; m[5] = false; }
         else if (pd == 2) { m[1] = false; m[3] = false; m[4] = false; m[5] = false; }
         else if (pd == 3) { m[3] = false; m[4] = false; m[5] = false; }
         if (!(m[0] || m[1] || m[2] || m[3] || m[4] || m[5])) m[0] = true;
 #pragma unroll
-        for (int k = 0; k < 6; k++) mask_out[(size_t)i * 6 + k] = m[k] ? 1 : 0;
+        for (int k = 0; k < 6; k++) mask_out[(size_t)x * 6 + k] = m[k] ? 1 : 0;
     }
-    if (state_out) ninja_state_row(st, i, state_out + (size_t)i * 40);
+    if (state_out) ninja_state_row(st, i, state_out + (size_t)x * 40);
+    if (pos_vel_out) {                                          // nppsim_step_host's block: xpos, ypos, xspeed, yspeed as [4][n_envs], then the state
+#pragma unroll
+        for (int k = 0; k < 4; k++) pos_vel_out[(size_t)k * st.n_envs + x] = NF_(k);
+    }
+    if (ninja_state_out) ninja_state_out[x] = state;
 #undef NF_
 #undef NI_
 }
@@ -309,10 +336,11 @@ __global__ void __launch_bounds__(128) replay_rows_kernel(nppsim_state_t st, npp
                                                           uint8_t* __restrict__ flags, int32_t* __restrict__ frame) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= st.n_envs) return;
-    const long long len = in.offset[i + 1] - in.offset[i];
+    const int x = npp_ext(st, i);
+    const long long len = in.offset[x + 1] - in.offset[x];
     if (obs_tick > len) return;
     const size_t N = npp_stride(st);
-    const size_t row = (size_t)(row_off[i] + obs_tick / frame_skip - 1);
+    const size_t row = (size_t)(row_off[x] + obs_tick / frame_skip - 1);
     const int state = st.nin_i[(size_t)I_STATE * N + i];
     if (game_state) {
         float* o = game_state + row * 41;
@@ -343,7 +371,7 @@ __global__ void __launch_bounds__(128) replay_rows_kernel(nppsim_state_t st, npp
             fl[0] = sw < 0 ? 1 : ((st.ent_flag[(size_t)sw * N + i] & FL_ACTIVE) ? 0 : 1);   // exit_switch_activated (:566-575)
             fl[1] = state == 8;                                           // ninja_has_won
             fl[2] = (state == 6 || state == 7);                           // Ninja.has_died
-            const int b = in.data[in.offset[i] + obs_tick - 1];
+            const int b = in.data[in.offset[x] + obs_tick - 1];
             const uint8_t to_action[8] = {0, 3, 2, 5, 1, 4, 0, 0};        // map_input_to_action (replay_executor.py:42-58)
             fl[3] = b < 8 ? to_action[b] : 0;
         }
@@ -361,7 +389,8 @@ __global__ void __launch_bounds__(128) curriculum_kernel(nppsim_state_t st, cons
                                                          const double* __restrict__ door_xy, int32_t* __restrict__ status) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= st.n_envs) return;
-    if (mask && !mask[i]) return;
+    const int x = npp_ext(st, i);
+    if (mask && !mask[x]) return;
     const size_t N = npp_stride(st);
     const uint8_t* blob = st.map_blob + st.map_off[st.env_map[i]];
     const NppMapHeader* h = reinterpret_cast<const NppMapHeader*>(blob);
@@ -369,11 +398,11 @@ __global__ void __launch_bounds__(128) curriculum_kernel(nppsim_state_t st, cons
     int sw = -1;
     #pragma unroll 1
     for (int id = (int)h->n_ent - 1; id >= 0; id--) if (ents[id].kind == NPP_K_EXIT_SWITCH) { sw = id; break; }
-    if (status) status[i] = sw < 0 ? -1 : 0;
+    if (status) status[x] = sw < 0 ? -1 : 0;
     if (sw < 0) return;                                       // the reference raises RuntimeError (:768-781)
     double* dynf = st.dyn_f + i; int32_t* dyni = st.dyn_i + i;
     const int s = ents[sw].dyn, d = ents[ents[sw].aux].dyn;
-    const double sx = switch_xy[i], sy = switch_xy[(size_t)st.n_envs + i];          // caller arrays are dense over this batch
+    const double sx = switch_xy[x], sy = switch_xy[(size_t)st.n_envs + x];          // caller arrays are dense over this batch
     dynf[(size_t)(s * 4 + 0) * N] = sx; dynf[(size_t)(s * 4 + 1) * N] = sy;
     if (st.nin_i[(size_t)I_FRAME * N + i] <= 10) st.ent_flag[(size_t)sw * N + i] |= FL_ACTIVE;
     int cx = min(max((int)floor(sx / 24), 0), NPP_NCX - 1), cy = min(max((int)floor(sy / 24), 0), NPP_NCY - 1);
@@ -382,7 +411,7 @@ __global__ void __launch_bounds__(128) curriculum_kernel(nppsim_state_t st, cons
         dyni[(size_t)(s * 3 + 0) * N] = cell;
         dyni[(size_t)(s * 3 + 1) * N] = st.env_i[(size_t)NPPSIM_ENV_STAMP * N + i]++;
     }
-    const double dx = door_xy[i], dy = door_xy[(size_t)st.n_envs + i];
+    const double dx = door_xy[x], dy = door_xy[(size_t)st.n_envs + x];
     dynf[(size_t)(d * 4 + 0) * N] = dx; dynf[(size_t)(d * 4 + 1) * N] = dy;
     cx = min(max((int)floor(dx / 24), 0), NPP_NCX - 1); cy = min(max((int)floor(dy / 24), 0), NPP_NCY - 1);
     cell = cx * NPP_NCY + cy;
@@ -437,7 +466,11 @@ int launch_step(const nppsim_state_t* st, const int8_t* hor, const int8_t* jump,
     if (!in && !actions && (!hor || !jump)) return fail(NPPSIM_E_ARG, "inputs are NULL");
     if (!in && !actions && !(input_ticks == 1 || input_ticks == n_ticks)) return fail(NPPSIM_E_ARG, "input_ticks must be 1 or n_ticks");
     const int block = STEP_BLOCK;
-    const int grid = (st->n_envs + block - 1) / block;
+    // solo blocks at the front of the grid for wedged envs (sim_variant.inc): 4 solo warps per 512 envs; all but the first
+    // eight blocks exit at once unless the previous launch left them an env
+    const int n_solo = st->handoff ? std::min(NPPSIM_HANDOFF_CAP / 4, std::max(2, st->n_envs / 512)) : 0;
+    const int solo_limit = std::max(64, st->n_envs / 384);      // envs per launch that start on solo warps; as many again may follow mid-launch
+    const int grid = (st->n_envs + block - 1) / block + n_solo;
     // shared-memory carve-out: room for the two blocks per SM the register file admits and not more -- the rest
     // of the 256 KB stays L1 for the level blobs (max-shared left 28 KB of L1: hit rate 40 % instead of 66 %)
     // (function attributes belong to the current device's context: set once per device, results checked)
@@ -461,12 +494,14 @@ int launch_step(const nppsim_state_t* st, const int8_t* hor, const int8_t* jump,
     // kind_mask == 0: census unknown (older callers) -> the full kernel
     const bool basic = st->kind_mask != 0 && (st->kind_mask & ~NPP_BASIC_MASK) == 0;
     auto kernel = basic ? sim_basic::step_kernel : sim_full::step_kernel;
-    kernel<<<grid, block, STEP_SMEM, (cudaStream_t)stream>>>(*st, hor, jump, actions, input_ticks, n_ticks, tick_limit, stop_on_terminal, frames_executed, sp);
+    kernel<<<grid, block, STEP_SMEM, (cudaStream_t)stream>>>(*st, hor, jump, actions, input_ticks, n_ticks, tick_limit, stop_on_terminal, frames_executed, sp, n_solo, 2 * solo_limit);
     g_launches++;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_fail(e, "step_kernel launch");
-    if (st->warp_order && st->warp_cost) {
-        sched_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(st->warp_order, st->warp_cost, (st->n_envs + 31) / 32);
+    if ((st->warp_order && st->warp_cost) || st->handoff) {
+        const size_t S = st->stride ? (size_t)st->stride : (size_t)st->n_envs;
+        sched_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(st->warp_cost ? st->warp_order : nullptr, st->warp_cost, (st->n_envs + 31) / 32, st->handoff,
+                                                           st->env_i + (size_t)NPPSIM_ENV_WEDGE * S, solo_limit);
         g_launches++;
         e = cudaGetLastError();
         if (e != cudaSuccess) return cuda_fail(e, "sched_kernel launch");
@@ -558,7 +593,7 @@ int nppsim_observe(const nppsim_state_t* st, const uint8_t* path_dir, uint8_t* m
     int rc = check_state(st);
     if (rc) return rc;
     if (!mask_out && !ninja_state_out) return fail(NPPSIM_E_ARG, "no output buffer");
-    obs_kernel<<<(st->n_envs + 127) / 128, 128, 0, (cudaStream_t)stream>>>(*st, path_dir, mask_out, ninja_state_out);
+    obs_kernel<<<(st->n_envs + 127) / 128, 128, 0, (cudaStream_t)stream>>>(*st, path_dir, mask_out, ninja_state_out, nullptr, nullptr);
     g_launches++;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_fail(e, "obs_kernel launch");
@@ -615,23 +650,35 @@ int nppsim_replay_rows(const nppsim_state_t* st, const nppsim_input_stream_t* in
     return 0;
 }
 
+int64_t nppsim_host_block_bytes(int32_t n_envs, int32_t with_obs) {
+    const int64_t n = n_envs > 0 ? n_envs : 0;
+    return n * (4 * 8 + 4) + (with_obs ? n * (40 * 4 + 6) : 0);
+}
+
 int nppsim_step_host(const nppsim_state_t* st, const uint8_t* actions_host, uint8_t* actions_dev, int32_t n_ticks,
-                     int32_t stop_on_terminal, double* pos_vel_host, int32_t* state_host, void* stream) {
+                     int32_t stop_on_terminal, uint8_t* staging_dev, uint8_t* out_host, int32_t with_obs, void* stream) {
     g_err[0] = 0;
     int rc = check_state(st);
     if (rc) return rc;
-    if (!actions_host || !actions_dev || !pos_vel_host || !state_host) return fail(NPPSIM_E_ARG, "a host/device buffer is NULL");
+    if (!actions_host || !actions_dev || !staging_dev || !out_host) return fail(NPPSIM_E_ARG, "a host/device buffer is NULL");
+    if (((uintptr_t)staging_dev & 7) != 0) return fail(NPPSIM_E_ARG, "staging_dev must be 8-byte aligned");
     cudaStream_t s = (cudaStream_t)stream;
-    const size_t N = (size_t)st->n_envs, S = st->stride ? (size_t)st->stride : N;
+    const size_t N = (size_t)st->n_envs;
     cudaError_t e = cudaMemcpyAsync(actions_dev, actions_host, N, cudaMemcpyHostToDevice, s);
     if (e != cudaSuccess) return cuda_fail(e, "actions H2D");
     rc = launch_step(st, nullptr, nullptr, actions_dev, 1, n_ticks, nullptr, stop_on_terminal, nullptr, stream);
     if (rc) return rc;
-    // xpos, ypos, xspeed, yspeed are fields 0..3 -> one contiguous [4][N] block; state is int field 0
-    e = cudaMemcpy2DAsync(pos_vel_host, N * sizeof(double), st->nin_f, S * sizeof(double), N * sizeof(double), 4, cudaMemcpyDeviceToHost, s);
-    if (e != cudaSuccess) return cuda_fail(e, "pos/vel D2H");
-    e = cudaMemcpyAsync(state_host, st->nin_i, N * sizeof(int32_t), cudaMemcpyDeviceToHost, s);
-    if (e != cudaSuccess) return cuda_fail(e, "state D2H");
+    // one pass over the batch packs what the caller reads every step, in the caller's env order, into one block: one D2H copy
+    double* pv = reinterpret_cast<double*>(staging_dev);
+    int32_t* stt = reinterpret_cast<int32_t*>(staging_dev + N * 32);
+    float* obs = with_obs ? reinterpret_cast<float*>(staging_dev + N * 36) : nullptr;
+    uint8_t* msk = with_obs ? staging_dev + N * 196 : nullptr;
+    obs_kernel<<<(st->n_envs + 127) / 128, 128, 0, s>>>(*st, nullptr, msk, obs, pv, stt);
+    g_launches++;
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "obs_kernel launch");
+    e = cudaMemcpyAsync(out_host, staging_dev, (size_t)nppsim_host_block_bytes(st->n_envs, with_obs), cudaMemcpyDeviceToHost, s);
+    if (e != cudaSuccess) return cuda_fail(e, "result D2H");
     e = cudaStreamSynchronize(s);
     if (e != cudaSuccess) return cuda_fail(e, "stream sync");
     return 0;

@@ -204,20 +204,34 @@ def test_reset_and_fast_reset(golden_replays):
             assert schema.state_hash(*s.state()) == schema.state_hash(*recs[k]), (k, st)
 
 
-def test_step_host_matches_device_path(golden_replays):
+def test_step_host_matches_device_path(golden_replays, golden_generated):
+    """nppsim_step_host: host actions in, one packed block out (position / velocity / state and, with_obs, the 40-float
+    ninja state + action mask), everything in the CALLER's env order although the engine keeps the envs of a level in
+    consecutive state columns (nppsim_state_t.ext_of: 3 levels interleaved over 96 envs here)."""
     import torch
     from nclone_b200 import BatchedSimulator
-    t = golden_replays.traj(3)
-    N = 64
+    maps = [golden_replays.traj(3)["map_data"], golden_generated.traj(0)["map_data"], golden_generated.traj(40)["map_data"]]
+    N = 96
+    e2m = np.arange(N) % 3
     a = np.random.default_rng(1).integers(0, 6, size=(20, N)).astype(np.uint8)
-    s1 = BatchedSimulator(N); s1.load_maps([t["map_data"]])
-    s2 = BatchedSimulator(N); s2.load_maps([t["map_data"]])
-    pv = np.zeros((4, N)); st = np.zeros(N, dtype=np.int32)
+    s1 = BatchedSimulator(N); s1.load_maps(maps, e2m)
+    s2 = BatchedSimulator(N); s2.load_maps(maps, e2m)
+    s3 = BatchedSimulator(N, placement="caller"); s3.load_maps(maps, e2m)
+    assert s1.slot_env is not None and s3.slot_env is None and np.array_equal(s1.env_map_host, e2m)
+    block, v = s2.host_block(with_obs=True)
+    block3, v3 = s3.host_block(with_obs=False)
     for k in range(20):
         s1.step(torch.from_numpy(a[k]).cuda(), 4, True)
-        s2.step_host(a[k], pv, st, 4, True)
-    assert np.array_equal(s1.nin_f[:4].cpu().numpy().view(np.int64), pv.view(np.int64))
-    assert np.array_equal(s1.nin_i[0].cpu().numpy(), st)
+        s2.step_host(a[k], block, 4, True, with_obs=True)
+        s3.step_host(a[k], block3, 4, True)
+    assert np.array_equal(s1.nin_f[:4].cpu().numpy().view(np.int64), v["pos_vel"].view(np.int64))
+    assert np.array_equal(s1.nin_i[0].cpu().numpy(), v["state"])
+    assert np.array_equal(v3["pos_vel"].view(np.int64), v["pos_vel"].view(np.int64)) and np.array_equal(v3["state"], v["state"])
+    assert np.array_equal(s1.get_ninja_state().cpu().numpy().view(np.int32), v["ninja_state"].view(np.int32))
+    assert np.array_equal(s1.get_action_mask().cpu().numpy().astype(np.uint8), v["action_mask"])
+    assert len(np.unique(v["pos_vel"][0])) > 3                     # the three levels really behave differently
+    with pytest.raises(ValueError):
+        s2.step_host(a[0].astype(np.int64), block)                 # dtype is checked, not reinterpreted
 
 
 def _oracle_rollout(maps, env_to_map, actions, frame_skip, max_frames, check_every):
@@ -320,8 +334,60 @@ def test_wedged_ninja_cooperative_loop_vs_oracle():
         badi = np.nonzero((gi != ni).any(1))[0]
         assert badf.size == 0 and badi.size == 0, (st, badf[:5], badi[:5])
         sim.reset_terminal(2000)
-    # the long loop must actually have been taken: warp cost = the longest per-lane chain of a launch (4 ticks x 4 substeps x 30)
-    assert most >= 350, most
+    assert most >= 1000, most      # several envs of the warp wedged in the same agent step (>= 354 iterations each)
+
+
+def test_wedged_ninja_handoff_to_solo_warps_vs_oracle():
+    """In-launch handoff (nppsim_state_t.handoff, csrc/sim_variant.inc): a wedged env leaves its home lane at the end of its
+    first wedged tick and finishes the agent step on a solo warp; envs wedged when the previous launch ended start there.
+    Same scenario as above with the queue switched on (it is on by default from 1,024 envs): full ninja record and
+    frames_executed against the oracle after every agent step, handoffs must have happened, no solo warp may have timed out.
+    Second half: per-tick input rows and per-env action streams (the two other input forms) through the handoff."""
+    import torch
+    from nclone_b200 import BatchedSimulator, ACTION_TO_INPUTS
+    d = np.load(os.path.join(ROOT, "bench_data", "wedges.npz"))
+    K = len(d["lens"])
+    maps = [d["maps"][k, :d["lens"][k]] for k in range(K)]
+    pre = [d["acts"][d["act_off"][k]:d["act_off"][k + 1]] for k in range(K)]
+    env_to_map = np.repeat(np.arange(K), 12)
+    N = len(env_to_map)
+    steps = max(len(p) for p in pre) + 30
+    actions = np.zeros((steps, N), dtype=np.uint8)
+    for e in range(N):
+        p = pre[env_to_map[e]]
+        actions[:len(p), e] = p
+        actions[len(p):, e] = e % 6
+    ref = _oracle_rollout(maps, env_to_map, actions, 4, 2000, 1)
+    for mode in ("actions", "rows", "stream"):
+        sim = BatchedSimulator(N, handoff=True)
+        sim.load_maps(maps, env_to_map)
+        hj = np.array(ACTION_TO_INPUTS, dtype=np.int8)
+        sp = sim.make_stream([actions[:, e] for e in range(N)], "actions", 4) if mode == "stream" else None
+        plain = None
+        seen_queue = 0
+        if mode == "actions":                          # frames_executed against the same batch without a queue
+            plain = BatchedSimulator(N, handoff=False); plain.load_maps(maps, env_to_map)
+        for st in range(steps):
+            if mode == "actions":
+                fe = sim.step(torch.from_numpy(actions[st]).cuda(), 4, True)
+                ticks = plain.step(torch.from_numpy(actions[st]).cuda(), 4, True).cpu().numpy(); plain.reset_terminal(2000)
+            elif mode == "rows":
+                hor = np.repeat(hj[actions[st], 0][None, :], 4, 0); jump = np.repeat(hj[actions[st], 1][None, :], 4, 0)
+                fe = sim.tick(hor, jump, n_ticks=4, stop_on_terminal=True)
+            else:
+                fe = sim.step_stream(sp, 4, start_tick=4 * st, stop_on_terminal=True)
+            _, nf, ni = ref[st]
+            gf = sim.nin_f.cpu().numpy().T; gi = sim.nin_i.cpu().numpy().T.astype(np.int64)
+            badf = np.nonzero((gf.view(np.int64) != nf.view(np.int64)).any(1))[0]
+            badi = np.nonzero((gi != ni).any(1))[0]
+            assert badf.size == 0 and badi.size == 0, (mode, st, badf[:5], badi[:5])
+            if mode == "actions":
+                assert np.array_equal(fe.cpu().numpy(), ticks), (mode, st)
+            seen_queue = max(seen_queue, sim.solo_queue_length())
+            sim.reset_terminal(2000)
+        assert sim.handoff_status() == 0
+        assert sim.handoff_count() >= 18, sim.handoff_count()      # mid-launch handoffs: one per wedge episode of 36 envs
+        assert seen_queue > 0                                       # and envs started launches on solo warps
 
 
 def test_basic_variant_vs_oracle_and_full_kernel():
@@ -329,6 +395,7 @@ def test_basic_variant_vs_oracle_and_full_kernel():
     (nppsim_state_t.kind_mask).  (1) 1,280 envs of the benchmark levels against the oracle;
     (2) 16,384 envs x 150 agent steps: basic and full kernels must leave identical state everywhere."""
     import torch
+    from nclone_b200 import fields as FD
     from nclone_b200 import BatchedSimulator
     from nclone_b200._lib import lib
     import bench
@@ -372,7 +439,9 @@ def test_basic_variant_vs_oracle_and_full_kernel():
         for st in range(150):
             s2.step(acts[st], 4, True)
             s2.reset_terminal(2000)
-        states.append([t.clone() for t in (s2.nin_f, s2.nin_i, s2.env_i, s2.ent_flag, s2.dyn_f, s2.dyn_i)])
+        envi = s2.env_i.clone()
+        envi[FD.ENV_WEDGE] = (envi[FD.ENV_WEDGE] != 0).int()       # the mark is the queue's tag, which differs per instance
+        states.append([t.clone() for t in (s2.nin_f, s2.nin_i, envi, s2.ent_flag, s2.dyn_f, s2.dyn_i)])
     for a, b in zip(*states):
         assert torch.equal(a.view(torch.uint8), b.view(torch.uint8))
 
@@ -538,14 +607,15 @@ def test_groups_views_step_independently(golden_replays, golden_generated):
     assert [g.n_envs for g in groups] == [64, 64, 39]
     streams = [torch.cuda.Stream() for _ in groups]
     torch.cuda.synchronize()
-    bounds = np.cumsum([0] + [g.n_envs for g in groups])
-    pv = [np.zeros((4, g.n_envs)) for g in groups]; stt = [np.zeros(g.n_envs, dtype=np.int32) for g in groups]
+    # a group is a range of state columns: the envs of the parent it holds (the engine keeps the envs of a level together)
+    assert sim.slot_env is not None and sorted(np.concatenate([g.env_ids for g in groups]).tolist()) == list(range(N))
+    blocks = [g.host_block() for g in groups]
     for k, (g, st) in enumerate(zip(groups, streams)):       # group k runs all its steps before group k+1 is even issued
         with torch.cuda.stream(st):
             for s in range(steps):
-                a = acts[s, bounds[k]:bounds[k + 1]]
+                a = acts[s, g.env_ids]
                 if s % 2:
-                    g.step_host(np.ascontiguousarray(a), pv[k], stt[k], 4, True)      # host-buffer entry point on a view
+                    g.step_host(np.ascontiguousarray(a), blocks[k][0], 4, True)      # host-buffer entry point on a view
                 else:
                     g.step(torch.from_numpy(np.ascontiguousarray(a)).cuda(), 4, True)
                 g.reset_terminal(60)
@@ -555,7 +625,7 @@ def test_groups_views_step_independently(golden_replays, golden_generated):
     assert int(sim.stats[0]) == int(whole.stats[0]) > 0
     # getters of a view are slices of the parent's
     x, _ = groups[1].ninja_position()
-    assert torch.equal(x, sim.ninja_position()[0][64:128])
+    assert torch.equal(x, sim.ninja_position()[0][torch.from_numpy(groups[1].env_ids).cuda()])
     assert groups[2].get_action_mask().shape == (39, 6) and groups[2].get_ninja_state().shape == (39, 40)
 
 
@@ -589,10 +659,13 @@ def test_full_size_replica_consistency_and_oracle_sample():
     e2m_d = torch.from_numpy(env_to_map).cuda()
     order = torch.argsort(e2m_d, stable=True).view(M, R)       # row m: the 16 envs on level m
     heavy = np.zeros(N // 32, dtype=np.int64)
+    from nclone_b200 import fields as FD
+    solo_envs = set()
     for st in range(steps):
         a = torch.from_numpy(acts_map[st]).cuda()[e2m_d]
         sim.step(a, 4, True)
         heavy = np.maximum(heavy, sim.warp_cost.cpu().numpy().astype(np.int64) - 1)
+        solo_envs.update(torch.nonzero(sim.env_i[FD.ENV_WEDGE]).flatten().tolist())     # envs that start the next launch on a solo warp
         if (st + 1) % 10 == 0:
             for t in (sim.nin_f, sim.nin_i):
                 v = t.view(torch.int64) if t.dtype == torch.float64 else t
@@ -600,17 +673,27 @@ def test_full_size_replica_consistency_and_oracle_sample():
                 assert bool((rows == rows[:, :, :1]).all()), st
             fl = sim.ent_flag[:, order]
             assert bool((fl == fl[:, :, :1]).all()), st
-        sim.reset_terminal(2000)
-    assert heavy.max() >= 300, heavy.max()                      # some ninja was wedged through a whole agent step
-    # (2) oracle replay of the envs in the heaviest warps + a random sample
-    top = np.argsort(-heavy)[:6]
-    pick = np.unique(np.concatenate([(top[:, None] * 32 + np.arange(32)[None, :]).ravel(), rng.integers(0, N, size=64)]))
+        if st + 1 < steps:
+            sim.reset_terminal(2000)
+    # wedged ninjas occurred, and they went through the solo-warp handoff (on by default at this size), both ways
+    assert sim.handoff_status() == 0
+    assert len(solo_envs) >= 8 and sim.handoff_count() >= 8, (len(solo_envs), sim.handoff_count())
+    # (2) oracle replay of the envs that ran on solo warps, of those in the heaviest warps and of a random sample
+    top = np.argsort(-heavy)[:4]
+    cols = (top[:, None] * 32 + np.arange(32)[None, :]).ravel()   # warp groups are ranges of state columns
+    heavy_envs = sim.slot_env[cols] if sim.slot_env is not None else cols
+    pick = np.unique(np.concatenate([np.array(sorted(solo_envs), dtype=np.int64)[:160], heavy_envs, rng.integers(0, N, size=64)]))
     sub_maps = env_to_map[pick]
     acts = acts_map[:, sub_maps]
     ref = _oracle_rollout(maps, sub_maps, acts, 4, 2000, steps)
     _, nf, ni = ref[-1]
-    # the oracle's checkpoint is taken before the post-step reset; redo the last device step without it
+    # the oracle's checkpoint is taken before the post-step reset, as the big batch was left above
+    tp = torch.from_numpy(pick).cuda()
+    gf = sim.nin_f[:, tp].cpu().numpy().T.copy(); gi = sim.nin_i[:, tp].cpu().numpy().T.astype(np.int64)
+    assert np.array_equal(gf.view(np.int64), nf.view(np.int64)) and np.array_equal(gi, ni)
+    # and the same envs as a small batch of their own (no handoff queue below 1,024 envs)
     sim2 = BatchedSimulator(len(pick)); sim2.load_maps(maps, sub_maps)
+    assert sim2.handoff is None
     for st in range(steps):
         sim2.step(torch.from_numpy(np.ascontiguousarray(acts[st])).cuda(), 4, True)
         if st + 1 < steps:
