@@ -254,6 +254,13 @@ class BatchedSimulator:
         self._need_maps()
         self._state.kind_mask = 0 if on else self.kind_mask
 
+    def kernel_variant(self):
+        """Which step-kernel instantiation launch_step picks for this batch (nppsim_kernels.cu: NPP_BASIC_MASK)."""
+        self._need_maps()
+        basic = sum(1 << k for k in (FD.K_NONE, FD.K_MINE, FD.K_GOLD, FD.K_EXIT, FD.K_EXIT_SWITCH, FD.K_DOOR_LOCKED, FD.K_DOOR_TRAP))
+        km = int(self._state.kind_mask)
+        return "sim_basic" if km != 0 and (km & ~basic) == 0 else "sim_full"
+
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 

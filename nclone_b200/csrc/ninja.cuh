@@ -138,13 +138,83 @@ DEV bool ninja_collide_vs_tiles(Nin& n, Ctx& c, WarpPool& wp, bool alive) {
         ct = clock64(); cacc[4]++;
 #endif
         const int lane = threadIdx.x & 31;
-        const int o = __ffs(todo) - 1;
-        const int ns = __shfl_sync(FULL_MASK, nseg, o);
-        const SegC g = seg_decode(lane < ns ? wp.lseg[o][lane] : 0u);
         const bool pushed_own = pushed;
 #define COOP_PARK(k, v) coop_slot(wp, k, lane) = v;
 #define COOP_TAKE(k, v) v = coop_slot(wp, k, o);
 #define COOP_BACK(k, v) v = coop_slot(wp, k, lane);
+#ifndef NPP_COOP_NOGROUPS
+        // Several lanes wait for service (the envs of a level share a warp, and a level that wedges one ninja wedges others):
+        // serve up to four of them AT ONCE, each by a group of W = 8 (or two by W = 16) lanes, instead of one after the other --
+        // the loop is a dependent chain per owner, so the chains of the groups overlap in the warp's instruction stream.
+        // Group g takes over the state of its owner exactly as the whole warp does below; its lane l evaluates the owner's
+        // l-th cached segment with exact squares (closest_eval_nb: no flagged squares, so the reference's strict-< scan is the
+        // first minimum in list order: a segmented butterfly minimum of the order-preserving keys and a ballot); the push is
+        // the same push_eval / push_commit on the same inputs.  Owners whose list does not fit a group (or overflowed) are
+        // left to the whole-warp service.
+        if (todo & (todo - 1)) {
+            int W = (__popc(todo) == 2) ? 16 : 8;
+            unsigned elig = __ballot_sync(FULL_MASK, need && nseg >= 0 && nseg <= W);
+            if (W == 8 && !(elig & (elig - 1))) { W = 16; elig = __ballot_sync(FULL_MASK, need && nseg >= 0 && nseg <= W); }
+            if (elig & (elig - 1)) {
+                const int G = 32 / W, grp = lane / W, l = lane - grp * W;
+                const unsigned gmask = (W == 16 ? 0xffffu : 0xffu) << (grp * W);
+                const unsigned fo = __fns(elig, 0, grp + 1);                 // the grp-th eligible owner (0xffffffff: none left)
+                const bool act = fo < 32u;
+                const int o = act ? (int)fo : lane;
+                const int ns_o = __shfl_sync(FULL_MASK, nseg, o);
+                const int ns = act ? ns_o : 0;
+                const SegC g = seg_decode((act && l < ns) ? wp.lseg[o][l] : 0u);
+                const bool served = need && ((elig >> lane) & 1u) && __popc(elig & ((1u << lane) - 1u)) < G;
+                COOP_STATE(COOP_PARK)
+                wp.seg[lane] = (uint32_t)n.i[I_CEILING_COUNT]; wp.seg[32 + lane] = (uint32_t)n.i[I_FLOOR_COUNT];
+                __syncwarp();
+                COOP_STATE(COOP_TAKE)
+                n.i[I_CEILING_COUNT] = (int)wp.seg[o]; n.i[I_FLOOR_COUNT] = (int)wp.seg[32 + o];
+                __syncwarp();                                                // every lane has taken before a leader writes back
+                bool live = act;
+                int it;
+                #pragma unroll 1
+                for (it = 2; it < 32; it++) {
+                    ncoop++;
+                    const double inf = __longlong_as_double(0x7ff0000000000000LL);
+                    double d2 = inf, a = 0, b = 0; int r = 0; bool ok = false;
+                    if (live && l < ns) ok = closest_eval_nb(g, xpos, ypos, d2, a, b, r);
+                    const long long bits = __double_as_longlong(d2);
+                    const unsigned long long key = ok ? (unsigned long long)(bits ^ ((bits >> 63) | (long long)0x8000000000000000ULL)) : ~0ULL;   // monotone in d2
+                    unsigned long long kmin = key;
+                    #pragma unroll
+                    for (int d = 1; d < 16; d <<= 1) {
+                        if (d < W) { const unsigned long long other = __shfl_xor_sync(FULL_MASK, kmin, d); kmin = other < kmin ? other : kmin; }
+                    }
+                    const unsigned cand = __ballot_sync(FULL_MASK, ok && key == kmin) & gmask;
+                    const int w = cand ? __ffs(cand) - 1 : lane;             // first minimum in list order (strict < scan, physics.py:170-176)
+                    a = __shfl_sync(FULL_MASK, a, w); b = __shfl_sync(FULL_MASK, b, w); r = __shfl_sync(FULL_MASK, r, w);
+                    const Push t = push_eval(cand ? r : 0, a, b);
+                    if (live && t.go) push_commit(t); else live = false;
+                    if (!__any_sync(FULL_MASK, live)) break;
+                }
+                // the group's first lane hands the owner's state back through the owner's slots; a chain that ran all 30
+                // iterations marks a wedged ninja (sim_variant.inc)
+                if (act && l == 0) {
+#define COOP_PUT(k, v) coop_slot(wp, k, o) = v;
+                    COOP_STATE(COOP_PUT)
+#undef COOP_PUT
+                    wp.seg[o] = (uint32_t)n.i[I_CEILING_COUNT]; wp.seg[32 + o] = (uint32_t)n.i[I_FLOOR_COUNT];
+                    wp.aux[o] = (uint8_t)((it == 32 && live) ? 1 : 0);
+                }
+                __syncwarp();
+                COOP_STATE(COOP_BACK)
+                n.i[I_CEILING_COUNT] = (int)wp.seg[lane]; n.i[I_FLOOR_COUNT] = (int)wp.seg[32 + lane];
+                pushed = pushed_own;
+                if (served) { need = false; if (wp.aux[lane]) c.wedged = 1; }
+                __syncwarp();
+                continue;
+            }
+        }
+#endif
+        const int o = __ffs(todo) - 1;
+        const int ns = __shfl_sync(FULL_MASK, nseg, o);
+        const SegC g = seg_decode(lane < ns ? wp.lseg[o][lane] : 0u);
         COOP_STATE(COOP_PARK)
         wp.seg[lane] = (uint32_t)n.i[I_CEILING_COUNT]; wp.seg[32 + lane] = (uint32_t)n.i[I_FLOOR_COUNT];
         __syncwarp();

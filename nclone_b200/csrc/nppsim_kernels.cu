@@ -528,6 +528,14 @@ int nppsim_debug_warp_span(unsigned long long* out, int n) {
     cudaDeviceSynchronize();
     return (int)cudaMemcpyFromSymbol(out, g_warp_span, sizeof(unsigned long long) * n * 2);
 }
+int nppsim_debug_solo_log(unsigned long long* out, int max_rows, int reset) {      // -> rows logged since the last reset
+    cudaDeviceSynchronize();
+    unsigned int n = 0;
+    cudaMemcpyFromSymbol(&n, g_solo_n, sizeof(n));
+    if (out) cudaMemcpyFromSymbol(out, g_solo_log, sizeof(unsigned long long) * 4 * (size_t)std::min<unsigned>(std::min<unsigned>(n, 8192u), (unsigned)max_rows));
+    if (reset) { unsigned int z = 0; cudaMemcpyToSymbol(g_solo_n, &z, sizeof(z)); }
+    return (int)n;
+}
 int nppsim_debug_coop_cycles(unsigned long long* out8, int reset) {
     cudaDeviceSynchronize();
     if (out8) cudaMemcpyFromSymbol(out8, g_coop_cycles, sizeof(unsigned long long) * 8);

@@ -19,6 +19,9 @@ __device__ unsigned long long g_warp_cycles[1 << 16];      // per warp: kernel d
 __device__ unsigned long long g_warp_span[1 << 16][2];    // per warp: %globaltimer (ns) at start / end of the last launch
 DEV unsigned long long global_ns() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 __device__ unsigned long long g_warp_phase[1 << 16][4];   // per warp: cycles in entities / sweep / closest / post of the last launch
+__device__ unsigned long long g_solo_log[8192][4];        // per env served by a solo warp: env | t_first << 24 | converted << 28 | initial << 29, ns at pickup, at end, at publication (b)
+__device__ unsigned int g_solo_n;
+__device__ unsigned long long g_hand_pub[1 << 12];        // per entry of (b): ns at publication
 __device__ unsigned long long g_coop_cycles[8];        // cooperative depenetration loop: [0] evaluate, [1] select, [2] push, [3] iterations, [4] services, [5] park/take/back
 #define COOP_T(acc, k, t) { long long _n = clock64(); (acc)[k] += _n - (t); (t) = _n; }
 #define PH_COUNT(k) atomicAdd(&g_phase_cycles[k], 1ULL)

@@ -10,6 +10,9 @@ Policy = bench.py's: uniform Discrete(6) actions (ACTION_TO_INPUTS, action_repla
 with the env wrapper's early exit on win / death (base_environment.py:605-609), Simulator.reset() when the episode ended
 or reached max_frames.  Each worker process owns the Simulators of its share of the levels.
 """
+import importlib.abc
+import importlib.util
+import marshal
 import multiprocessing as mp
 import os
 import random
@@ -23,7 +26,7 @@ ACTION_TO_INPUTS = ((0, 0), (-1, 0), (1, 0), (0, 1), (-1, 1), (1, 1))
 def ref_path():
     """Where the reference's `nclone` package can be imported from, or None."""
     compiled = os.path.join(HERE, "_ref")
-    if os.path.isfile(os.path.join(compiled, "nclone", "nsim.pyc")):
+    if os.path.isfile(os.path.join(compiled, "nclone", "nsim.refc")):
         return compiled
     src = os.environ.get("NCLONE_REF", "/root/reference")
     if os.path.isfile(os.path.join(src, "nclone", "nsim.py")):
@@ -35,6 +38,43 @@ def available():
     return ref_path() is not None
 
 
+class _RefLoader(importlib.abc.Loader):
+    def __init__(self, path):
+        self.path = path
+
+    def create_module(self, spec):
+        return None
+
+    def exec_module(self, module):
+        with open(self.path, "rb") as f:
+            code = marshal.loads(f.read()[16:])          # .pyc image: 16-byte header, then the marshalled code object
+        module.__file__ = self.path                       # constants/physics_constants.py:243 builds a path from it (animation data: unused headless)
+        exec(code, module.__dict__)
+
+
+class _RefFinder(importlib.abc.MetaPathFinder):
+    """Imports `nclone.*` from the compiled modules of oracle/_ref (make_ref.py writes .pyc images as *.refc)."""
+
+    def __init__(self, root):
+        self.root = root
+
+    def find_spec(self, name, path=None, target=None):
+        if name.split(".")[0] != "nclone":
+            return None
+        base = os.path.join(self.root, *name.split("."))
+        if os.path.isfile(os.path.join(base, "__init__.refc")):
+            spec = importlib.util.spec_from_loader(name, _RefLoader(os.path.join(base, "__init__.refc")), origin=os.path.join(base, "__init__.refc"), is_package=True)
+            spec.submodule_search_locations = [base]
+            return spec
+        if os.path.isfile(base + ".refc"):
+            return importlib.util.spec_from_loader(name, _RefLoader(base + ".refc"), origin=base + ".refc")
+        if os.path.isdir(base):                                  # a package without __init__ (namespace)
+            spec = importlib.util.spec_from_loader(name, None, is_package=True)
+            spec.submodule_search_locations = [base]
+            return spec
+        return None
+
+
 def _import():
     p = ref_path()
     if p is None:
@@ -43,7 +83,10 @@ def _import():
     os.makedirs(scratch, exist_ok=True)
     os.environ["HOME"] = scratch
     sys.dont_write_bytecode = True
-    if p not in sys.path:
+    if os.path.isfile(os.path.join(p, "nclone", "nsim.refc")):
+        if not any(isinstance(f, _RefFinder) for f in sys.meta_path):
+            sys.meta_path.insert(0, _RefFinder(p))
+    elif p not in sys.path:
         sys.path.insert(0, p)
     from nclone.nsim import Simulator
     from nclone.sim_config import SimConfig
@@ -56,7 +99,7 @@ def _as_list(md):
 
 
 def _worker(args):
-    maps, seed, frame_skip, max_frames, seconds = args
+    maps, seed, frame_skip, max_frames, seconds, n_slices = args
     Simulator, SimConfig = _import()
     sims = []
     for md in maps:
@@ -64,36 +107,47 @@ def _worker(args):
         s.load(_as_list(md))
         sims.append(s)
     rng = random.Random(seed)
-    ticks = 0
-    t0 = time.perf_counter()
-    deadline = t0 + seconds
-    while time.perf_counter() < deadline:
-        for s in sims:
-            h, j = ACTION_TO_INPUTS[rng.randrange(6)]
-            for _ in range(frame_skip):
-                s.tick(h, j)
-                ticks += 1
-                if s.ninja.state in (6, 7, 8):
-                    break
-            if s.ninja.state in (6, 7, 8) or s.frame >= max_frames:
-                s.reset()
-    return ticks, time.perf_counter() - t0
+    out = []
+    for _ in range(n_slices):
+        ticks = 0
+        t0 = time.perf_counter()
+        deadline = t0 + seconds
+        while time.perf_counter() < deadline:
+            for s in sims:
+                h, j = ACTION_TO_INPUTS[rng.randrange(6)]
+                for _ in range(frame_skip):
+                    s.tick(h, j)
+                    ticks += 1
+                    if s.ninja.state in (6, 7, 8):
+                        break
+                if s.ninja.state in (6, 7, 8) or s.frame >= max_frames:
+                    s.reset()
+        out.append((ticks, time.perf_counter() - t0))
+    return out
 
 
-def run(maps, processes, seconds, frame_skip=4, max_frames=2000, seed=0, envs_per_process=8):
-    """-> (ticks/s over all processes, ticks, wall seconds, processes used, envs used).  `maps`: list of map_data rows;
-    every process gets `envs_per_process` of them (round-robin)."""
+def run_slices(maps, processes, seconds, n_slices, frame_skip=4, max_frames=2000, seed=0, envs_per_process=8):
+    """One worker pool; every worker loads `envs_per_process` of `maps` (round-robin) once and then runs `n_slices` timed
+    slices of `seconds` each (the envs keep their episode state across slices).
+    -> (list over slices of (ticks/s summed over workers, ticks), wall seconds, processes, envs)."""
     processes = max(1, int(processes))
     shares = [[maps[(p * envs_per_process + k) % len(maps)] for k in range(envs_per_process)] for p in range(processes)]
-    jobs = [(shares[p], seed * 1000 + p, frame_skip, max_frames, seconds) for p in range(processes)]
+    jobs = [(shares[p], seed * 1000 + p, frame_skip, max_frames, seconds, n_slices) for p in range(processes)]
     ctx = mp.get_context("fork")
     t0 = time.perf_counter()
     with ctx.Pool(processes) as pool:
         res = pool.map(_worker, jobs)
     wall = time.perf_counter() - t0
-    ticks = sum(r[0] for r in res)
-    busy = max(r[1] for r in res)          # the measured region of the slowest worker (startup / map loading excluded)
-    return ticks / busy, ticks, wall, processes, processes * envs_per_process
+    slices = []
+    for k in range(n_slices):
+        slices.append((sum(r[k][0] / r[k][1] for r in res), sum(r[k][0] for r in res)))
+    return slices, wall, processes, processes * envs_per_process
+
+
+def run(maps, processes, seconds, frame_skip=4, max_frames=2000, seed=0, envs_per_process=8):
+    """One slice: -> (ticks/s over all processes, ticks, wall seconds, processes used, envs used)."""
+    slices, wall, procs, envs = run_slices(maps, processes, seconds, 1, frame_skip, max_frames, seed, envs_per_process)
+    return slices[0][0], slices[0][1], wall, procs, envs
 
 
 def config1(map_data, hor, jump, reps=1000):

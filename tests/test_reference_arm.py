@@ -1,0 +1,47 @@
+"""bench.py's reference arm: the compiled reference of oracle/_ref (oracle/make_ref.py) reproduces BASELINE.json configs[0]'s
+known answer, and both arms describe the workload with the same `config` object."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench  # noqa: E402
+from oracle import ref_baseline as rb  # noqa: E402
+
+needs_ref = pytest.mark.skipif(not rb.available(), reason="oracle/_ref not built (python -m oracle.make_ref in the build container)")
+
+
+@needs_ref
+def test_compiled_reference_reproduces_config1_known_answer():
+    r = bench.config1_reference(2)
+    assert r["frames"] == 37 and r["final_state"] == 8
+    assert r["final_pos"] == [812.0036311681246, 542.0]            # BASELINE.json configs[0]
+    assert r["known_answer_ok"]
+
+
+@needs_ref
+def test_reference_pool_counts_ticks_of_the_workload_policy():
+    arr, lens = bench.load_maps("simplest_with_mines")
+    slices, wall, procs, envs = rb.run_slices([arr[k, :lens[k]] for k in range(4)], 2, 0.3, 2, envs_per_process=2)
+    assert procs == 2 and envs == 4 and len(slices) == 2
+    assert all(rate > 100 and ticks > 30 for rate, ticks in slices)
+
+
+def test_both_arms_describe_the_workload_identically():
+    a = bench.config_dict("c3", 65536, 4096, "scattered", True)
+    b = bench.config_dict("c3", 65536, 4096, "scattered", True)
+    assert a == b and set(a) >= {"workload", "envs_per_gpu", "frame_skip", "max_frames", "distinct_levels"}
+    assert "model" not in a
+
+
+def test_reference_modules_are_compiler_output_only():
+    """oracle/_ref holds no reference source text (only marshalled code objects and a manifest)."""
+    root = os.path.join(ROOT, "oracle", "_ref")
+    if not os.path.isdir(root):
+        pytest.skip("oracle/_ref not built")
+    for d, _, files in os.walk(root):
+        for f in files:
+            assert f.endswith(".refc") or f == "MANIFEST.txt", os.path.join(d, f)

@@ -16,7 +16,7 @@ L.osim_get_state.argtypes = [C.c_void_p, dp, C.POINTER(C.c_int64), dp, C.POINTER
 L.osim_num_entities.argtypes = [C.c_void_p]
 n_maps = int(sys.argv[1]) if len(sys.argv) > 1 else 256
 n_steps = int(sys.argv[2]) if len(sys.argv) > 2 else 400
-arr, lens = bench.load_maps("simplest_with_mines")
+arr, lens = bench.load_maps(os.environ.get("FIXTURE", "simplest_with_mines"))
 rng = np.random.default_rng(0)
 H = [0, -1, 1, 0, -1, 1]; J = [0, 0, 0, 1, 1, 1]
 calls = (C.c_long).in_dll(L, "osim_stat_calls")

@@ -15,11 +15,14 @@ import torch
 import bench
 from nclone_b200 import BatchedSimulator
 from nclone_b200._lib import lib as L
-n_envs = int(sys.argv[1]) if len(sys.argv) > 1 and sys.argv[1].isdigit() else 65536
+n_envs = next((int(a) for a in sys.argv[1:] if a.isdigit()), 65536)
 fixture = next((a for a in sys.argv[1:] if a in ("simplest_with_mines", "locked_doors", "bc_replays", "first_replay")), "simplest_with_mines")
 arr, lens = bench.load_maps(fixture)
-sim = BatchedSimulator(n_envs)
+handoff = {"--handoff=on": True, "--handoff=off": False}.get(next((a for a in sys.argv[1:] if a.startswith("--handoff=")), ""), None)
+placement = "caller" if "--engine-order=caller" in sys.argv else "level"
+sim = BatchedSimulator(n_envs, handoff=handoff, placement=placement)
 sim.load_maps([arr[k, :lens[k]] for k in range(len(arr))], np.arange(n_envs) % len(arr))
+print(f"fixture {fixture}, engine order {placement}, handoff {'on' if sim.handoff is not None else 'off'}, kernel {sim.kernel_variant()}")
 gen = torch.Generator(device="cuda"); gen.manual_seed(1)
 acts = torch.randint(0, 6, (64, n_envs), generator=gen, device="cuda", dtype=torch.uint8)
 for s in range(100):
@@ -52,13 +55,18 @@ lib_.nppsim_debug_warp_cycles.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_i
 ph0 = ph.copy(); lib_.nppsim_debug_warp_cycles(wc.ctypes.data, ph0.ctypes.data, nw, 0)
 torch.cuda.synchronize()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+lib_.nppsim_debug_solo_log.argtypes = [C.c_void_p, C.c_int, C.c_int]
+lib_.nppsim_debug_solo_log(None, 0, 1)
 e0.record(); sim.step(acts[7], 4, True); e1.record(); torch.cuda.synchronize()
+solo_log = np.zeros((8192, 4), dtype=np.uint64)
+n_solo_log = min(8192, lib_.nppsim_debug_solo_log(solo_log.ctypes.data, 8192, 0))
 lib_.nppsim_debug_warp_cycles(wc.ctypes.data, ph.ctypes.data, nw, 0)
 d = (ph - ph0).astype(np.float64); w = wc.astype(np.float64)
 print(f"last launch: {e0.elapsed_time(e1):.3f} ms = {e0.elapsed_time(e1) * 1.965e6:,.0f} cycles @1.965GHz")
 print("per-warp kernel cycles: mean %.0f p50 %.0f p90 %.0f p99 %.0f max %.0f" % (w.mean(), *np.percentile(w, [50, 90, 99]), w.max()))
 order = np.argsort(-w)[:8]
-n_ent = np.array([sim.maps[m].n_ent for m in sim.env_map_host])
+col_env = sim.slot_env if sim.slot_env is not None else np.arange(n_envs)      # state column -> caller's env
+n_ent = np.array([sim.maps[m].n_ent for m in np.asarray(sim.env_map_host)[col_env]])
 for o in order:
     envs = np.arange(o * 32, min(o * 32 + 32, n_envs))
     print(f"  warp {o}: total {w[o]:,.0f} entities/sweep/closest/post {d[o]} max n_ent in warp {n_ent[envs].max()}")
@@ -84,3 +92,24 @@ for o in long_:
     print(f"    {o:6d} {st[o]:8.1f} {en[o]:8.1f} {en[o] - st[o]:8.1f} {cost[o]:6d}   {d[o].astype(np.int64)}")
 quiet = np.nonzero(cost == 0)[0]
 print("  warps without cooperative iterations: mean cycles entities / sweep / closest / post:", d[quiet].mean(0).astype(np.int64), "duration us mean", (en - st)[quiet].mean())
+
+# ---- envs served by solo warps in the last launch (handoff): who ends the kernel now?
+if n_solo_log:
+    lg = solo_log[:n_solo_log]
+    env = (lg[:, 0] & 0xffffff).astype(np.int64); tf = ((lg[:, 0] >> 24) & 15).astype(np.int64)
+    conv = ((lg[:, 0] >> 28) & 1).astype(bool); init = ((lg[:, 0] >> 29) & 1).astype(bool)
+    pick = (lg[:, 1].astype(np.float64) - float(t0)) / 1e3; end = (lg[:, 2].astype(np.float64) - float(t0)) / 1e3
+    pub = np.where(lg[:, 3] > 0, (lg[:, 3].astype(np.float64) - float(t0)) / 1e3, np.nan)
+    print(f"solo warps: {n_solo_log} envs served, {int(init.sum())} queued at launch (a), {int((~init).sum())} handed over mid-launch (b), "
+          f"{int(conv.sum())} of them by warps of finished regular blocks")
+    print(f"  regular warps: last one finished at {en.max():.1f} us; solo services: last one finished at {end.max():.1f} us")
+    if init.any():
+        print(f"  (a) service duration us: mean {np.mean((end - pick)[init]):.1f} max {np.max((end - pick)[init]):.1f}; ends: p50 {np.percentile(end[init], 50):.1f} p90 {np.percentile(end[init], 90):.1f} max {end[init].max():.1f}")
+    b = ~init
+    if b.any():
+        print(f"  (b) published at us: p10 {np.nanpercentile(pub[b], 10):.1f} p50 {np.nanpercentile(pub[b], 50):.1f} p90 {np.nanpercentile(pub[b], 90):.1f} max {np.nanmax(pub[b]):.1f}; "
+              f"wait for a warp us: mean {np.nanmean((pick - pub)[b]):.1f} max {np.nanmax((pick - pub)[b]):.1f}; service us: mean {np.mean((end - pick)[b]):.1f} max {np.max((end - pick)[b]):.1f}")
+        print("  (b) first tick handed over: " + ", ".join(f"t={k}: {int((tf[b] == k).sum())}" for k in range(1, 4)))
+    print("  last solo services: (column, kind, first tick, published us, picked up us, ended us)")
+    for o in np.argsort(-end)[:16]:
+        print(f"    {env[o]:7d} {'a' if init[o] else ('b/conv' if conv[o] else 'b'):7s} {tf[o]:2d} {pub[o]:9.1f} {pick[o]:9.1f} {end[o]:9.1f}")
