@@ -397,7 +397,7 @@ def main():
     ap.add_argument("--no-flush", action="store_true", help="do not flush L2 between timed steps")
     ap.add_argument("--async-groups", type=int, default=4, help="also time the batch stepped as this many independent groups on separate streams (0: skip)")
     ap.add_argument("--placement", default="scattered", choices=["scattered", "adjacent"], help="caller's env -> level assignment: replicas of a level n_levels envs apart, or consecutive")
-    ap.add_argument("--engine-order", default="level", choices=["level", "caller"], help="BatchedSimulator placement: envs of a level in consecutive state columns (default), or the caller's order")
+    ap.add_argument("--engine-order", default="auto", choices=["level", "caller", "auto"], help="BatchedSimulator placement: envs of a level in consecutive state columns, the caller's order, or (default) by replicas per level")
     ap.add_argument("--handoff", default="auto", choices=["auto", "on", "off"], help="solo-warp handoff of wedged envs")
     ap.add_argument("--spread", type=int, default=300, help="untimed agent steps run first so envs sit at mixed episode phases")
     args = ap.parse_args()

@@ -17,22 +17,24 @@ from .map_compile import compile_map, content_key, MapTables
 
 
 class BatchedSimulator:
-    def __init__(self, n_envs, device="cuda:0", handoff=None, placement="level"):
+    def __init__(self, n_envs, device="cuda:0", handoff=None, placement="auto"):
         """handoff: run wedged envs on solo warps (nppsim_state_t.handoff; identical results, shorter step kernel).
-        Default: on for batches of at least 1,024 envs.
-        placement: "level" (default) keeps the envs of one level in consecutive state columns, whatever order the caller
-        numbers them in -- the lanes of a warp then read the same level tables and run the same entity loops -- and
-        every per-env array of this API stays in the caller's order (nppsim_state_t.ext_of); "caller": columns = env ids."""
+        Default (None): by batch size, see _auto_handoff.
+        placement: "level" keeps the envs of one level in consecutive state columns, whatever order the caller numbers them
+        in -- the lanes of a warp then read the same level tables and run the same entity loops -- and every per-env array of
+        this API stays in the caller's order (nppsim_state_t.ext_of); "caller": columns = env ids; "auto" (default): "level"
+        when a level has at least a warp's worth of replicas (n_envs >= 32 x distinct levels), else "caller"."""
         if not torch.cuda.is_available():
             raise RuntimeError("BatchedSimulator needs a CUDA device (there is no CPU fallback)")
         self.n_envs = int(n_envs)
-        self.use_handoff = (int(n_envs) >= 1024) if handoff is None else bool(handoff)
-        if placement not in ("level", "caller"):
-            raise ValueError("placement must be 'level' or 'caller'")
+        self._handoff_arg = handoff
+        if placement not in ("level", "caller", "auto"):
+            raise ValueError("placement must be 'level', 'caller' or 'auto'")
         self.placement = placement
         self.slot_env = None        # numpy [N]: caller env id of state column s (None: identity)
         self._slot_of = None        # device int64 [N]: state column of caller env e
         self.device = torch.device(device)
+        self.use_handoff = self._auto_handoff(self.n_envs) if handoff is None else bool(handoff)
         self.L = lib()
         self.maps = []          # MapTables per distinct level
         self._keys = {}
@@ -131,7 +133,10 @@ class BatchedSimulator:
         or no two envs share a level.  Sets env_map (device, column order), slot_env / _slot_of / ext_of."""
         N, dev = self.n_envs, self.device
         order = None
-        if self.placement == "level" and N > 1:
+        want = self.placement == "level"
+        if self.placement == "auto":                    # a level must be able to fill a warp for the grouping to pay (profiles/r02_handoff_ab.md)
+            want = N >= 32 * len(np.unique(env_map_host))
+        if want and N > 1:
             o = np.argsort(env_map_host, kind="stable")
             if not np.array_equal(o, np.arange(N)) and len(np.unique(env_map_host)) < N:
                 order = o
@@ -233,11 +238,20 @@ class BatchedSimulator:
         st.ent_flag, st.dyn_f, st.dyn_i = v._ent_flag.data_ptr(), v._dyn_f.data_ptr(), v._dyn_i.data_ptr()
         st.env_map, st.map_blob, st.map_off = v.env_map.data_ptr(), parent.map_blob, parent.map_off
         st.warp_order, st.warp_cost = v.warp_order.data_ptr(), v.warp_cost.data_ptr()
-        v.handoff = self._new_handoff() if self.use_handoff else None   # one queue per concurrently stepped state
+        v.use_handoff = self._auto_handoff(v.n_envs) if self._handoff_arg is None else self.use_handoff
+        v._handoff_arg = self._handoff_arg
+        v.handoff = self._new_handoff() if v.use_handoff else None      # one queue per concurrently stepped state
         st.handoff = v.handoff.data_ptr() if v.handoff is not None else None
         st.kind_mask = parent.kind_mask
         v._state = st
         return v
+
+    def _auto_handoff(self, n_envs):
+        """Solo-warp handoff of wedged envs pays while the launch is bound by its longest dependent chain -- up to two waves of
+        resident warps (8 per SM at 255 registers) -- and costs a few per cent once the launch is throughput bound (measured:
+        65,536 envs +7 %, 131,072 envs -3 ... -20 %; profiles/r02_handoff_ab.md)."""
+        sms = torch.cuda.get_device_properties(self.device).multi_processor_count
+        return 1024 <= n_envs and (n_envs + 31) // 32 <= 2 * 8 * sms
 
     _handoff_tags = 0
 
@@ -259,7 +273,9 @@ class BatchedSimulator:
         self._need_maps()
         basic = sum(1 << k for k in (FD.K_NONE, FD.K_MINE, FD.K_GOLD, FD.K_EXIT, FD.K_EXIT_SWITCH, FD.K_DOOR_LOCKED, FD.K_DOOR_TRAP))
         km = int(self._state.kind_mask)
-        return "sim_basic" if km != 0 and (km & ~basic) == 0 else "sim_full"
+        if km != 0 and (km & ~basic) == 0:
+            return "sim_basic_solo" if self.handoff is not None else "sim_basic"
+        return "sim_full"
 
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
@@ -532,6 +548,10 @@ class BatchedSimulator:
         """Per env: entity id / dyn slot of the LAST exit switch in entity_dic[3]
         (nplay_headless.py:546-564 iterates reversed) and of its parent door; -1 if none."""
         if getattr(self, "_exit_cache", None) is None or self._exit_cache[0] is not self.env_map:
+            if isinstance(self.maps, _DeviceMaps):
+                # device-compiled levels: read the blob headers and entity tables where they are (no blob crosses PCIe)
+                self._exit_cache = (self.env_map,) + self.maps.exit_slots(self.ent_cap, self.env_map[self._cols()])      # caller order
+                return self._exit_cache[1:]
             sw_id = np.full(len(self.maps), -1); sw_slot = sw_id.copy(); dr_slot = sw_id.copy()
             for k, t in enumerate(self.maps):
                 ids = np.nonzero(t.ents["kind"] == FD.K_EXIT_SWITCH)[0]
@@ -622,6 +642,39 @@ class _DeviceMaps:
 
     def __iter__(self):
         return (self[k] for k in range(self._n))
+
+    def exit_slots(self, ent_cap, env_map):
+        """Per env of `env_map` (device int64): entity id / dyn slot of the last exit switch of its level and the dyn slot
+        of that switch's door, -1 if none -- torch ops over the blobs' headers and NppStaticEnt tables in HBM (map_blob.h:
+        n_ent at byte 8, off_ents at byte 72; per 32-byte record kind at +16, dyn i16 at +20, aux i16 at +22)."""
+        dev = self._blob.device
+        B = self._blob[:self._n * self._stride].view(self._n, self._stride)
+
+        def u32(off):
+            w = B[:, off:off + 4].to(torch.int64)
+            return w[:, 0] | (w[:, 1] << 8) | (w[:, 2] << 16) | (w[:, 3] << 24)
+
+        def i16(pos):                                              # little-endian int16 at byte positions pos [M]
+            lo = B.gather(1, pos[:, None]).to(torch.int64)[:, 0]; hi = B.gather(1, pos[:, None] + 1).to(torch.int64)[:, 0]
+            v = lo | (hi << 8)
+            return torch.where(v >= 32768, v - 65536, v)
+
+        n_ent, off_ents = u32(8), u32(72)
+        e = torch.arange(max(1, int(ent_cap)), device=dev, dtype=torch.int64)[None, :]
+        valid = e < n_ent[:, None]
+        pos = (off_ents[:, None] + 32 * e + 16).clamp(max=self._stride - 1)
+        kind = B.gather(1, pos)
+        is_sw = valid & (kind == FD.K_EXIT_SWITCH)
+        sw_id = torch.where(is_sw, e, torch.full_like(e, -1)).max(dim=1).values          # the LAST one (nplay_headless.py:546-564)
+        base = off_ents + 32 * sw_id.clamp(min=0)
+        sw_slot = i16(base + 20)
+        door = i16(base + 22)
+        dr_slot = i16(off_ents + 32 * door.clamp(min=0) + 20)
+        none = sw_id < 0
+        sw_slot = torch.where(none, torch.full_like(sw_slot, -1), sw_slot)
+        dr_slot = torch.where(none | (door < 0), torch.full_like(dr_slot, -1), dr_slot)
+        em = env_map.to(torch.int64)
+        return sw_id[em], sw_slot[em], dr_slot[em]
 
 
 def _entity_rows(t, fl, df, di, order_mode):

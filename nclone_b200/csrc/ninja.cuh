@@ -142,7 +142,7 @@ DEV bool ninja_collide_vs_tiles(Nin& n, Ctx& c, WarpPool& wp, bool alive) {
 #define COOP_PARK(k, v) coop_slot(wp, k, lane) = v;
 #define COOP_TAKE(k, v) v = coop_slot(wp, k, o);
 #define COOP_BACK(k, v) v = coop_slot(wp, k, lane);
-#ifndef NPP_COOP_NOGROUPS
+#if NPP_GROUPS
         // Several lanes wait for service (the envs of a level share a warp, and a level that wedges one ninja wedges others):
         // serve up to four of them AT ONCE, each by a group of W = 8 (or two by W = 16) lanes, instead of one after the other --
         // the loop is a dependent chain per owner, so the chains of the groups overlap in the warp's instruction stream.

@@ -128,20 +128,44 @@ __global__ void __launch_bounds__(128) reset_kernel(nppsim_state_t st, const uin
 #ifndef STEP_BLOCKS_PER_SM
 #define STEP_BLOCKS_PER_SM 1
 #endif
+#ifdef NPP_STAGE_TMA
+#define NPP_STAGE_BYTES (NPP_NCELL * 4 + NPP_NCELL * NPP_SEGS_PER_CELL * 4)        // cell_hdr + segs: contiguous behind the blob header
+#define STEP_SMEM ((STEP_BLOCK / 32) * sizeof(WarpPool) + NPP_STAGE_BYTES + 16)
+#else
 #define STEP_SMEM ((STEP_BLOCK / 32) * sizeof(WarpPool))
+#endif
 #define NPP_MOVE_MASK ((1u << NPP_K_DRONE_ZAP) | (1u << NPP_K_MINI_DRONE) | (1u << NPP_K_BOUNCE) | (1u << NPP_K_THWUMP))
 #define NPP_THINK_MASK ((1u << NPP_K_DOOR_REGULAR) | (1u << NPP_K_THWUMP) | (1u << NPP_K_DEATH_BALL) | (1u << NPP_K_SHWUMP))
 #define NPP_PHYS_MASK ((1u << NPP_K_ONE_WAY) | (1u << NPP_K_BOUNCE) | (1u << NPP_K_THWUMP) | (1u << NPP_K_SHWUMP))
 // "basic" levels: nothing moves, nothing pushes (every generated curriculum category of BASELINE.json's configs)
 #define NPP_BASIC_MASK ((1u << NPP_K_NONE) | (1u << NPP_K_MINE) | (1u << NPP_K_GOLD) | (1u << NPP_K_EXIT) | (1u << NPP_K_EXIT_SWITCH) | (1u << NPP_K_DOOR_LOCKED) | (1u << NPP_K_DOOR_TRAP))
 
+// NPP_GROUPS: the grouped cooperative service of ninja.cuh (several waiting lanes of a warp served at once).  It pays wherever
+// the launch is throughput bound (+7 % config 4, +11 % 131,072 envs of config 3, +45 % the 130 replay levels) and costs 2 % in
+// code size / registers where wedged envs leave their warps anyway (handoff: up to two waves of warps), so the basic kernel
+// exists with and without it and the launcher picks by whether the state carries a handoff queue (profiles/r02_handoff_ab.md).
+#ifdef NPP_COOP_NOGROUPS
+#define NPP_GROUPS_DEFAULT 0
+#else
+#define NPP_GROUPS_DEFAULT 1
+#endif
 #define NPP_VARIANT sim_full
 #define NPP_KINDS 0xffffffffu
+#define NPP_GROUPS NPP_GROUPS_DEFAULT
 #include "sim_variant.inc"
 #undef NPP_VARIANT
 #undef NPP_KINDS
+#undef NPP_GROUPS
+#define NPP_VARIANT sim_basic_solo
+#define NPP_KINDS NPP_BASIC_MASK
+#define NPP_GROUPS 0
+#include "sim_variant.inc"
+#undef NPP_VARIANT
+#undef NPP_KINDS
+#undef NPP_GROUPS
 #define NPP_VARIANT sim_basic
 #define NPP_KINDS NPP_BASIC_MASK
+#define NPP_GROUPS NPP_GROUPS_DEFAULT
 #include "sim_variant.inc"
 #undef NPP_VARIANT
 #undef NPP_KINDS
@@ -466,14 +490,11 @@ int launch_step(const nppsim_state_t* st, const int8_t* hor, const int8_t* jump,
     if (!in && !actions && (!hor || !jump)) return fail(NPPSIM_E_ARG, "inputs are NULL");
     if (!in && !actions && !(input_ticks == 1 || input_ticks == n_ticks)) return fail(NPPSIM_E_ARG, "input_ticks must be 1 or n_ticks");
     const int block = STEP_BLOCK;
-    // solo blocks at the front of the grid for wedged envs (sim_variant.inc): 4 solo warps per 512 envs; all but the first
-    // eight blocks exit at once unless the previous launch left them an env
-    const int n_solo = st->handoff ? std::min(NPPSIM_HANDOFF_CAP / 4, std::max(2, st->n_envs / 512)) : 0;
-    const int solo_limit = std::max(64, st->n_envs / 384);      // envs per launch that start on solo warps; as many again may follow mid-launch
-    const int grid = (st->n_envs + block - 1) / block + n_solo;
+    static int sm_count[64] = {0};
     // shared-memory carve-out: room for the two blocks per SM the register file admits and not more -- the rest
     // of the 256 KB stays L1 for the level blobs (max-shared left 28 KB of L1: hit rate 40 % instead of 66 %)
     // (function attributes belong to the current device's context: set once per device, results checked)
+    int sms = 148;
     {
         static std::mutex init_mu;
         static bool init_done[64] = {false};
@@ -486,14 +507,26 @@ int launch_step(const nppsim_state_t* st, const int8_t* hor, const int8_t* jump,
             ie = cudaFuncSetAttribute(sim_basic::step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
             if (ie == cudaSuccess) ie = cudaFuncSetAttribute(sim_full::step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
             if (ie == cudaSuccess) ie = cudaFuncSetAttribute(sim_basic::step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)STEP_SMEM);
+            if (ie == cudaSuccess) ie = cudaFuncSetAttribute(sim_basic_solo::step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+            if (ie == cudaSuccess) ie = cudaFuncSetAttribute(sim_basic_solo::step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)STEP_SMEM);
             if (ie == cudaSuccess) ie = cudaFuncSetAttribute(sim_full::step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)STEP_SMEM);
             if (ie == cudaSuccess && dev >= 0 && dev < 64) init_done[dev] = true;
         }
         if (ie != cudaSuccess) return cuda_fail(ie, "step kernel attributes");
+        if (dev >= 0 && dev < 64 && !sm_count[dev]) cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev);
+        sms = (dev >= 0 && dev < 64 && sm_count[dev] > 0) ? sm_count[dev] : 148;
     }
+    // Solo blocks at the front of the grid for wedged envs (sim_variant.inc): 4 solo warps per 512 envs; all but the first
+    // eight blocks exit at once unless the previous launch left them an env.  Solo warps that had work stay resident and
+    // poll until the regular blocks are done, so their number is bounded well below the resident block slots (2 per SM):
+    // at most sms / 2 blocks can stay, whatever the batch size -- the regular blocks they wait for always find a slot.
+    const int stay_cap = std::max(1, sms / 2 - 8) * (block / 32);
+    const int n_solo = st->handoff ? std::min(sms / 2, std::max(2, st->n_envs / 512)) : 0;
+    const int solo_limit = std::min(stay_cap, std::max(64, st->n_envs / 384));      // envs per launch that start on solo warps; as many again may follow mid-launch
+    const int grid = (st->n_envs + block - 1) / block + n_solo;
     // kind_mask == 0: census unknown (older callers) -> the full kernel
     const bool basic = st->kind_mask != 0 && (st->kind_mask & ~NPP_BASIC_MASK) == 0;
-    auto kernel = basic ? sim_basic::step_kernel : sim_full::step_kernel;
+    auto kernel = basic ? (st->handoff ? sim_basic_solo::step_kernel : sim_basic::step_kernel) : sim_full::step_kernel;
     kernel<<<grid, block, STEP_SMEM, (cudaStream_t)stream>>>(*st, hor, jump, actions, input_ticks, n_ticks, tick_limit, stop_on_terminal, frames_executed, sp, n_solo, 2 * solo_limit);
     g_launches++;
     cudaError_t e = cudaGetLastError();

@@ -106,12 +106,12 @@ DEV int gather_list(WarpPool& wp, const Ctx& c, bool active, double x1, double y
             #pragma unroll 1
             for (int yc = cy0; yc <= cy1; yc += 2) {
                 const int ci = xc * NPP_NCY + yc;
-                const uint32_t h0 = __ldg(c.cell_hdr + ci), h1 = (yc < cy1) ? __ldg(c.cell_hdr + ci + 1) : 0u;
+                const uint32_t h0 = NPP_LDG(c.cell_hdr + ci), h1 = (yc < cy1) ? NPP_LDG(c.cell_hdr + ci + 1) : 0u;
                 const bool p0 = cell_pass(h0, min_x, min_y, max_x, max_y), p1 = cell_pass(h1, min_x, min_y, max_x, max_y);
                 const uint4* sp = reinterpret_cast<const uint4*>(c.segs + ci * NPP_SEGS_PER_CELL);
                 uint4 a0 = z, b0 = z, a1 = z, b1 = z;
-                if (p0) { a0 = __ldg(sp); if ((h0 & 15) > 4) b0 = __ldg(sp + 1); }
-                if (p1) { a1 = __ldg(sp + 2); if ((h1 & 15) > 4) b1 = __ldg(sp + 3); }
+                if (p0) { a0 = NPP_LDG(sp); if ((h0 & 15) > 4) b0 = NPP_LDG(sp + 1); }
+                if (p1) { a1 = NPP_LDG(sp + 2); if ((h1 & 15) > 4) b1 = NPP_LDG(sp + 3); }
                 if (p0) n = list_append(dst, n, a0, b0, h0 & 15);
                 if (p1) n = list_append(dst, n, a1, b1, h1 & 15);
             }

@@ -84,3 +84,63 @@ long osim_baseline_run(const double *maps, const int32_t *lens, int n_maps, int 
     free(th); free(jobs);
     return total;
 }
+
+/* ---- rollout with checkpoints (tests/test_gpu_parity.py soak slice): env e runs on map row env_map[e]; the ninja record
+   (31 doubles, 27 ints: osim_get_state) after every `every`-th agent step -- before the turnover of that step -- goes to
+   out_f[(s / every) * n_envs + e][31] / out_i[...][27].  Turnover = a fresh load of the level (the GPU's reset mode 0), on
+   win / death or at max_frames, as tests/test_gpu_parity.py::_oracle_rollout does it. */
+typedef struct {
+    const double *maps; const int32_t *lens; int stride; const int32_t *env_map; int env_lo, env_hi, n_envs;
+    const uint8_t *actions; int n_steps; int frame_skip; int max_frames; int every;
+    double *out_f; int64_t *out_i; long ticks;
+} RJob;
+
+static void *rollout_worker(void *arg) {
+    RJob *j = (RJob *)arg;
+    OSim *S = osim_create();
+    long ticks = 0;
+    for (int e = j->env_lo; e < j->env_hi; e++) {
+        const int m = j->env_map[e];
+        const double *md = j->maps + (size_t)m * j->stride;
+        if (osim_load(S, md, j->lens[m])) continue;
+        for (int s = 0; s < j->n_steps; s++) {
+            int a = j->actions[(size_t)s * j->n_envs + e] % 6;          /* actions[step][env], as the GPU takes them */
+            double nf[31]; int64_t ni[27];
+            for (int k = 0; k < j->frame_skip; k++) {
+                osim_tick(S, ACT_H[a], ACT_J[a]); ticks++;
+                osim_get_state(S, nf, ni, NULL, NULL);
+                if (ni[0] >= 6 && ni[0] <= 8) break;
+            }
+            if ((s + 1) % j->every == 0) {
+                size_t row = (size_t)(s / j->every) * j->n_envs + e;
+                for (int q = 0; q < 31; q++) j->out_f[row * 31 + q] = nf[q];
+                for (int q = 0; q < 27; q++) j->out_i[row * 27 + q] = ni[q];
+            }
+            if ((ni[0] >= 6 && ni[0] <= 8) || ni[26] >= j->max_frames) osim_load(S, md, j->lens[m]);
+        }
+    }
+    osim_destroy(S);
+    j->ticks = ticks;
+    return NULL;
+}
+
+long osim_rollout_records(const double *maps, const int32_t *lens, int stride, const int32_t *env_map, int n_envs,
+                          const uint8_t *actions, int n_steps, int frame_skip, int max_frames, int every, int n_threads,
+                          double *out_f, int64_t *out_i) {
+    if (n_threads < 1) n_threads = 1;
+    if (n_threads > n_envs) n_threads = n_envs;
+    pthread_t *th = (pthread_t *)malloc(sizeof(pthread_t) * n_threads);
+    RJob *jobs = (RJob *)calloc(n_threads, sizeof(RJob));
+    for (int t = 0; t < n_threads; t++) {
+        RJob *j = &jobs[t];
+        j->maps = maps; j->lens = lens; j->stride = stride; j->env_map = env_map; j->n_envs = n_envs;
+        j->env_lo = (int)((long)n_envs * t / n_threads); j->env_hi = (int)((long)n_envs * (t + 1) / n_threads);
+        j->actions = actions; j->n_steps = n_steps; j->frame_skip = frame_skip; j->max_frames = max_frames; j->every = every;
+        j->out_f = out_f; j->out_i = out_i;
+        pthread_create(&th[t], NULL, rollout_worker, j);
+    }
+    long total = 0;
+    for (int t = 0; t < n_threads; t++) { pthread_join(th[t], NULL); total += jobs[t].ticks; }
+    free(th); free(jobs);
+    return total;
+}

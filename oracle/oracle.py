@@ -56,6 +56,8 @@ def lib():
         L.osim_action_mask.argtypes = [C.c_void_p, C.c_int, u8p]
         L.osim_baseline_run.argtypes = [dp, i32p, C.c_int, C.c_int, u8p, C.c_int, C.c_int, C.c_int, C.c_int, dp, dp]
         L.osim_baseline_run.restype = C.c_long
+        L.osim_rollout_records.argtypes = [dp, i32p, C.c_int, i32p, C.c_int, u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, dp, ip]
+        L.osim_rollout_records.restype = C.c_long
         _lib = L
     return _lib
 
@@ -182,3 +184,17 @@ def baseline_run(maps, lens, actions, frame_skip, max_frames, n_threads):
                                     _p(actions, C.c_uint8), actions.shape[1], frame_skip, max_frames, n_threads,
                                     C.byref(cs), C.byref(secs))
     return int(ticks), secs.value
+
+
+def rollout_records(maps, lens, env_map, actions, frame_skip, max_frames, every, n_threads):
+    """Multi-threaded oracle rollout with checkpoints (baseline_runner.c: osim_rollout_records).  maps [M,stride] f64,
+    env_map [N], actions [S,N] u8 (step-major, as the GPU takes them) -> (ticks, nin_f [S//every, N, 31], nin_i [S//every, N, 27])
+    taken after every `every`-th agent step, before that step's turnover (fresh load on win / death / max_frames)."""
+    maps = np.ascontiguousarray(maps, dtype=np.float64); lens = np.ascontiguousarray(lens, dtype=np.int32)
+    env_map = np.ascontiguousarray(env_map, dtype=np.int32); actions = np.ascontiguousarray(actions, dtype=np.uint8)
+    S, N = actions.shape
+    out_f = np.zeros((S // every, N, 31)); out_i = np.zeros((S // every, N, 27), dtype=np.int64)
+    ticks = lib().osim_rollout_records(_p(maps, C.c_double), _p(lens, C.c_int32), maps.shape[1], _p(env_map, C.c_int32), N,
+                                       _p(actions, C.c_uint8), S, frame_skip, max_frames, every, n_threads,
+                                       _p(out_f, C.c_double), _p(out_i, C.c_int64))
+    return int(ticks), out_f, out_i

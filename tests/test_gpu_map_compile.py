@@ -189,6 +189,11 @@ def test_load_maps_device_equals_load_maps(golden_generated):
         x, y = getattr(a, name), getattr(b, name)
         assert torch.equal(x.view(torch.uint8), y.view(torch.uint8)), name
     assert torch.equal(a.env_i[:5], b.env_i[:5])
+    # the exit getters of a device-compiled batch read the entity tables in HBM: same answers, no blob pulled to the host
+    for fa, fb in ((a.exit_switch_position(), b.exit_switch_position()), (a.exit_door_position(), b.exit_door_position())):
+        assert torch.equal(fa[0], fb[0]) and torch.equal(fa[1], fb[1])
+    assert torch.equal(a.exit_switch_activated(), b.exit_switch_activated())
+    assert a.exit_switch_position()[0].abs().sum() > 0 and len(b.maps._cache) == 0
     ra, rb = a.canonical_state([0, 7, N - 1]), b.canonical_state([0, 7, N - 1])
     from oracle import schema
     assert [schema.state_hash(*r) for r in ra] == [schema.state_hash(*r) for r in rb]

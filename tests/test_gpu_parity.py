@@ -286,8 +286,9 @@ def test_large_random_rollout_vs_oracle(golden_replays):
     for st in range(1, steps):
         keep = (st % hold[st]) != 0
         actions[st, keep] = actions[st - 1, keep]
-    sim = BatchedSimulator(N)
+    sim = BatchedSimulator(N, placement="level")              # state columns permuted against the caller's env order (ext_of)
     sim.load_maps(maps, env_to_map)
+    assert sim.slot_env is not None
     ref = _oracle_rollout(maps, env_to_map, actions, 4, 2000, every)
     ci = 0
     for st in range(steps):
@@ -299,6 +300,47 @@ def test_large_random_rollout_vs_oracle(golden_replays):
             badi = np.nonzero((gi != ni).any(1))[0]
             assert badf.size == 0 and badi.size == 0, (st, badf[:5], badi[:5], env_to_map[badf[:5]])
         sim.reset_terminal(2000)
+
+
+def test_soak_slice_random_rollout_vs_oracle():
+    """A bounded slice of tools/soak_parity.py inside the suite (about 30 s): 12,288 envs on random levels of both bench level
+    sets (config 3's mines, config 4's locked doors), 160 agent steps of held random actions (7.4 M ticks): every env's
+    ninja record compared bit-for-bit with the oracle every 20 steps.  The oracle side is the threaded C rollout
+    (oracle/baseline_runner.c: osim_rollout_records), itself pinned to the per-tick loop in test_oracle_golden.py.
+    The seed is fixed so that a failure reproduces; tools/soak_parity.py takes any seed and size."""
+    import torch
+    from nclone_b200 import BatchedSimulator
+    from oracle import oracle as orc
+    import bench
+    arr, lens = bench.load_maps("simplest_with_mines")
+    arr2, lens2 = bench.load_maps("locked_doors")
+    stride = max(arr.shape[1], arr2.shape[1])
+    maps = np.zeros((len(arr) + len(arr2), stride)); maps[:len(arr), :arr.shape[1]] = arr; maps[len(arr):, :arr2.shape[1]] = arr2
+    mlens = np.concatenate([lens, lens2]).astype(np.int32)
+    N, steps, every = 12288, 160, 20
+    rng = np.random.default_rng(2026)
+    env_to_map = rng.integers(0, len(maps), size=N)
+    actions = rng.integers(0, 6, size=(steps, N)).astype(np.uint8)
+    hold = rng.integers(1, 8, size=(steps, N))
+    for st in range(1, steps):
+        keep = (st % hold[st]) != 0
+        actions[st, keep] = actions[st - 1, keep]
+    used = np.unique(env_to_map)                                   # compile only the levels in use
+    remap = np.zeros(len(maps), dtype=np.int64); remap[used] = np.arange(len(used))
+    ticks, of, oi = orc.rollout_records(maps, mlens, env_to_map, actions, 4, 2000, every, os.cpu_count() or 1)
+    sim = BatchedSimulator(N)
+    sim.load_maps([maps[k, :mlens[k]] for k in used], remap[env_to_map])
+    for st in range(steps):
+        sim.step(torch.from_numpy(actions[st]).cuda(), 4, True)
+        if (st + 1) % every == 0:
+            c = st // every
+            gf = sim.nin_f.cpu().numpy().T; gi = sim.nin_i.cpu().numpy().T.astype(np.int64)
+            badf = np.nonzero((gf.view(np.int64) != of[c].view(np.int64)).any(1))[0]
+            badi = np.nonzero((gi != oi[c]).any(1))[0]
+            assert badf.size == 0 and badi.size == 0, (st, badf[:5], badi[:5], env_to_map[badf[:5]])
+        sim.reset_terminal(2000)
+    assert sim.total_ticks() == ticks and ticks > 6_000_000
+    assert sim.handoff_status() == 0
 
 
 def test_wedged_ninja_cooperative_loop_vs_oracle():
@@ -602,7 +644,7 @@ def test_groups_views_step_independently(golden_replays, golden_generated):
     for s in range(steps):
         whole.step(torch.from_numpy(acts[s]).cuda(), 4, True); whole.reset_terminal(60)
     want = [schema.state_hash(*r) for r in whole.canonical_state()]
-    sim = BatchedSimulator(N); sim.load_maps(maps, env_to_map)
+    sim = BatchedSimulator(N, placement="level"); sim.load_maps(maps, env_to_map)
     groups = sim.groups(3)
     assert [g.n_envs for g in groups] == [64, 64, 39]
     streams = [torch.cuda.Stream() for _ in groups]
@@ -647,7 +689,7 @@ def test_full_size_replica_consistency_and_oracle_sample():
     # replica r of level m lives at env (m * 7 + r * 4099) % N-ish: a permutation that spreads replicas over warps and lanes
     perm = (np.arange(N, dtype=np.int64) * 40503) % N          # 40503 is odd, N a power of two: a bijection
     env_to_map = np.empty(N, dtype=np.int64); env_to_map[perm] = np.arange(N) % M
-    sim = BatchedSimulator(N)
+    sim = BatchedSimulator(N, placement="level")              # the permuted layout at full size (the default here would be the caller's order: 16 replicas per level)
     sim.load_maps(maps, env_to_map)
     rng = np.random.default_rng(3)
     steps = 60

@@ -191,3 +191,37 @@ def test_oracle_checkpoint_replay_matches_reference():
         assert (nf[0], nf[1]) == tuple(d["ck_pos"][k])
         assert np.array_equal(nf.view(np.int64), d["ck_nin_f"][k].view(np.int64)) and np.array_equal(ni, d["ck_nin_i"][k])
         assert np.array_equal(ef.view(np.int64), d["ck_ent_f"][e0:e1].view(np.int64)) and np.array_equal(ei, d["ck_ent_i"][e0:e1])
+
+
+def test_threaded_rollout_records_match_the_per_tick_loop():
+    """oracle/baseline_runner.c: osim_rollout_records (the soak slice's checker) == the per-env, per-tick OracleSim loop."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    from oracle import oracle as orc
+    arr, lens = bench.load_maps("locked_doors")
+    N, S, every, M = 96, 60, 10, 24
+    rng = np.random.default_rng(5)
+    em = rng.integers(0, M, size=N)
+    acts = rng.integers(0, 6, size=(S, N)).astype(np.uint8)
+    ticks, of, oi = orc.rollout_records(arr[:M], lens[:M], em, acts, 4, 300, every, 4)
+    L = orc.lib()
+    import ctypes as C
+    total = 0
+    nf = np.zeros(31); ni = np.zeros(27, dtype=np.int64)
+    for e in range(N):
+        s = orc.OracleSim(); md = arr[em[e], :lens[em[e]]]; s.load(md)
+        for st in range(S):
+            h, j = ((0, 0), (-1, 0), (1, 0), (0, 1), (-1, 1), (1, 1))[acts[st, e]]
+            for _ in range(4):
+                L.osim_tick(s.h, h, j); total += 1
+                L.osim_get_state(s.h, nf.ctypes.data_as(C.POINTER(C.c_double)), ni.ctypes.data_as(C.POINTER(C.c_int64)), None, None)
+                if ni[0] in (6, 7, 8):
+                    break
+            if (st + 1) % every == 0:
+                c = st // every
+                assert (nf.view(np.int64) == of[c, e].view(np.int64)).all() and (ni == oi[c, e]).all(), (e, st)
+            if ni[0] in (6, 7, 8) or ni[26] >= 300:
+                s.load(md)
+    assert total == ticks

@@ -1,0 +1,19 @@
+#!/bin/bash
+# round 2, GPU call 11: three-variant build (basic / basic_solo / full), TMA staging A/B
+mkdir -p gpurun_out/r02k
+O=gpurun_out/r02k
+summ() { python -c "
+import sys, json
+l = json.loads(sys.stdin.read().strip().split('\n')[-1])
+print('$1', 'value %.1fM e2e %.1fM step_kernel %.3f ms reset %.3f ms' % (l['value'] / 1e6, l['e2e']['value'] / 1e6, l['kernel_ms']['step_kernel'], l['kernel_ms']['reset_kernel']), l.get('kernel'), l.get('handoff'))"; }
+echo "== parity"; timeout 1200 python -m pytest tests/test_gpu_parity.py -x -q -m gpu > $O/parity.log 2>&1; tail -3 $O/parity.log
+echo "== parity (tma.so)"; NPPSIM_LIB=$PWD/variants/tma.so timeout 1200 python -m pytest tests/test_gpu_parity.py -x -q -m gpu -k "bc_replays or generated or doors or large_random or handoff or full_size or groups" > $O/parity_tma.log 2>&1; tail -3 $O/parity_tma.log
+for so in main tma; do
+  for cfg in "c3 65536 auto" "c4 131072 auto" "c5 65536 auto" "c5 65536 off" "c3 131072 auto" "c2 4096 auto" "c2 4096 off"; do
+    set -- $cfg
+    lib=$PWD/variants/$so.so; [ $so = main ] && lib=$PWD/nclone_b200/libnppsim.so
+    NPPSIM_LIB=$lib timeout 300 python bench.py --workload $1 --envs $2 --handoff $3 --steps 60 --warmup 5 --no-cpu-baseline --no-secondary --async-groups 0 2>$O/err_${so}_$1_$2_$3.log | tail -1 > $O/bench_${so}_$1_$2_$3.json
+    summ "$so $1 $2 handoff=$3" < $O/bench_${so}_$1_$2_$3.json
+  done
+done
+echo "== default bench"; ( time timeout 900 python bench.py --no-cpu-baseline > $O/bench_default.json 2>$O/bench_default.err ) 2>&1 | grep real; summ default < $O/bench_default.json
