@@ -188,10 +188,11 @@ class BatchedSimulator:
         self.warp_order = torch.arange(nw, dtype=torch.int32, device=dev)      # longest-first launch order (csrc/sim_variant.inc)
         self.warp_cost = torch.zeros(nw, dtype=torch.int32, device=dev)
         st.warp_order, st.warp_cost = self.warp_order.data_ptr(), self.warp_cost.data_ptr()
-        self.handoff = self._new_handoff() if self.use_handoff else None
-        st.handoff = self.handoff.data_ptr() if self.handoff is not None else None
         self.kind_mask = int(kind_mask)
         st.kind_mask = self.kind_mask
+        # solo warps exist in the basic kernel only (csrc/nppsim_kernels.cu: NPP_SOLO)
+        self.handoff = self._new_handoff() if (self.use_handoff and self._is_basic(self.kind_mask)) else None
+        st.handoff = self.handoff.data_ptr() if self.handoff is not None else None
         self._state = st
 
     # ------------------------------------------------------------------ sub-batches for asynchronous stepping
@@ -240,7 +241,7 @@ class BatchedSimulator:
         st.warp_order, st.warp_cost = v.warp_order.data_ptr(), v.warp_cost.data_ptr()
         v.use_handoff = self._auto_handoff(v.n_envs) if self._handoff_arg is None else self.use_handoff
         v._handoff_arg = self._handoff_arg
-        v.handoff = self._new_handoff() if v.use_handoff else None      # one queue per concurrently stepped state
+        v.handoff = self._new_handoff() if (v.use_handoff and self._is_basic(parent.kind_mask)) else None      # one queue per concurrently stepped state
         st.handoff = v.handoff.data_ptr() if v.handoff is not None else None
         st.kind_mask = parent.kind_mask
         v._state = st
@@ -268,12 +269,15 @@ class BatchedSimulator:
         self._need_maps()
         self._state.kind_mask = 0 if on else self.kind_mask
 
-    def kernel_variant(self):
-        """Which step-kernel instantiation launch_step picks for this batch (nppsim_kernels.cu: NPP_BASIC_MASK)."""
-        self._need_maps()
+    @staticmethod
+    def _is_basic(kind_mask):
         basic = sum(1 << k for k in (FD.K_NONE, FD.K_MINE, FD.K_GOLD, FD.K_EXIT, FD.K_EXIT_SWITCH, FD.K_DOOR_LOCKED, FD.K_DOOR_TRAP))
-        km = int(self._state.kind_mask)
-        if km != 0 and (km & ~basic) == 0:
+        return kind_mask != 0 and (kind_mask & ~basic) == 0
+
+    def kernel_variant(self):
+        """Which step-kernel instantiation launch_step picks for this batch (nppsim_kernels.cu: NPP_BASIC_MASK, NPP_SOLO)."""
+        self._need_maps()
+        if self._is_basic(int(self._state.kind_mask)):
             return "sim_basic_solo" if self.handoff is not None else "sim_basic"
         return "sim_full"
 

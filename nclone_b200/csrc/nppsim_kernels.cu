@@ -149,26 +149,35 @@ __global__ void __launch_bounds__(128) reset_kernel(nppsim_state_t st, const uin
 #else
 #define NPP_GROUPS_DEFAULT 1
 #endif
+// NPP_SOLO: solo warps + handoff queue (sim_variant.inc).  Only sim_basic_solo carries them: the flag tests at every phase
+// barrier and the generalised tick loop cost the other variants 3-7 % (one-level config 2: 0.096 -> 0.104 ms per launch).
 #define NPP_VARIANT sim_full
 #define NPP_KINDS 0xffffffffu
 #define NPP_GROUPS NPP_GROUPS_DEFAULT
+#define NPP_SOLO 0
 #include "sim_variant.inc"
 #undef NPP_VARIANT
 #undef NPP_KINDS
 #undef NPP_GROUPS
+#undef NPP_SOLO
 #define NPP_VARIANT sim_basic_solo
 #define NPP_KINDS NPP_BASIC_MASK
 #define NPP_GROUPS 0
+#define NPP_SOLO 1
 #include "sim_variant.inc"
 #undef NPP_VARIANT
 #undef NPP_KINDS
 #undef NPP_GROUPS
+#undef NPP_SOLO
 #define NPP_VARIANT sim_basic
 #define NPP_KINDS NPP_BASIC_MASK
 #define NPP_GROUPS NPP_GROUPS_DEFAULT
+#define NPP_SOLO 0
 #include "sim_variant.inc"
 #undef NPP_VARIANT
 #undef NPP_KINDS
+#undef NPP_GROUPS
+#undef NPP_SOLO
 
 namespace {
 // Longest-first order for the next launch from the costs of this one (one block; nw <= 2^20 / 32).
@@ -521,19 +530,20 @@ int launch_step(const nppsim_state_t* st, const int8_t* hor, const int8_t* jump,
     // poll until the regular blocks are done, so their number is bounded well below the resident block slots (2 per SM):
     // at most sms / 2 blocks can stay, whatever the batch size -- the regular blocks they wait for always find a slot.
     const int stay_cap = std::max(1, sms / 2 - 8) * (block / 32);
-    const int n_solo = st->handoff ? std::min(sms / 2, std::max(2, st->n_envs / 512)) : 0;
+    // kind_mask == 0: census unknown (older callers) -> the full kernel.  Solo warps exist in the basic kernel only.
+    const bool basic = st->kind_mask != 0 && (st->kind_mask & ~NPP_BASIC_MASK) == 0;
+    int32_t* const handoff = basic ? st->handoff : nullptr;
+    const int n_solo = handoff ? std::min(sms / 2, std::max(2, st->n_envs / 512)) : 0;
     const int solo_limit = std::min(stay_cap, std::max(64, st->n_envs / 384));      // envs per launch that start on solo warps; as many again may follow mid-launch
     const int grid = (st->n_envs + block - 1) / block + n_solo;
-    // kind_mask == 0: census unknown (older callers) -> the full kernel
-    const bool basic = st->kind_mask != 0 && (st->kind_mask & ~NPP_BASIC_MASK) == 0;
-    auto kernel = basic ? (st->handoff ? sim_basic_solo::step_kernel : sim_basic::step_kernel) : sim_full::step_kernel;
+    auto kernel = basic ? (handoff ? sim_basic_solo::step_kernel : sim_basic::step_kernel) : sim_full::step_kernel;
     kernel<<<grid, block, STEP_SMEM, (cudaStream_t)stream>>>(*st, hor, jump, actions, input_ticks, n_ticks, tick_limit, stop_on_terminal, frames_executed, sp, n_solo, 2 * solo_limit);
     g_launches++;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_fail(e, "step_kernel launch");
-    if ((st->warp_order && st->warp_cost) || st->handoff) {
+    if ((st->warp_order && st->warp_cost) || handoff) {
         const size_t S = st->stride ? (size_t)st->stride : (size_t)st->n_envs;
-        sched_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(st->warp_cost ? st->warp_order : nullptr, st->warp_cost, (st->n_envs + 31) / 32, st->handoff,
+        sched_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(st->warp_cost ? st->warp_order : nullptr, st->warp_cost, (st->n_envs + 31) / 32, handoff,
                                                            st->env_i + (size_t)NPPSIM_ENV_WEDGE * S, solo_limit);
         g_launches++;
         e = cudaGetLastError();

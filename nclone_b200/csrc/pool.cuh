@@ -46,8 +46,9 @@ __device__ unsigned long long g_coop_cycles[8];        // cooperative depenetrat
 #endif
 // (a solo warp -- Ctx::solo, block-uniform -- runs handed-off envs by itself and takes no part in block barriers)
 #if NPP_PHASE_SYNC
-#define NPP_BLOCK_ANY(p) (c.solo ? (__any_sync(0xffffffffu, (p)) != 0) : (__syncthreads_or((int)(p)) != 0))
-#define NPP_BLOCK_SYNC() do { if (!c.solo) __syncthreads(); } while (0)
+// (NPP_SOLO is the including variant's compile-time switch, sim_variant.inc: only a kernel with solo warps tests the flag)
+#define NPP_BLOCK_ANY(p) ((NPP_SOLO && c.solo) ? (__any_sync(0xffffffffu, (p)) != 0) : (__syncthreads_or((int)(p)) != 0))
+#define NPP_BLOCK_SYNC() do { if (!(NPP_SOLO && c.solo)) __syncthreads(); } while (0)
 #else
 #define NPP_BLOCK_ANY(p) __any_sync(FULL_MASK, (p))
 #define NPP_BLOCK_SYNC()
