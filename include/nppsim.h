@@ -97,9 +97,11 @@ typedef struct {
                                    NULL: every env stays in its home lane.  Results are identical either way. */
 } nppsim_state_t;
 #define NPPSIM_HANDOFF_CAP   4096
-#define NPPSIM_HANDOFF_HDR   8      /* [0] entries reserved, [1] tickets taken, [2] regular blocks finished (per launch); [3] error
+#define NPPSIM_HANDOFF_HDR   16     /* [0] entries reserved, [1] tickets taken, [2] regular blocks finished (per launch); [3] error
                                        bits, [4] mid-launch handoffs so far (both sticky); [5] length of the next launch's list;
-                                       [6] tag (caller); [7] initial entries of the current launch */
+                                       [6] tag (caller); [7] initial entries of the current launch; [8] regular block slots claimed,
+                                       [9] initial entries claimed, [10] SMs reserved for solo blocks, [11] blocks that went solo on
+                                       such an SM (all four per launch; "solo SMs", csrc/sim_variant.inc); [12..15] reserved */
 #define NPPSIM_HANDOFF_WORDS (NPPSIM_HANDOFF_HDR + 2 * NPPSIM_HANDOFF_CAP)
 
 /* Per-env input streams for nppsim_step_stream: env i owns data[offset[i] .. offset[i+1]) -- ragged, no padding. */

@@ -620,6 +620,10 @@ class BatchedSimulator:
         """Envs that will start the next launch on a solo warp (their last tick was wedged)."""
         return 0 if self.handoff is None else int(self.handoff[7].item())
 
+    def solo_sms(self):
+        """SMs reserved for solo blocks in the next launch (0: solo blocks sit at the front of the grid; include/nppsim.h, word 10)."""
+        return 0 if self.handoff is None else int(self.handoff[10].item())
+
     def launch_count(self):
         return int(self.L.nppsim_launch_count())
 

@@ -114,13 +114,29 @@ DEV bool ninja_collide_vs_tiles(Nin& n, Ctx& c, WarpPool& wp, bool alive) {
     // lane (0.2 %) but long (a wedged ninja takes all 32), so the warp serves one such lane at a time
     // with its cached segments spread over the lanes.
     double a0 = 0, b0 = 0; int nseg = 0;
+    bool need;
+    int it_first = 2;                                       // first iteration of the cooperative service below (warp-uniform)
+#if NPP_SOLO
+    // A solo warp runs ONE env (sim_variant.inc): the pooled machinery for iterations 0 and 1 -- queue scan, shared-memory
+    // staging, ordered fold, built for 32 sparse queries -- cost it ~7 k cycles per substep for two evaluations.  It gathers
+    // the env's list and enters the cooperative service at iteration 0 instead: the same query and the same push per
+    // iteration, on the same inputs.
+    if (c.solo) {
+        nseg = gather_list(wp, c, alive, gx1, gy1, gx2, gy2);
+        __syncwarp();
+        need = alive;
+        it_first = 0;
+    } else
+#endif
+    {
     int result0 = pooled_closest_point(wp, c, alive, gx1, gy1, gx2, gy2, xpos, ypos, a0, b0, nseg);
-    bool need = alive && depen(result0, a0, b0);
+    need = alive && depen(result0, a0, b0);
     NPP_BLOCK_SYNC();
     if (__any_sync(FULL_MASK, need)) {                      // iteration 1: 5 % of lanes, i.e. most warps -> pooled again
         double a = 0, b = 0;
         int result = pooled_list_closest(wp, c, need, nseg, gx1, gy1, gx2, gy2, xpos, ypos, a, b);
         if (need) need = depen(result, a, b);
+    }
     }
     unsigned todo;
 #ifndef NPP_COOP_LEGACY
@@ -224,7 +240,7 @@ DEV bool ninja_collide_vs_tiles(Nin& n, Ctx& c, WarpPool& wp, bool alive) {
         int w1 = -1, w2 = -1;                                // winning lanes of the last two calls (-1: unknown)
         int it;
         #pragma unroll 1
-        for (it = 2; it < 32; it++) {
+        for (it = it_first; it < 32; it++) {
             ncoop++;
 #ifdef NPP_COOP_SPEC   // measured slower than the plain uniform loop (the broadcast of the push costs what the select saved); kept for A/B
             // Speculative push: every lane pushes from ITS segment's closest point while the warp minimum is being
@@ -358,6 +374,7 @@ DEV bool ninja_collide_vs_tiles(Nin& n, Ctx& c, WarpPool& wp, bool alive) {
     if ((threadIdx.x & 31) == 0) wp.coop += ncoop;
 #ifdef NPP_PROFILE
     if ((threadIdx.x & 31) == 0 && ncoop) { for (int k = 0; k < 6; k++) if (k != 3) atomicAdd(&g_coop_cycles[k], (unsigned long long)cacc[k]); atomicAdd(&g_coop_cycles[3], (unsigned long long)ncoop); }
+    if ((threadIdx.x & 31) == 0 && ncoop && wp.group < 0) { wp.sph[4] += (unsigned long long)(cacc[0] + cacc[1] + cacc[2]); wp.sph[5] += (unsigned long long)cacc[5]; }
 #endif
 #undef COOP_STATE
 #undef COOP_PARK
@@ -629,10 +646,16 @@ DEV void ninja_think(Nin& n, const Ctx& c, int hor_input, int jump_input) {
 
 // Simulator.tick: nsim.py:221-292 (headless: enable_anim, log_data false).  Warp-synchronous: all 32
 // lanes call it together; `run` lanes advance their env by one frame.
-DEV void sim_tick(Nin& n, Ctx& c, WarpPool& wp, bool run, int hor_input, int jump_input) {
+// s_resume > 0 (solo warps, warp-uniform): the tick was started by the env's home lane, which left it after substep
+// s_resume - 1 (mid-tick handoff, below); everything before the substep loop has run and is in the env's state.
+DEV void sim_tick(Nin& n, Ctx& c, WarpPool& wp, bool run, int hor_input, int jump_input, int s_resume = 0) {
     bool alive = false, phys = false;
     double gx = 0, gy = 0;
     PH_BEGIN
+#if NPP_SOLO
+    if (run && s_resume > 0) { alive = true; c.wedged = 1; }       // (only a live, wedged ninja is handed over)
+    else
+#endif
     if (run) {
         c.wedged = 0;
         n.i[I_FRAME] += 1;
@@ -659,10 +682,20 @@ DEV void sim_tick(Nin& n, Ctx& c, WarpPool& wp, bool run, int hor_input, int jum
     // substeps would repeat it verbatim: they are skipped (typical: free flight, or resting after substep 2).
     bool sub = alive;
     #pragma unroll 1
-    for (int s = 0; s < 4 && NPP_BLOCK_ANY(sub); s++) {
+    for (int s = (NPP_SOLO ? s_resume : 0); s < 4 && NPP_BLOCK_ANY(sub); s++) {
         if (HAS_ANY(NPP_PHYS_MASK) && sub && phys) ninja_collide_vs_objects(n, c, gx, gy);
         bool idle = ninja_collide_vs_tiles(n, c, wp, sub);
         if (idle && !phys) sub = false;
+#if NPP_SOLO
+        // Mid-tick handoff: a substep that used all 32 iterations marks a wedged ninja; the three substeps that follow are
+        // the same 30-iteration chain again.  The home lane leaves the tick HERE -- between two substeps everything the
+        // rest of the tick reads is in the ninja record and the env's tables (nothing physical on these levels: no phys /
+        // gx / gy) -- reserves a queue entry and sits out; step_kernel stores the state and publishes (env, tick, s + 1).
+        if (!HAS_ANY(NPP_PHYS_MASK) && sub && s < 3 && c.wedged && c.hq && *reinterpret_cast<const volatile int32_t*>(c.hq) < c.hand_cap) {
+            const int slot = atomicAdd(c.hq, 1);
+            if (slot < NPPSIM_HANDOFF_CAP) { c.mid_slot = slot; c.mid_s = s + 1; sub = false; alive = false; run = false; }
+        }
+#endif
     }
     PH_MARK(4)
     NPP_BLOCK_SYNC();

@@ -4,6 +4,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 
@@ -119,6 +120,25 @@ __global__ void __launch_bounds__(128) reset_kernel(nppsim_state_t st, const uin
 
 }  // namespace
 
+// ---- SM ranks for the solo SMs of sim_variant.inc ---------------------------------------------------------
+// %smid values need not be contiguous, so each device gets a table smid -> rank among the SMs that exist (ascending: the
+// two SMs of a TPC stay neighbours), built once by a probe launch; an SM the probe never saw ranks last and is never reserved.
+#define NPP_MAX_SMID 1024
+__device__ int g_smid_rank[NPP_MAX_SMID];
+namespace {
+__global__ void smid_probe_kernel(int* seen) {
+    unsigned smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    if (threadIdx.x == 0 && smid < NPP_MAX_SMID) seen[smid] = 1;
+    const long long t0 = clock64();
+    while (clock64() - t0 < 20000) { }                  // hold the slot for ~10 us so that the grid spreads over every SM
+}
+__global__ void smid_rank_kernel(const int* seen) {
+    int r = 0;
+    for (int k = 0; k < NPP_MAX_SMID; k++) g_smid_rank[k] = seen[k] ? r++ : (1 << 30);
+}
+}  // namespace
+
 // ---- step kernel variants ------------------------------------------------------------------------------
 #ifndef STEP_BLOCK
 #define STEP_BLOCK 128
@@ -162,7 +182,11 @@ __global__ void __launch_bounds__(128) reset_kernel(nppsim_state_t st, const uin
 #undef NPP_SOLO
 #define NPP_VARIANT sim_basic_solo
 #define NPP_KINDS NPP_BASIC_MASK
+#ifdef NPP_SOLO_GROUPS
+#define NPP_GROUPS NPP_GROUPS_DEFAULT
+#else
 #define NPP_GROUPS 0
+#endif
 #define NPP_SOLO 1
 #include "sim_variant.inc"
 #undef NPP_VARIANT
@@ -189,7 +213,7 @@ __device__ __forceinline__ int sched_class(unsigned long long v, unsigned long l
     return v > 24 * mean ? 0 : (v > 12 * mean ? 1 : (v > 6 * mean ? 2 : (v > 3 * mean ? 3 : (2 * v > 3 * mean ? 4 : 5))));
 }
 __global__ void __launch_bounds__(1024) sched_kernel(int32_t* __restrict__ order, const uint32_t* __restrict__ cost, int nw, int32_t* __restrict__ handoff,
-                                                     int32_t* __restrict__ wedge_mark, int solo_limit) {
+                                                     int32_t* __restrict__ wedge_mark, int solo_limit, int solo_sm_max, int solo_sm_q8) {
     __shared__ unsigned long long s_sum;
     if (handoff) {
         // Handoff queue between two launches (sim_variant.inc): the envs the finished launch appended to `next` become the
@@ -206,7 +230,13 @@ __global__ void __launch_bounds__(1024) sched_kernel(int32_t* __restrict__ order
             if (v > 0) wedge_mark[v - 1] = tag;
         }
         __syncthreads();
-        if (threadIdx.x == 0) { handoff[0] = n_new; handoff[1] = n_new; handoff[2] = 0; handoff[5] = 0; handoff[7] = n_new; }
+        if (threadIdx.x == 0) {
+            handoff[0] = n_new; handoff[1] = n_new; handoff[2] = 0; handoff[5] = 0; handoff[7] = n_new;
+            // SMs reserved for solo blocks in the next launch: solo_sm_q8 / 256 warps per initial entry, eight warps per SM, at
+            // least one SM (the envs handed over mid-launch need a warp too)
+            handoff[8] = 0; handoff[9] = 0; handoff[11] = 0;
+            handoff[10] = solo_sm_max > 0 ? max(1, min(solo_sm_max, (n_new * solo_sm_q8 + 8 * 256 - 1) / (8 * 256))) : 0;
+        }
     }
     if (!order || !cost) return;
     __shared__ int s_cnt[SCHED_NCLS], s_pos[SCHED_NCLS];
@@ -519,6 +549,19 @@ int launch_step(const nppsim_state_t* st, const int8_t* hor, const int8_t* jump,
             if (ie == cudaSuccess) ie = cudaFuncSetAttribute(sim_basic_solo::step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
             if (ie == cudaSuccess) ie = cudaFuncSetAttribute(sim_basic_solo::step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)STEP_SMEM);
             if (ie == cudaSuccess) ie = cudaFuncSetAttribute(sim_full::step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)STEP_SMEM);
+            if (ie == cudaSuccess) {                                   // g_smid_rank of this device (solo SMs)
+                int* seen = nullptr;
+                ie = cudaMalloc(&seen, NPP_MAX_SMID * sizeof(int));
+                if (ie == cudaSuccess) ie = cudaMemset(seen, 0, NPP_MAX_SMID * sizeof(int));
+                if (ie == cudaSuccess) {
+                    int n_sm = 148;
+                    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+                    smid_probe_kernel<<<n_sm * 16, 128>>>(seen);
+                    smid_rank_kernel<<<1, 1>>>(seen);
+                    ie = cudaDeviceSynchronize();
+                }
+                if (seen) cudaFree(seen);
+            }
             if (ie == cudaSuccess && dev >= 0 && dev < 64) init_done[dev] = true;
         }
         if (ie != cudaSuccess) return cuda_fail(ie, "step kernel attributes");
@@ -533,18 +576,29 @@ int launch_step(const nppsim_state_t* st, const int8_t* hor, const int8_t* jump,
     // kind_mask == 0: census unknown (older callers) -> the full kernel.  Solo warps exist in the basic kernel only.
     const bool basic = st->kind_mask != 0 && (st->kind_mask & ~NPP_BASIC_MASK) == 0;
     int32_t* const handoff = basic ? st->handoff : nullptr;
-    const int n_solo = handoff ? std::min(sms / 2, std::max(2, st->n_envs / 512)) : 0;
+    const int n_regular = (st->n_envs + block - 1) / block;
+    // Solo SMs (sim_variant.inc): from one full wave of blocks up, solo blocks are dealt by SM -- up to solo_sm_max SMs run
+    // nothing but solo warps for the launch (sched_kernel sizes the reservation from the queue) -- and only two front blocks
+    // remain as the guaranteed servers; the grid holds a block for every slot of every SM that may be reserved.  Smaller
+    // launches keep solo blocks at the front of the grid.  NPPSIM_SOLO_SM=0|1|2 / NPPSIM_SOLO_SM_MAX / NPPSIM_SOLO_SM_Q8: A/B knobs.
+    // (read per launch: the parity tests switch them; 2 = solo SMs at any grid size)
+    const char* const ev_sm = getenv("NPPSIM_SOLO_SM"); const char* const ev_max = getenv("NPPSIM_SOLO_SM_MAX"); const char* const ev_q8 = getenv("NPPSIM_SOLO_SM_Q8");
+    const int env_sm = ev_sm ? atoi(ev_sm) : 1, env_sm_max = ev_max ? atoi(ev_max) : 0, env_sm_q8 = ev_q8 ? atoi(ev_q8) : 256;
+    const bool sm_solo = handoff && env_sm && (n_regular >= 2 * sms || env_sm == 2);
+    const int solo_sm_max = sm_solo ? (env_sm_max > 0 ? std::min(env_sm_max, sms / 4) : sms / 8) : 0;
+    const int n_solo = !handoff ? 0 : (sm_solo ? 2 : std::min(sms / 2, std::max(2, st->n_envs / 512)));
     const int solo_limit = std::min(stay_cap, std::max(64, st->n_envs / 384));      // envs per launch that start on solo warps; as many again may follow mid-launch
-    const int grid = (st->n_envs + block - 1) / block + n_solo;
+    const int grid = n_regular + n_solo + 2 * solo_sm_max;
     auto kernel = basic ? (handoff ? sim_basic_solo::step_kernel : sim_basic::step_kernel) : sim_full::step_kernel;
-    kernel<<<grid, block, STEP_SMEM, (cudaStream_t)stream>>>(*st, hor, jump, actions, input_ticks, n_ticks, tick_limit, stop_on_terminal, frames_executed, sp, n_solo, 2 * solo_limit);
+    kernel<<<grid, block, STEP_SMEM, (cudaStream_t)stream>>>(*st, hor, jump, actions, input_ticks, n_ticks, tick_limit, stop_on_terminal, frames_executed, sp, n_solo, 2 * solo_limit,
+                                                               n_regular, sm_solo ? 1 : 0);
     g_launches++;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_fail(e, "step_kernel launch");
     if ((st->warp_order && st->warp_cost) || handoff) {
         const size_t S = st->stride ? (size_t)st->stride : (size_t)st->n_envs;
         sched_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(st->warp_cost ? st->warp_order : nullptr, st->warp_cost, (st->n_envs + 31) / 32, handoff,
-                                                           st->env_i + (size_t)NPPSIM_ENV_WEDGE * S, solo_limit);
+                                                           st->env_i + (size_t)NPPSIM_ENV_WEDGE * S, solo_limit, solo_sm_max, env_sm_q8);
         g_launches++;
         e = cudaGetLastError();
         if (e != cudaSuccess) return cuda_fail(e, "sched_kernel launch");
@@ -575,7 +629,7 @@ int nppsim_debug_solo_log(unsigned long long* out, int max_rows, int reset) {   
     cudaDeviceSynchronize();
     unsigned int n = 0;
     cudaMemcpyFromSymbol(&n, g_solo_n, sizeof(n));
-    if (out) cudaMemcpyFromSymbol(out, g_solo_log, sizeof(unsigned long long) * 4 * (size_t)std::min<unsigned>(std::min<unsigned>(n, 8192u), (unsigned)max_rows));
+    if (out) cudaMemcpyFromSymbol(out, g_solo_log, sizeof(unsigned long long) * 12 * (size_t)std::min<unsigned>(std::min<unsigned>(n, 8192u), (unsigned)max_rows));
     if (reset) { unsigned int z = 0; cudaMemcpyToSymbol(g_solo_n, &z, sizeof(z)); }
     return (int)n;
 }

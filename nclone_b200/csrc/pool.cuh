@@ -19,7 +19,7 @@ __device__ unsigned long long g_warp_cycles[1 << 16];      // per warp: kernel d
 __device__ unsigned long long g_warp_span[1 << 16][2];    // per warp: %globaltimer (ns) at start / end of the last launch
 DEV unsigned long long global_ns() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 __device__ unsigned long long g_warp_phase[1 << 16][4];   // per warp: cycles in entities / sweep / closest / post of the last launch
-__device__ unsigned long long g_solo_log[8192][4];        // per env served by a solo warp: env | t_first << 24 | converted << 28 | initial << 29, ns at pickup, at end, at publication (b)
+__device__ unsigned long long g_solo_log[8192][12];        // per env served by a solo warp: env | t_first << 24 | converted << 28 | initial << 29, ns at pickup, at end, at publication (b), cooperative iterations, %smid, cycles in entities / sweep / closest-point loop / post_collision
 __device__ unsigned int g_solo_n;
 __device__ unsigned long long g_hand_pub[1 << 12];        // per entry of (b): ns at publication
 __device__ unsigned long long g_coop_cycles[8];        // cooperative depenetration loop: [0] evaluate, [1] select, [2] push, [3] iterations, [4] services, [5] park/take/back
@@ -28,7 +28,7 @@ __device__ unsigned long long g_coop_cycles[8];        // cooperative depenetrat
 #define PH_T0 long long _q0 = clock64();
 #define PH_ACC(k) { long long _q1 = clock64(); if ((threadIdx.x & 31) == 0) atomicAdd(&g_phase_cycles[k], (unsigned long long)(_q1 - _q0)); _q0 = _q1; }
 #define PH_BEGIN long long _ph_t = clock64();
-#define PH_MARK(k) { long long _t2 = clock64(); if ((threadIdx.x & 31) == (__ffs(__activemask()) - 1)) { atomicAdd(&g_phase_cycles[k], (unsigned long long)(_t2 - _ph_t)); int _w = wp.group; int _b = (k) <= 3 ? 0 : ((k) == 5 ? 1 : ((k) == 6 ? 2 : (((k) == 9 || (k) == 10) ? 3 : -1))); if (_b >= 0 && _w >= 0 && _w < (1 << 16)) g_warp_phase[_w][_b] += (unsigned long long)(_t2 - _ph_t); } _ph_t = _t2; }
+#define PH_MARK(k) { long long _t2 = clock64(); if ((threadIdx.x & 31) == (__ffs(__activemask()) - 1)) { atomicAdd(&g_phase_cycles[k], (unsigned long long)(_t2 - _ph_t)); int _w = wp.group; int _b = (k) <= 3 ? 0 : ((k) == 5 ? 1 : ((k) == 6 ? 2 : (((k) == 9 || (k) == 10) ? 3 : -1))); if (_b >= 0 && _w >= 0 && _w < (1 << 16)) g_warp_phase[_w][_b] += (unsigned long long)(_t2 - _ph_t); if (_b >= 0 && _w < 0) wp.sph[_b] += (unsigned long long)(_t2 - _ph_t); } _ph_t = _t2; }
 #else
 #define PH_BEGIN
 #define PH_MARK(k)
@@ -67,6 +67,9 @@ struct WarpPool {
     uint32_t lseg[32][POOL_LCAP];   // per-lane copy of the segments gathered for the current substep (ninja.py:282-285)
     int coop;                       // cooperative depenetration iterations this launch: the warp's cost for longest-first scheduling
     int group;                      // the env group this warp works on (profile build: per-warp phase attribution)
+#ifdef NPP_PROFILE
+    unsigned long long sph[6];      // solo warps: cycles per phase group (entities / sweep / closest-point loop / post_collision)
+#endif
 };
 
 // ---- gather: the segments of a query box, per lane, in SpatialSegmentIndex.query_region order -----------

@@ -379,14 +379,18 @@ def test_wedged_ninja_cooperative_loop_vs_oracle():
     assert most >= 1000, most      # several envs of the warp wedged in the same agent step (>= 354 iterations each)
 
 
-def test_wedged_ninja_handoff_to_solo_warps_vs_oracle():
+@pytest.mark.parametrize("solo_sm", ["1", "2"])
+def test_wedged_ninja_handoff_to_solo_warps_vs_oracle(solo_sm, monkeypatch):
     """In-launch handoff (nppsim_state_t.handoff, csrc/sim_variant.inc): a wedged env leaves its home lane at the end of its
     first wedged tick and finishes the agent step on a solo warp; envs wedged when the previous launch ended start there.
     Same scenario as above with the queue switched on (it is on by default from 1,024 envs): full ninja record and
     frames_executed against the oracle after every agent step, handoffs must have happened, no solo warp may have timed out.
-    Second half: per-tick input rows and per-env action streams (the two other input forms) through the handoff."""
+    Second half: per-tick input rows and per-env action streams (the two other input forms) through the handoff.
+    solo_sm = "2": the same with the solo blocks dealt by SM (whole SMs reserved for solo warps, regular blocks taking their envs
+    from a counter) -- what launches of a full wave and more do by themselves -- forced onto this small grid."""
     import torch
     from nclone_b200 import BatchedSimulator, ACTION_TO_INPUTS
+    monkeypatch.setenv("NPPSIM_SOLO_SM", solo_sm)
     d = np.load(os.path.join(ROOT, "bench_data", "wedges.npz"))
     K = len(d["lens"])
     maps = [d["maps"][k, :d["lens"][k]] for k in range(K)]
@@ -430,6 +434,7 @@ def test_wedged_ninja_handoff_to_solo_warps_vs_oracle():
         assert sim.handoff_status() == 0
         assert sim.handoff_count() >= 18, sim.handoff_count()      # mid-launch handoffs: one per wedge episode of 36 envs
         assert seen_queue > 0                                       # and envs started launches on solo warps
+        assert (sim.solo_sms() >= 1) == (solo_sm == "2")
 
 
 def test_basic_variant_vs_oracle_and_full_kernel():

@@ -58,7 +58,7 @@ e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=Tr
 lib_.nppsim_debug_solo_log.argtypes = [C.c_void_p, C.c_int, C.c_int]
 lib_.nppsim_debug_solo_log(None, 0, 1)
 e0.record(); sim.step(acts[7], 4, True); e1.record(); torch.cuda.synchronize()
-solo_log = np.zeros((8192, 4), dtype=np.uint64)
+solo_log = np.zeros((8192, 12), dtype=np.uint64)
 n_solo_log = min(8192, lib_.nppsim_debug_solo_log(solo_log.ctypes.data, 8192, 0))
 lib_.nppsim_debug_warp_cycles(wc.ctypes.data, ph.ctypes.data, nw, 0)
 d = (ph - ph0).astype(np.float64); w = wc.astype(np.float64)
@@ -110,6 +110,12 @@ if n_solo_log:
         print(f"  (b) published at us: p10 {np.nanpercentile(pub[b], 10):.1f} p50 {np.nanpercentile(pub[b], 50):.1f} p90 {np.nanpercentile(pub[b], 90):.1f} max {np.nanmax(pub[b]):.1f}; "
               f"wait for a warp us: mean {np.nanmean((pick - pub)[b]):.1f} max {np.nanmax((pick - pub)[b]):.1f}; service us: mean {np.mean((end - pick)[b]):.1f} max {np.max((end - pick)[b]):.1f}")
         print("  (b) first tick handed over: " + ", ".join(f"t={k}: {int((tf[b] == k).sum())}" for k in range(1, 4)))
-    print("  last solo services: (column, kind, first tick, published us, picked up us, ended us)")
-    for o in np.argsort(-end)[:16]:
-        print(f"    {env[o]:7d} {'a' if init[o] else ('b/conv' if conv[o] else 'b'):7s} {tf[o]:2d} {pub[o]:9.1f} {pick[o]:9.1f} {end[o]:9.1f}")
+    its = lg[:, 4].astype(np.int64); smid = lg[:, 5].astype(np.int64)
+    long_ = its >= 300
+    if long_.any():
+        cyc = (end - pick)[long_] * 1965.0 / its[long_]
+        print(f"  services of >= 300 cooperative iterations: {int(long_.sum())}; cycles per iteration (whole service / iterations): mean {cyc.mean():.0f} min {cyc.min():.0f} max {cyc.max():.0f}")
+    print(f"  SMs that ran solo services: {len(np.unique(smid))} ({np.unique(smid)[:40].tolist()})")
+    print("  last solo services: (column, kind, first tick, published us, picked up us, ended us, cooperative iterations, smid, us in entities / sweep / closest-point loop / post_collision)")
+    for o in np.argsort(-end)[:24]:
+        print(f"    {env[o]:7d} {'a' if init[o] else ('b/conv' if conv[o] else 'b'):7s} {tf[o]:2d} {pub[o]:9.1f} {pick[o]:9.1f} {end[o]:9.1f} {its[o]:6d} {smid[o]:4d}   phases us {np.round(lg[o, 6:10].astype(np.float64) / 1965.0, 1).tolist()} in-loop cycles/iteration {lg[o, 10] / max(its[o], 1):.0f} park/take us {lg[o, 11] / 1965.0:.1f}")

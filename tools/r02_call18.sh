@@ -1,0 +1,27 @@
+#!/bin/bash
+# round 2, GPU call 18: solo SMs (whole SMs reserved for solo warps, regular blocks dealt from a counter) vs solo blocks at the front of the grid
+mkdir -p gpurun_out/r02r
+O=gpurun_out/r02r
+summ() { python -c "
+import sys, json
+l = json.loads(sys.stdin.read().strip().split('\n')[-1])
+print('$1', 'value %.1fM e2e %.1fM step_kernel %.3f ms reset %.3f ms' % (l['value'] / 1e6, l['e2e']['value'] / 1e6, l['kernel_ms']['step_kernel'], l['kernel_ms']['reset_kernel']), l.get('kernel'), l.get('handoff'))"; }
+echo "== parity (handoff paths + full size)"
+timeout 1500 python -m pytest tests/test_gpu_parity.py -x -q -m gpu -k "handoff or full_size or cooperative or soak" > $O/parity.log 2>&1; tail -3 $O/parity.log
+run() {  # name workload envs handoff [env...]
+  local name=$1 w=$2 n=$3 h=$4; shift 4
+  env "$@" timeout 300 python bench.py --workload $w --envs $n --handoff $h --steps 100 --warmup 10 --no-cpu-baseline --no-secondary --async-groups 0 2>$O/err_$name.log | tail -1 > $O/bench_$name.json
+  summ "$name" < $O/bench_$name.json
+}
+run c3_65k_front   c3 65536 on NPPSIM_SOLO_SM=0
+run c3_65k_sm      c3 65536 on NPPSIM_SOLO_SM=1
+run c3_65k_sm_q384 c3 65536 on NPPSIM_SOLO_SM=1 NPPSIM_SOLO_SM_Q8=384
+run c3_65k_sm_q128 c3 65536 on NPPSIM_SOLO_SM=1 NPPSIM_SOLO_SM_Q8=128
+run c3_65k_sm_max8 c3 65536 on NPPSIM_SOLO_SM=1 NPPSIM_SOLO_SM_MAX=8
+run c3_65k_off     c3 65536 off NPPSIM_SOLO_SM=0
+run c3_131k_front  c3 131072 on NPPSIM_SOLO_SM=0
+run c3_131k_sm     c3 131072 on NPPSIM_SOLO_SM=1
+run c3_131k_sm_q128 c3 131072 on NPPSIM_SOLO_SM=1 NPPSIM_SOLO_SM_Q8=128
+run c3_131k_off    c3 131072 off NPPSIM_SOLO_SM=0
+run c4_131k_sm     c4 131072 on NPPSIM_SOLO_SM=1 NPPSIM_SOLO_SM_MAX=36
+run c4_131k_off    c4 131072 off NPPSIM_SOLO_SM=0

