@@ -289,7 +289,8 @@ def measure(workload, n_envs, args, rank, world, dev, dist, steps, warmup, sprea
     out["elapsed_ms"] = float(step_ms.sum() + reset_ms.sum())
     out["ticks"] = sim.total_ticks() - ticks0
     out["handoff"] = {"enabled": sim.handoff is not None, "mid_launch_per_step": (sim.handoff_count() - handoffs0) / steps,
-                      "solo_start_queue": sim.solo_queue_length(), "solo_sms": sim.solo_sms(), "status": sim.handoff_status()}
+                      "solo_start_queue": sim.solo_queue_length(), "solo_sms": sim.solo_sms(), "status": sim.handoff_status(),
+                      "policy": args.handoff, "saturated_launches": list(sim.handoff_saturation())}
     out["engine_order"] = "envs of a level in consecutive state columns" if sim.slot_env is not None else "caller's order"
 
     # ---- e2e: host buffers through the C ABI, copies inside the timed region -------------------------

@@ -101,7 +101,10 @@ typedef struct {
                                        bits, [4] mid-launch handoffs so far (both sticky); [5] length of the next launch's list;
                                        [6] tag (caller); [7] initial entries of the current launch; [8] regular block slots claimed,
                                        [9] initial entries claimed, [10] SMs reserved for solo blocks, [11] blocks that went solo on
-                                       such an SM (all four per launch; "solo SMs", csrc/sim_variant.inc); [12..15] reserved */
+                                       such an SM (all four per launch; "solo SMs", csrc/sim_variant.inc); [12] launches after which more envs
+                                       asked for a solo start than the queue admits, [13] launches (both sticky: when [12] / [13] is
+                                       large the wedged envs are the bulk of the work, not its tail, and the caller should step
+                                       without a queue); [14..15] reserved */
 #define NPPSIM_HANDOFF_WORDS (NPPSIM_HANDOFF_HDR + 2 * NPPSIM_HANDOFF_CAP)
 
 /* Per-env input streams for nppsim_step_stream: env i owns data[offset[i] .. offset[i+1]) -- ragged, no padding. */

@@ -192,7 +192,9 @@ class BatchedSimulator:
         st.kind_mask = self.kind_mask
         # solo warps exist in the basic kernel only (csrc/nppsim_kernels.cu: NPP_SOLO)
         self.handoff = self._new_handoff() if (self.use_handoff and self._is_basic(self.kind_mask)) else None
+        self._retired_handoff = None
         st.handoff = self.handoff.data_ptr() if self.handoff is not None else None
+        self._adapt_calls, self._adapt_pending, self._adapt_seen, self._adapt_buf = 0, None, (0, 0), None
         self._state = st
 
     # ------------------------------------------------------------------ sub-batches for asynchronous stepping
@@ -219,6 +221,7 @@ class BatchedSimulator:
         v.__dict__.update(self.__dict__)
         v.n_envs = e - b
         v._exit_cache = None
+        v._adapt_calls, v._adapt_pending, v._adapt_seen, v._adapt_buf, v._retired_handoff = 0, None, (0, 0), None, None      # (_adapt_handoff: per queue)
         # a view is a range of state COLUMNS; its own env numbering is the column order (no permutation inside a view)
         for name in ("_nin_f", "_nin_i", "_env_i", "_ent_flag", "_dyn_f", "_dyn_i"):
             setattr(v, name, getattr(self, name)[:, b:e])
@@ -248,11 +251,45 @@ class BatchedSimulator:
         return v
 
     def _auto_handoff(self, n_envs):
-        """Solo-warp handoff of wedged envs pays while the launch is bound by its longest dependent chain -- up to two waves of
-        resident warps (8 per SM at 255 registers) -- and costs a few per cent once the launch is throughput bound (measured:
-        65,536 envs +7 %, 131,072 envs -3 ... -20 %; profiles/r02_handoff_ab.md)."""
-        sms = torch.cuda.get_device_properties(self.device).multi_processor_count
-        return 1024 <= n_envs and (n_envs + 31) // 32 <= 2 * 8 * sms
+        """Solo-warp handoff of wedged envs (solo SMs, mid-tick handoff) is on from 1,024 envs: it pays wherever the wedged
+        ninjas are the tail of a launch (config 3: 65,536 envs +8 %, 131,072 +10 %) and loses where they are the bulk of the
+        work (config 4's locked-door levels -20 %, config 3 at 262,144 envs -11 %: one warp per env takes the slots the
+        regular warps need).  That is a property of the levels, not of the batch size, so the engine measures it: sched_kernel
+        counts the launches whose wedged envs overflowed the queue, and _adapt_handoff drops the queue when most do
+        (profiles/r02_handoff_ab.md section 11)."""
+        return 1024 <= n_envs
+
+    def _adapt_handoff(self):
+        """Called after every step: every 16th launch, read the queue's saturation counters (asynchronously -- the copy is
+        looked at once its event has completed) and, under the automatic policy, stop using the queue when more than half of
+        the launches overflowed it.  The kernels without a queue run every env in its home lane; results are identical."""
+        if self.handoff is None or self._handoff_arg is not None:
+            return
+        self._adapt_calls = getattr(self, "_adapt_calls", 0) + 1
+        pending = getattr(self, "_adapt_pending", None)
+        if pending is not None:
+            ev, buf = pending
+            if not ev.query():
+                return
+            self._adapt_pending = None
+            clipped, total = int(buf[0]), int(buf[1])
+            seen = getattr(self, "_adapt_seen", (0, 0))
+            if total - seen[1] >= 16:
+                self._adapt_seen = (clipped, total)
+                if 2 * (clipped - seen[0]) > total - seen[1]:
+                    self._retired_handoff = self.handoff          # (launches in flight still read it)
+                    self.handoff = None
+                    self._state.handoff = None
+            return
+        if self._adapt_calls % 16 == 0:
+            buf = getattr(self, "_adapt_buf", None)
+            if buf is None:
+                buf = self._adapt_buf = torch.zeros(2, dtype=torch.int32).pin_memory()
+            with torch.cuda.device(self.device):
+                buf.copy_(self.handoff[12:14], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record()
+            self._adapt_pending = (ev, buf)
 
     _handoff_tags = 0
 
@@ -382,6 +419,7 @@ class BatchedSimulator:
             check(self.L.nppsim_step_actions(C.byref(self._state), C.c_void_p(a.data_ptr()), int(frame_skip),
                                              int(bool(stop_on_terminal)), C.c_void_p(self._frames_executed.data_ptr()),
                                              self._stream()))
+        self._adapt_handoff()
         return self.frames_executed
 
     # ------------------------------------------------------------------ per-env input streams
@@ -460,6 +498,7 @@ class BatchedSimulator:
             check(self.L.nppsim_step_host(C.byref(self._state), C.c_void_p(a.ctypes.data), C.c_void_p(self._actions_dev.data_ptr()),
                                           int(frame_skip), int(bool(stop_on_terminal)), C.c_void_p(stg),
                                           C.c_void_p(block.data_ptr()), int(bool(with_obs)), self._stream()))
+        self._adapt_handoff()
 
     # ------------------------------------------------------------------ NPlayHeadless getters, batched
     def _f(self, name):
@@ -608,13 +647,19 @@ class BatchedSimulator:
             out.append((nf[k], ni[k]) + _entity_rows(t, fl[:, k], df[:, k], di[:, k], int(order[k])))
         return out
 
+    def _queue(self):
+        """The handoff queue in use, else the one the automatic policy retired (its counters stay readable)."""
+        return self.handoff if self.handoff is not None else getattr(self, "_retired_handoff", None)
+
     def handoff_status(self):
         """Sticky error bits of the handoff queue (0 = fine; 1 = a solo warp gave up waiting)."""
-        return 0 if self.handoff is None else int(self.handoff[3].item())
+        q = self._queue()
+        return 0 if q is None else int(q[3].item())
 
     def handoff_count(self):
         """Envs that left their home lane for a solo warp in the middle of a launch since load_maps (0 without a queue)."""
-        return 0 if self.handoff is None else int(self.handoff[4].item())
+        q = self._queue()
+        return 0 if q is None else int(q[4].item())
 
     def solo_queue_length(self):
         """Envs that will start the next launch on a solo warp (their last tick was wedged)."""
@@ -623,6 +668,11 @@ class BatchedSimulator:
     def solo_sms(self):
         """SMs reserved for solo blocks in the next launch (0: solo blocks sit at the front of the grid; include/nppsim.h, word 10)."""
         return 0 if self.handoff is None else int(self.handoff[10].item())
+
+    def handoff_saturation(self):
+        """(launches after which the wedged envs overflowed the queue, launches) -- what _adapt_handoff decides on."""
+        q = self._queue()
+        return (0, 0) if q is None else (int(q[12].item()), int(q[13].item()))
 
     def launch_count(self):
         return int(self.L.nppsim_launch_count())

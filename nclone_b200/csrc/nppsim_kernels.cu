@@ -231,6 +231,9 @@ __global__ void __launch_bounds__(1024) sched_kernel(int32_t* __restrict__ order
         }
         __syncthreads();
         if (threadIdx.x == 0) {
+            // saturation counters for the caller's policy: launches whose wedged envs did not all fit the queue / launches
+            if (handoff[5] > solo_limit) handoff[12]++;
+            handoff[13]++;
             handoff[0] = n_new; handoff[1] = n_new; handoff[2] = 0; handoff[5] = 0; handoff[7] = n_new;
             // SMs reserved for solo blocks in the next launch: solo_sm_q8 / 256 warps per initial entry, eight warps per SM, at
             // least one SM (the envs handed over mid-launch need a warp too)

@@ -437,6 +437,44 @@ def test_wedged_ninja_handoff_to_solo_warps_vs_oracle(solo_sm, monkeypatch):
         assert (sim.solo_sms() >= 1) == (solo_sm == "2")
 
 
+def test_automatic_handoff_policy_drops_a_saturated_queue():
+    """BatchedSimulator's default policy (handoff=None): the queue is on from 1,024 envs and is dropped once most launches
+    overflow it -- wedged ninjas are then the bulk of the work, not its tail (sched_kernel's counters, words 12 / 13 of the
+    queue; BatchedSimulator._adapt_handoff).  1,200 envs on the three wedge levels, every replica driven into its corner and
+    held there: the policy must switch kernels mid-run, and the state must stay bit-identical to a batch stepped without a
+    queue from the start (which the tests above pin to the oracle)."""
+    import torch
+    from nclone_b200 import BatchedSimulator
+    d = np.load(os.path.join(ROOT, "bench_data", "wedges.npz"))
+    K = len(d["lens"])
+    maps = [d["maps"][k, :d["lens"][k]] for k in range(K)]
+    pre = [d["acts"][d["act_off"][k]:d["act_off"][k + 1]] for k in range(K)]
+    env_to_map = np.repeat(np.arange(K), 400)
+    N = len(env_to_map)
+    steps = max(len(p) for p in pre) + 72
+    actions = np.zeros((steps, N), dtype=np.uint8)
+    for e in range(N):
+        p = pre[env_to_map[e]]
+        actions[:len(p), e] = p
+        actions[len(p):, e] = p[-1]                      # keep pushing into the corner
+    auto = BatchedSimulator(N); auto.load_maps(maps, env_to_map)
+    plain = BatchedSimulator(N, handoff=False); plain.load_maps(maps, env_to_map)
+    assert auto.handoff is not None and auto.kernel_variant() == "sim_basic_solo"
+    for st in range(steps):
+        a = torch.from_numpy(actions[st]).cuda()
+        fa = auto.step(a, 4, True); fp = plain.step(a, 4, True)
+        if st % 8 == 7 or st == steps - 1:
+            torch.cuda.synchronize()
+            assert torch.equal(fa, fp), st
+            for x, y in ((auto.nin_f.view(torch.int64), plain.nin_f.view(torch.int64)), (auto.nin_i, plain.nin_i), (auto.ent_flag, plain.ent_flag)):
+                assert torch.equal(x, y), st
+        auto.reset_terminal(2000); plain.reset_terminal(2000)
+    clipped, launches = auto.handoff_saturation()
+    assert launches >= 32 and clipped >= 16, (clipped, launches)
+    assert auto.handoff is None and auto.kernel_variant() == "sim_basic", auto.handoff_saturation()
+    assert auto.handoff_status() == 0
+
+
 def test_basic_variant_vs_oracle_and_full_kernel():
     """Level sets without moving / pushing entities run on the specialised `sim_basic` kernel
     (nppsim_state_t.kind_mask).  (1) 1,280 envs of the benchmark levels against the oracle;
@@ -694,7 +732,9 @@ def test_full_size_replica_consistency_and_oracle_sample():
     # replica r of level m lives at env (m * 7 + r * 4099) % N-ish: a permutation that spreads replicas over warps and lanes
     perm = (np.arange(N, dtype=np.int64) * 40503) % N          # 40503 is odd, N a power of two: a bijection
     env_to_map = np.empty(N, dtype=np.int64); env_to_map[perm] = np.arange(N) % M
-    sim = BatchedSimulator(N, placement="level")              # the permuted layout at full size (the default here would be the caller's order: 16 replicas per level)
+    # the permuted layout at full size (the default here would be the caller's order: 16 replicas per level); the queue pinned
+    # on: all 16 replicas of a level wedge together here, which the automatic policy would (rightly) answer by dropping it
+    sim = BatchedSimulator(N, placement="level", handoff=True)
     sim.load_maps(maps, env_to_map)
     rng = np.random.default_rng(3)
     steps = 60
