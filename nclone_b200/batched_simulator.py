@@ -262,7 +262,7 @@ class BatchedSimulator:
     def _adapt_handoff(self):
         """Called after every step: every 16th launch, read the queue's saturation counters (asynchronously -- the copy is
         looked at once its event has completed) and, under the automatic policy, stop using the queue when more than half of
-        the launches overflowed it.  The kernels without a queue run every env in its home lane; results are identical."""
+        the launches overflowed it, or when no env has used it in 256 launches.  The kernels without a queue run every env in its home lane; results are identical."""
         if self.handoff is None or self._handoff_arg is not None:
             return
         self._adapt_calls = getattr(self, "_adapt_calls", 0) + 1
@@ -272,21 +272,27 @@ class BatchedSimulator:
             if not ev.query():
                 return
             self._adapt_pending = None
-            clipped, total = int(buf[0]), int(buf[1])
+            used, clipped, total = int(buf[0]) + int(buf[3]), int(buf[8]), int(buf[9])      # words 4 + 7 | 12 | 13
             seen = getattr(self, "_adapt_seen", (0, 0))
+            drop = False
             if total - seen[1] >= 16:
                 self._adapt_seen = (clipped, total)
-                if 2 * (clipped - seen[0]) > total - seen[1]:
-                    self._retired_handoff = self.handoff          # (launches in flight still read it)
-                    self.handoff = None
-                    self._state.handoff = None
+                drop = 2 * (clipped - seen[0]) > total - seen[1]
+            # and a queue no env has ever used after 256 launches (levels without corners to wedge into, e.g. config 2's
+            # single level) only costs the solo kernel's 3-6 % over the plain one
+            if not drop and total >= 256 and used == 0:
+                drop = True
+            if drop:
+                self._retired_handoff = self.handoff              # (launches in flight still read it)
+                self.handoff = None
+                self._state.handoff = None
             return
         if self._adapt_calls % 16 == 0:
             buf = getattr(self, "_adapt_buf", None)
             if buf is None:
-                buf = self._adapt_buf = torch.zeros(2, dtype=torch.int32).pin_memory()
+                buf = self._adapt_buf = torch.zeros(10, dtype=torch.int32).pin_memory()
             with torch.cuda.device(self.device):
-                buf.copy_(self.handoff[12:14], non_blocking=True)
+                buf.copy_(self.handoff[4:14], non_blocking=True)
                 ev = torch.cuda.Event()
                 ev.record()
             self._adapt_pending = (ev, buf)

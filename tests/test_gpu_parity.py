@@ -220,10 +220,17 @@ def test_step_host_matches_device_path(golden_replays, golden_generated):
     assert s1.slot_env is not None and s3.slot_env is None and np.array_equal(s1.env_map_host, e2m)
     block, v = s2.host_block(with_obs=True)
     block3, v3 = s3.host_block(with_obs=False)
+    # pinned blocks are written by the step kernel itself (zero-copy stores as each env finishes); a pageable block takes the
+    # staged path (pack kernel + one copy): both must deliver the same bytes
+    s4 = BatchedSimulator(N); s4.load_maps(maps, e2m)
+    block4 = torch.zeros(block.numel(), dtype=torch.uint8)
+    assert block.is_pinned() and not block4.is_pinned()
     for k in range(20):
         s1.step(torch.from_numpy(a[k]).cuda(), 4, True)
         s2.step_host(a[k], block, 4, True, with_obs=True)
         s3.step_host(a[k], block3, 4, True)
+        s4.step_host(a[k], block4, 4, True, with_obs=True)
+        assert np.array_equal(block4.numpy(), block.numpy()), k
     assert np.array_equal(s1.nin_f[:4].cpu().numpy().view(np.int64), v["pos_vel"].view(np.int64))
     assert np.array_equal(s1.nin_i[0].cpu().numpy(), v["state"])
     assert np.array_equal(v3["pos_vel"].view(np.int64), v["pos_vel"].view(np.int64)) and np.array_equal(v3["state"], v["state"])
