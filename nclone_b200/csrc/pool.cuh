@@ -19,7 +19,7 @@ __device__ unsigned long long g_warp_cycles[1 << 16];      // per warp: kernel d
 __device__ unsigned long long g_warp_span[1 << 16][2];    // per warp: %globaltimer (ns) at start / end of the last launch
 DEV unsigned long long global_ns() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 __device__ unsigned long long g_warp_phase[1 << 16][4];   // per warp: cycles in entities / sweep / closest / post of the last launch
-__device__ unsigned long long g_solo_log[8192][12];        // per env served by a solo warp: env | t_first << 24 | converted << 28 | initial << 29, ns at pickup, at end, at publication (b), cooperative iterations, %smid, cycles in entities / sweep / closest-point loop / post_collision
+__device__ unsigned long long g_solo_log[8192][12];        // per env served by a solo warp: env | t_first << 24 | converted << 32 | initial << 33 | resume substep << 34, ns at pickup, at end, at publication (b), cooperative iterations, %smid, cycles in entities / sweep / closest-point loop / post_collision
 __device__ unsigned int g_solo_n;
 __device__ unsigned long long g_hand_pub[1 << 12];        // per entry of (b): ns at publication
 __device__ unsigned long long g_coop_cycles[8];        // cooperative depenetration loop: [0] evaluate, [1] select, [2] push, [3] iterations, [4] services, [5] park/take/back
@@ -376,6 +376,54 @@ DEV bool closest_eval(const SegC& g, double x, double y, double& d2, double& a, 
     if (!back) d2 -= 0.1;
     r = back ? -1 : 1;
     return true;
+}
+// The closest point alone -- closest_eval's first half, same expressions -- for the speculative chain of the batched
+// cooperative loop (ninja.cuh): the push needs (a, b, side), not the distance.  Returns the bounds test.
+DEV bool closest_ab(const SegC& g, double x, double y, double& a, double& b, bool& back) {
+    const bool inb = !(g.bx1 < x - NINJA_RADIUS || g.bx0 > x + NINJA_RADIUS || g.by1 < y - NINJA_RADIUS || g.by0 > y + NINJA_RADIUS);
+    const double dx = x - g.x1, dy = y - g.y1;
+    if (!g.arc) {                                                            // entities.py:43-59
+        double u = div_seglen(dx * g.px + dy * g.py, g.lensq);
+        if (0 > u) u = 0;
+        if (1 < u) u = 1;
+        a = g.x1 + u * g.px; b = g.y1 + u * g.py;
+        back = (dy * g.px - dx * g.py < 0);
+    } else {                                                                 // entities.py:127-157
+        back = false;
+        if (dx * g.px > 0 && dy * g.py > 0) {
+            double dist = SQRT(SQ(dx) + SQ(dy));
+            double qa, qb;
+            div2(24.0 * dx, 24.0 * dy, dist, qa, qb);
+            a = g.x1 + qa; b = g.y1 + qb;
+            back = (g.lensq != 0) ? (dist < 24.0) : (dist > 24.0);
+        } else if (dx * g.px > dy * g.py) { a = g.x1 + 24.0 * g.px; b = g.y1; }
+        else { a = g.x1; b = g.y1 + 24.0 * g.py; }
+    }
+    return inb;
+}
+// Decoded segments of the served owner's list in shared memory (the first 16 entries; rows of 16 in the idle part of
+// wp.rb): the batched loop evaluates the PREDICTED segment on every lane, and its verification pass gives lane l segment
+// l % 8 (lists of up to 8: four iterations per batch) or l % 16 (up to 16: two).
+// Measured (tools/r02_call34.sh, profiles/r02_handoff_ab.md section 15): every batch verified (0 failures on the three wedge
+// fixtures), yet a batch costs what it saves -- lists of up to 8 (four iterations per batch) 1,273 against 1,372 cycles per
+// iteration on the line wedge, lists of 9-16 (two per batch) 2,217 against 2,101 (arc) and 1,532 against 1,380 (lines);
+// config 3 at 65,536 envs 358 against 377 M.  The predicted path had taken the selection off the chain already; what the
+// batch removes (the other lanes' evaluations) is less than its table reads, snapshot and verification pass.  Off.
+#ifndef NPP_COOP_BATCH
+#define NPP_COOP_BATCH 0
+#endif
+#define COOP_TAB 32                     // wp.rb[32 .. 192): 10 rows x 16 segments
+#define COOP_POS 192                    // wp.rb[192 .. 200): positions of the batch's iterations, x then y
+#define COOP_SNAP 200                   // wp.rb[200 .. 212): the state before the batch
+DEV void seg_tab_put(WarpPool& wp, int j, const SegC& g) {
+    double* t = wp.rb + COOP_TAB + j;
+    t[0] = g.bx0; t[16] = g.by0; t[32] = g.bx1; t[48] = g.by1; t[64] = g.x1; t[80] = g.y1; t[96] = g.px; t[112] = g.py; t[128] = g.lensq; t[144] = g.arc ? 1.0 : 0.0;
+}
+DEV SegC seg_tab_get(const WarpPool& wp, int j) {
+    const double* t = wp.rb + COOP_TAB + j;
+    SegC g;
+    g.bx0 = t[0]; g.by0 = t[16]; g.bx1 = t[32]; g.by1 = t[48]; g.x1 = t[64]; g.y1 = t[80]; g.px = t[96]; g.py = t[112]; g.lensq = t[128]; g.arc = t[144] != 0.0;
+    return g;
 }
 DEV bool closest_item(uint32_t s, double x, double y, double& d2, double& a, double& b, int& r, bool& ix) {
     return closest_eval(seg_decode(s), x, y, d2, a, b, r, ix);

@@ -96,8 +96,8 @@ print("  warps without cooperative iterations: mean cycles entities / sweep / cl
 # ---- envs served by solo warps in the last launch (handoff): who ends the kernel now?
 if n_solo_log:
     lg = solo_log[:n_solo_log]
-    env = (lg[:, 0] & 0xffffff).astype(np.int64); tf = ((lg[:, 0] >> 24) & 15).astype(np.int64)
-    conv = ((lg[:, 0] >> 28) & 1).astype(bool); init = ((lg[:, 0] >> 29) & 1).astype(bool)
+    env = (lg[:, 0] & 0xffffff).astype(np.int64); tf = ((lg[:, 0] >> 24) & 31).astype(np.int64)
+    conv = ((lg[:, 0] >> 32) & 1).astype(bool); init = ((lg[:, 0] >> 33) & 1).astype(bool); sres = ((lg[:, 0] >> 34) & 3).astype(np.int64)
     pick = (lg[:, 1].astype(np.float64) - float(t0)) / 1e3; end = (lg[:, 2].astype(np.float64) - float(t0)) / 1e3
     pub = np.where(lg[:, 3] > 0, (lg[:, 3].astype(np.float64) - float(t0)) / 1e3, np.nan)
     print(f"solo warps: {n_solo_log} envs served, {int(init.sum())} queued at launch (a), {int((~init).sum())} handed over mid-launch (b), "
@@ -109,7 +109,8 @@ if n_solo_log:
     if b.any():
         print(f"  (b) published at us: p10 {np.nanpercentile(pub[b], 10):.1f} p50 {np.nanpercentile(pub[b], 50):.1f} p90 {np.nanpercentile(pub[b], 90):.1f} max {np.nanmax(pub[b]):.1f}; "
               f"wait for a warp us: mean {np.nanmean((pick - pub)[b]):.1f} max {np.nanmax((pick - pub)[b]):.1f}; service us: mean {np.mean((end - pick)[b]):.1f} max {np.max((end - pick)[b]):.1f}")
-        print("  (b) first tick handed over: " + ", ".join(f"t={k}: {int((tf[b] == k).sum())}" for k in range(1, 4)))
+        print("  (b) first tick on the solo warp: " + ", ".join(f"t={k}: {int((tf[b] == k).sum())}" for k in range(0, 4)) +
+              f"; handed over mid-tick (resumed at substep 1 / 2 / 3): {int((sres[b] == 1).sum())} / {int((sres[b] == 2).sum())} / {int((sres[b] == 3).sum())}, at a tick boundary: {int((sres[b] == 0).sum())}")
     its = lg[:, 4].astype(np.int64); smid = lg[:, 5].astype(np.int64)
     long_ = its >= 300
     if long_.any():

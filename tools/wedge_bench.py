@@ -71,6 +71,7 @@ def main():
             print("  phase cycles (4 warps of the block add up; /4 for the wedge warp's share when the others idle at barriers):")
             print("   ", ", ".join(f"{names[k]} {ph[k]:,}" for k in sorted(names)))
             v = list(out); it = max(v[3], 1)
+            print(f"  batches {v[6]}, failed {v[7] & 0xffffffff} (sum of first bad lanes {v[7] >> 32})")
             print(f"  per iteration (clock64): evaluate {v[0] / it:.0f}, select {v[1] / it:.0f}, push {v[2] / it:.0f}; park/take/back {v[5] / max(v[4], 1):.0f} per service, {v[4]} services, {v[3]} iterations")
         t, b = float(np.median(times)), float(np.median(base))
         print(f"wedge {k}: step {t:.1f} us (rest step {b:.1f} us), {coop} cooperative iterations of {d['cp_calls'][k]} closest-point calls"
