@@ -90,8 +90,9 @@ typedef struct {
                                    outputs, nppsim_step_host's block) stays in the caller's env order.  NULL = identity. */
     int32_t*  handoff;          /* optional [NPPSIM_HANDOFF_WORDS]: queue through which envs whose ninja is wedged in a corner (all
                                    32 depenetration iterations of every substep, ninja.py:303-379) leave their home lane and run
-                                   their ticks alone on "solo" warps at the front of the grid -- from the start of a launch when
-                                   their previous tick was wedged, else from the end of their first wedged tick.  The caller
+                                   their ticks alone on "solo" warps -- on SMs reserved for them from one full wave of blocks
+                                   up, else in blocks at the front of the grid -- from the start of a launch when their previous
+                                   tick was wedged, else from the end of their first wedged substep.  The caller
                                    zero-initialises it once and sets word [6] to a non-zero tag unique among the queues used
                                    on the same env arrays (sub-batches: one queue each); the library maintains the rest.
                                    NULL: every env stays in its home lane.  Results are identical either way. */

@@ -262,7 +262,7 @@ class BatchedSimulator:
     def _adapt_handoff(self):
         """Called after every step: every 16th launch, read the queue's saturation counters (asynchronously -- the copy is
         looked at once its event has completed) and, under the automatic policy, stop using the queue when more than half of
-        the launches overflowed it, or when no env has used it in 256 launches.  The kernels without a queue run every env in its home lane; results are identical."""
+        the launches overflowed it, or when no env has used it in 128 launches.  The kernels without a queue run every env in its home lane; results are identical."""
         if self.handoff is None or self._handoff_arg is not None:
             return
         self._adapt_calls = getattr(self, "_adapt_calls", 0) + 1
@@ -278,9 +278,9 @@ class BatchedSimulator:
             if total - seen[1] >= 16:
                 self._adapt_seen = (clipped, total)
                 drop = 2 * (clipped - seen[0]) > total - seen[1]
-            # and a queue no env has ever used after 256 launches (levels without corners to wedge into, e.g. config 2's
+            # and a queue no env has ever used after 128 launches (levels without corners to wedge into, e.g. config 2's
             # single level) only costs the solo kernel's 3-6 % over the plain one
-            if not drop and total >= 256 and used == 0:
+            if not drop and total >= 128 and used == 0:
                 drop = True
             if drop:
                 self._retired_handoff = self.handoff              # (launches in flight still read it)
