@@ -316,10 +316,18 @@ __device__ __noinline__ int death_ball_think(Ctx c, double ninja_x, double ninja
 }
 
 // ---- move / think for the dynamic slots (entity_dic order; nsim.py:235-251) --------------------------------
+#ifdef NPP_PROFILE
+#define KIND_T0 long long _kt = clock64();
+#define KIND_T1(ph, kind) { long long _k1 = clock64(); if ((threadIdx.x & 31) == 0) { atomicAdd(&g_kind_cycles[ph][(kind) & 31][0], (unsigned long long)(_k1 - _kt)); atomicAdd(&g_kind_cycles[ph][(kind) & 31][1], 1ULL); } }
+#else
+#define KIND_T0
+#define KIND_T1(ph, kind)
+#endif
 DEV void dyn_move_phase(Ctx& c) {
     if (!HAS_ANY(NPP_MOVE_MASK)) return;
     #pragma unroll 1
     for (int s = 0; s < c.n_dyn; s++) {
+        KIND_T0
         uint32_t de = __ldg(c.dyn_ent + s);
         int kind = (de >> 16) & 255, id = de & 0xffff, p = de >> 24;
         if (kind == NPP_K_DRONE_ZAP || kind == NPP_K_MINI_DRONE) c.stamp = drone_move(c, s, id, p, kind == NPP_K_MINI_DRONE);
@@ -333,12 +341,14 @@ DEV void dyn_move_phase(Ctx& c) {
             DYNF(c, s, 0) = xpos; DYNF(c, s, 1) = ypos; DYNF(c, s, 2) = xspeed; DYNF(c, s, 3) = yspeed;
             grid_move(c, s, xpos, ypos);
         } else if (kind == NPP_K_THWUMP) c.stamp = thwump_move(c, s, id, p);
+        KIND_T1(0, kind)
     }
 }
 DEV void dyn_think_phase(const Nin& n, Ctx& c) {
     if (!HAS_ANY(NPP_THINK_MASK)) return;
     #pragma unroll 1
     for (int s = 0; s < c.n_dyn; s++) {
+        KIND_T0
         uint32_t de = __ldg(c.dyn_ent + s);
         int kind = (de >> 16) & 255, id = de & 0xffff, p = de >> 24;
         if (kind == NPP_K_DOOR_REGULAR) {                         // entity_door_regular.py:46-53
@@ -350,6 +360,7 @@ DEV void dyn_think_phase(const Nin& n, Ctx& c) {
         } else if (kind == NPP_K_THWUMP) thwump_think(c, n.f[F_XPOS], n.f[F_YPOS], ninja_valid_target(n), s, id, p);
         else if (kind == NPP_K_DEATH_BALL) c.stamp = death_ball_think(c, n.f[F_XPOS], n.f[F_YPOS], ninja_valid_target(n), s, id);
         else if (kind == NPP_K_SHWUMP) c.stamp = shwump_think(c, s, id);
+        KIND_T1(1, kind)
     }
 }
 

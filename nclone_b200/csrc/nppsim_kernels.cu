@@ -642,6 +642,12 @@ int nppsim_debug_coop_cycles(unsigned long long* out8, int reset) {
     if (reset) { unsigned long long z[8] = {0}; cudaMemcpyToSymbol(g_coop_cycles, z, sizeof(z)); }
     return 0;
 }
+int nppsim_debug_kind_cycles(unsigned long long* out128, int reset) {      // [move | think][32 kinds][cycles, calls]
+    cudaDeviceSynchronize();
+    if (out128) cudaMemcpyFromSymbol(out128, g_kind_cycles, sizeof(unsigned long long) * 128);
+    if (reset) { unsigned long long z[128] = {0}; cudaMemcpyToSymbol(g_kind_cycles, z, sizeof(z)); }
+    return 0;
+}
 int nppsim_debug_phase_cycles(unsigned long long* out16, int reset) {
     cudaDeviceSynchronize();
     if (out16) cudaMemcpyFromSymbol(out16, g_phase_cycles, sizeof(unsigned long long) * 16);

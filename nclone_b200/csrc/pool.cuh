@@ -22,6 +22,7 @@ __device__ unsigned long long g_warp_phase[1 << 16][4];   // per warp: cycles in
 __device__ unsigned long long g_solo_log[8192][12];        // per env served by a solo warp: env | t_first << 24 | converted << 32 | initial << 33 | resume substep << 34, ns at pickup, at end, at publication (b), cooperative iterations, %smid, cycles in entities / sweep / closest-point loop / post_collision
 __device__ unsigned int g_solo_n;
 __device__ unsigned long long g_hand_pub[1 << 12];        // per entry of (b): ns at publication
+__device__ unsigned long long g_kind_cycles[2][32][2];   // roaming-entity phases: [move | think][kind][cycles, calls] (lane 0 of every warp)
 __device__ unsigned long long g_coop_cycles[8];        // cooperative depenetration loop: [0] evaluate, [1] select, [2] push, [3] iterations, [4] services, [5] park/take/back
 #define COOP_T(acc, k, t) { long long _n = clock64(); (acc)[k] += _n - (t); (t) = _n; }
 #define PH_COUNT(k) atomicAdd(&g_phase_cycles[k], 1ULL)
