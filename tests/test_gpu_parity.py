@@ -444,6 +444,46 @@ def test_wedged_ninja_handoff_to_solo_warps_vs_oracle(solo_sm, monkeypatch):
         assert (sim.solo_sms() >= 1) == (solo_sm == "2")
 
 
+@pytest.mark.parametrize("solo_sm", ["1", "2"])
+def test_handoff_with_tick_limits_and_long_launches(solo_sm, monkeypatch):
+    """The handoff under per-env tick limits (nppsim_step's tick_limit: 0 .. n_ticks ticks per env and launch, so that envs
+    are handed over with any number of ticks left, including none) and under launches of 8 ticks (two agent steps fused):
+    state and frames_executed must equal those of a batch stepped without a queue, launch by launch."""
+    import torch
+    from nclone_b200 import BatchedSimulator, ACTION_TO_INPUTS
+    monkeypatch.setenv("NPPSIM_SOLO_SM", solo_sm)
+    d = np.load(os.path.join(ROOT, "bench_data", "wedges.npz"))
+    K = len(d["lens"])
+    maps = [d["maps"][k, :d["lens"][k]] for k in range(K)]
+    pre = [d["acts"][d["act_off"][k]:d["act_off"][k + 1]] for k in range(K)]
+    env_to_map = np.repeat(np.arange(K), 16)
+    N = len(env_to_map)
+    rng = np.random.default_rng(9)
+    hj = np.array(ACTION_TO_INPUTS, dtype=np.int8)
+    for n_ticks in (4, 8):
+        launches = (max(len(p) for p in pre) * 4) // n_ticks + 40
+        sim = BatchedSimulator(N, handoff=True); sim.load_maps(maps, env_to_map)
+        plain = BatchedSimulator(N, handoff=False); plain.load_maps(maps, env_to_map)
+        budget = np.zeros(N, dtype=np.int64)             # ticks of the prefix already played, per env
+        for st in range(launches):
+            lim = rng.integers(0, n_ticks + 1, size=N).astype(np.int32)
+            hor = np.zeros((n_ticks, N), dtype=np.int8); jump = np.zeros((n_ticks, N), dtype=np.int8)
+            for e in range(N):
+                p = pre[env_to_map[e]]
+                for t in range(n_ticks):                 # the prefix action of the tick this env would be at, then its last one held
+                    a = p[min((budget[e] + t) // 4, len(p) - 1)]
+                    hor[t, e], jump[t, e] = hj[a]
+            fe = sim.tick(hor, jump, n_ticks=n_ticks, tick_limit=lim, stop_on_terminal=True)
+            fp = plain.tick(hor, jump, n_ticks=n_ticks, tick_limit=lim, stop_on_terminal=True)
+            torch.cuda.synchronize()
+            assert torch.equal(fe, fp), (n_ticks, st)
+            budget += fe.cpu().numpy()
+            for x, y in ((sim.nin_f.view(torch.int64), plain.nin_f.view(torch.int64)), (sim.nin_i, plain.nin_i), (sim.ent_flag, plain.ent_flag)):
+                assert torch.equal(x, y), (n_ticks, st)
+        assert sim.handoff_status() == 0
+        assert sim.handoff_count() >= 8, (n_ticks, sim.handoff_count())
+
+
 def test_automatic_handoff_policy_drops_a_saturated_queue():
     """BatchedSimulator's default policy (handoff=None): the queue is on from 1,024 envs and is dropped once most launches
     overflow it -- wedged ninjas are then the bulk of the work, not its tail (sched_kernel's counters, words 12 / 13 of the
