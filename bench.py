@@ -304,14 +304,17 @@ def measure(workload, n_envs, args, rank, world, dev, dist, steps, warmup, sprea
         if world > 1:
             dist.barrier()
         t1 = sim.total_ticks()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
+        # timed per step like the device-resident loop, so that the same untimed L2 flush can sit between the steps
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
         for s in range(steps):
+            if flush is not None:
+                flush.zero_()
+            evs[s][0].record()
             sim.step_host(ah[s % POOL], block, FRAME_SKIP, True, with_obs)
             sim.reset_terminal(MAX_FRAMES)
-        e1.record()
+            evs[s][1].record()
         torch.cuda.synchronize(dev)
-        return e0.elapsed_time(e1), sim.total_ticks() - t1, int(block.numel())
+        return float(sum(a.elapsed_time(b) for a, b in evs)), sim.total_ticks() - t1, int(block.numel())
 
     out["e2e_ms"], out["e2e_ticks"], out["e2e_d2h"] = e2e_leg(False)
     if do_obs:
