@@ -299,7 +299,7 @@ def measure(workload, n_envs, args, rank, world, dev, dist, steps, warmup, sprea
     def e2e_leg(with_obs):
         block, _ = sim.host_block(with_obs)
         for s in range(3):
-            sim.step_host(ah[s % POOL], block, FRAME_SKIP, True, with_obs); sim.reset_terminal(MAX_FRAMES)
+            sim.step_host(ah[s % POOL], block, FRAME_SKIP, True, with_obs, reset_max_frames=MAX_FRAMES)
         torch.cuda.synchronize(dev)
         if world > 1:
             dist.barrier()
@@ -310,8 +310,7 @@ def measure(workload, n_envs, args, rank, world, dev, dist, steps, warmup, sprea
             if flush is not None:
                 flush.zero_()
             evs[s][0].record()
-            sim.step_host(ah[s % POOL], block, FRAME_SKIP, True, with_obs)
-            sim.reset_terminal(MAX_FRAMES)
+            sim.step_host(ah[s % POOL], block, FRAME_SKIP, True, with_obs, reset_max_frames=MAX_FRAMES)     # nppsim_step_host_reset: step + episode turnover, one call
             evs[s][1].record()
         torch.cuda.synchronize(dev)
         return float(sum(a.elapsed_time(b) for a, b in evs)), sim.total_ticks() - t1, int(block.numel())

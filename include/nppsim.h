@@ -228,6 +228,13 @@ int64_t nppsim_host_block_bytes(int32_t n_envs, int32_t with_obs);
 int nppsim_step_host(const nppsim_state_t* st, const uint8_t* actions_host, uint8_t* actions_dev,
                      int32_t n_ticks, int32_t stop_on_terminal, uint8_t* staging_dev, uint8_t* out_host,
                      int32_t with_obs, void* stream);
+/* nppsim_step_host_reset: nppsim_step_host followed by nppsim_reset_terminal(max_frames, reset_mode, stats) in the same call --
+ * a vectorised wrapper's whole step: the block receives the step's results (the terminal observation of an env that just won
+ * or died included), the episode turnover is queued behind it on the stream, and ONE synchronisation ends the call, so the
+ * device does not idle while the host comes back for the reset (base_environment.py: step(), then reset() of the done envs). */
+int nppsim_step_host_reset(const nppsim_state_t* st, const uint8_t* actions_host, uint8_t* actions_dev,
+                           int32_t n_ticks, int32_t stop_on_terminal, uint8_t* staging_dev, uint8_t* out_host,
+                           int32_t with_obs, int32_t max_frames, int32_t reset_mode, unsigned long long* stats, void* stream);
 
 /* nppsim_observe: the two per-step observation primitives the env wrapper calls.
  *   ninja_state_out  optional device float32 [N][40]: NPlayHeadless.get_ninja_state (nplay_headless.py:735-917);

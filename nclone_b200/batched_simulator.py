@@ -487,10 +487,12 @@ class BatchedSimulator:
             views["action_mask"] = raw[196 * N:202 * N].reshape(N, 6)
         return block, views
 
-    def step_host(self, actions_host, block, frame_skip=4, stop_on_terminal=True, with_obs=False):
+    def step_host(self, actions_host, block, frame_skip=4, stop_on_terminal=True, with_obs=False, reset_max_frames=None, reset_mode="reset"):
         """Host-buffer entry point (nppsim_step_host): numpy uint8 actions [N] in, `block` (host_block()) out -- ninja
         position / velocity / state and optionally the per-step observations, all in the caller's env order; copies are
-        part of the call and the stream is synchronised on return."""
+        part of the call and the stream is synchronised on return.
+        reset_max_frames (not None): nppsim_step_host_reset -- the episode turnover of reset_terminal(reset_max_frames,
+        reset_mode) is queued behind the results in the same call (the block still shows the terminal states)."""
         self._need_maps()
         a = np.asarray(actions_host)
         if a.dtype != np.uint8 or a.shape != (self.n_envs,) or not a.flags["C_CONTIGUOUS"]:
@@ -501,9 +503,15 @@ class BatchedSimulator:
         stg = self._staging.data_ptr()
         stg += (-stg) % 8
         with torch.cuda.device(self.device):
-            check(self.L.nppsim_step_host(C.byref(self._state), C.c_void_p(a.ctypes.data), C.c_void_p(self._actions_dev.data_ptr()),
-                                          int(frame_skip), int(bool(stop_on_terminal)), C.c_void_p(stg),
-                                          C.c_void_p(block.data_ptr()), int(bool(with_obs)), self._stream()))
+            if reset_max_frames is None:
+                check(self.L.nppsim_step_host(C.byref(self._state), C.c_void_p(a.ctypes.data), C.c_void_p(self._actions_dev.data_ptr()),
+                                              int(frame_skip), int(bool(stop_on_terminal)), C.c_void_p(stg),
+                                              C.c_void_p(block.data_ptr()), int(bool(with_obs)), self._stream()))
+            else:
+                check(self.L.nppsim_step_host_reset(C.byref(self._state), C.c_void_p(a.ctypes.data), C.c_void_p(self._actions_dev.data_ptr()),
+                                                    int(frame_skip), int(bool(stop_on_terminal)), C.c_void_p(stg),
+                                                    C.c_void_p(block.data_ptr()), int(bool(with_obs)), int(reset_max_frames),
+                                                    {"reset": 0, "fast": 1}[reset_mode], C.c_void_p(self.stats.data_ptr()), self._stream()))
         self._adapt_handoff()
 
     # ------------------------------------------------------------------ NPlayHeadless getters, batched

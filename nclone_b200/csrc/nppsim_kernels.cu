@@ -769,8 +769,9 @@ int64_t nppsim_host_block_bytes(int32_t n_envs, int32_t with_obs) {
     return n * (4 * 8 + 4) + (with_obs ? n * (40 * 4 + 6) : 0);
 }
 
-int nppsim_step_host(const nppsim_state_t* st, const uint8_t* actions_host, uint8_t* actions_dev, int32_t n_ticks,
-                     int32_t stop_on_terminal, uint8_t* staging_dev, uint8_t* out_host, int32_t with_obs, void* stream) {
+static int step_host_impl(const nppsim_state_t* st, const uint8_t* actions_host, uint8_t* actions_dev, int32_t n_ticks,
+                          int32_t stop_on_terminal, uint8_t* staging_dev, uint8_t* out_host, int32_t with_obs, void* stream,
+                          bool turnover, int32_t max_frames, int32_t reset_mode, unsigned long long* stats) {
     g_err[0] = 0;
     int rc = check_state(st);
     if (rc) return rc;
@@ -812,9 +813,27 @@ int nppsim_step_host(const nppsim_state_t* st, const uint8_t* actions_host, uint
         e = cudaMemcpyAsync(out_host + skip, staging_dev + skip, (size_t)nppsim_host_block_bytes(st->n_envs, with_obs) - skip, cudaMemcpyDeviceToHost, s);
         if (e != cudaSuccess) return cuda_fail(e, "result D2H");
     }
+    if (turnover) {                                              // the block holds the step's results; the episode turnover queues behind them
+        if (reset_mode != 0 && reset_mode != 1) return fail(NPPSIM_E_ARG, "mode must be 0 (load/reset) or 1 (fast_reset)");
+        reset_kernel<<<(st->n_envs + 127) / 128, 128, 0, s>>>(*st, nullptr, reset_mode, 1, max_frames, stats);
+        g_launches++;
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return cuda_fail(e, "reset_kernel launch");
+    }
     e = cudaStreamSynchronize(s);
     if (e != cudaSuccess) return cuda_fail(e, "stream sync");
     return 0;
+}
+
+int nppsim_step_host(const nppsim_state_t* st, const uint8_t* actions_host, uint8_t* actions_dev, int32_t n_ticks,
+                     int32_t stop_on_terminal, uint8_t* staging_dev, uint8_t* out_host, int32_t with_obs, void* stream) {
+    return step_host_impl(st, actions_host, actions_dev, n_ticks, stop_on_terminal, staging_dev, out_host, with_obs, stream, false, 0, 0, nullptr);
+}
+
+int nppsim_step_host_reset(const nppsim_state_t* st, const uint8_t* actions_host, uint8_t* actions_dev, int32_t n_ticks,
+                           int32_t stop_on_terminal, uint8_t* staging_dev, uint8_t* out_host, int32_t with_obs,
+                           int32_t max_frames, int32_t reset_mode, unsigned long long* stats, void* stream) {
+    return step_host_impl(st, actions_host, actions_dev, n_ticks, stop_on_terminal, staging_dev, out_host, with_obs, stream, true, max_frames, reset_mode, stats);
 }
 
 }  // extern "C"

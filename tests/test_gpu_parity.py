@@ -239,6 +239,22 @@ def test_step_host_matches_device_path(golden_replays, golden_generated):
     assert len(np.unique(v["pos_vel"][0])) > 3                     # the three levels really behave differently
     with pytest.raises(ValueError):
         s2.step_host(a[0].astype(np.int64), block)                 # dtype is checked, not reinterpreted
+    # nppsim_step_host_reset: the same call queues the episode turnover behind the results -- the block shows the step's
+    # (terminal) states, the device state is the one after reset_terminal
+    s5 = BatchedSimulator(N); s5.load_maps(maps, e2m)
+    s6 = BatchedSimulator(N, placement="caller"); s6.load_maps(maps, e2m)
+    block5, v5 = s5.host_block(with_obs=True)
+    block6, v6 = s6.host_block(with_obs=True)
+    terminal = 0
+    for k in range(20):
+        s5.step_host(a[k], block5, 4, True, with_obs=True)
+        s6.step_host(a[k], block6, 4, True, with_obs=True, reset_max_frames=24)
+        assert np.array_equal(block5.numpy(), block6.numpy()), k
+        terminal += int(np.isin(v6["state"], (6, 7, 8)).sum())
+        s5.reset_terminal(24)
+        for x, y in ((s5.nin_f.view(torch.int64), s6.nin_f.view(torch.int64)), (s5.nin_i, s6.nin_i), (s5.ent_flag, s6.ent_flag)):
+            assert torch.equal(x, y), k
+    assert int(s6.stats[0].item()) == int(s5.stats[0].item()) >= N     # every env was truncated at 24 frames at least once
 
 
 def _oracle_rollout(maps, env_to_map, actions, frame_skip, max_frames, check_every):
