@@ -217,6 +217,7 @@ int nppsim_replay_rows(const nppsim_state_t* st, const nppsim_input_stream_t* in
  * with_obs != 0, of the observations the wrapper pulls every step, base_environment.py:2822, 3107 -- for the batch):
  * copies `actions_host` [N] to `actions_dev`, runs nppsim_step_actions, packs the results in the CALLER's env order into
  * `staging_dev` and copies that block to `out_host` with ONE device-to-host copy, then synchronises the stream.
+ * Pinned `actions_host` is read in place by the step kernel (mapped host memory, no copy operation; `actions_dev` is then unused).
  * When `out_host` is pinned (page-locked) memory and the state is not permuted (ext_of == NULL), the step kernel stores
  * position / velocity / state into it directly as each env finishes (mapped host memory; no pack, no copy for that part).
  * Block layout (nppsim_host_block_bytes(N, with_obs) bytes; staging_dev 8-byte aligned, out_host pinned for speed):

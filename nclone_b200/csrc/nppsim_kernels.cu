@@ -779,8 +779,21 @@ static int step_host_impl(const nppsim_state_t* st, const uint8_t* actions_host,
     if (((uintptr_t)staging_dev & 7) != 0) return fail(NPPSIM_E_ARG, "staging_dev must be 8-byte aligned");
     cudaStream_t s = (cudaStream_t)stream;
     const size_t N = (size_t)st->n_envs;
-    cudaError_t e = cudaMemcpyAsync(actions_dev, actions_host, N, cudaMemcpyHostToDevice, s);
-    if (e != cudaSuccess) return cuda_fail(e, "actions H2D");
+    // Pinned actions are read by the step kernel where they are (one byte per env as the env is loaded: mapped host memory)
+    // -- no copy operation in front of the kernel; pageable actions are copied to actions_dev first.
+    const uint8_t* actions_in = actions_dev;
+    cudaError_t e = cudaSuccess;
+    {
+        const char* const ev_zc = getenv("NPPSIM_ZEROCOPY");
+        cudaPointerAttributes attr;
+        if ((!ev_zc || atoi(ev_zc) != 0) && cudaPointerGetAttributes(&attr, actions_host) == cudaSuccess && attr.type == cudaMemoryTypeHost && attr.devicePointer)
+            actions_in = reinterpret_cast<const uint8_t*>(attr.devicePointer);
+        else {
+            cudaGetLastError();
+            e = cudaMemcpyAsync(actions_dev, actions_host, N, cudaMemcpyHostToDevice, s);
+            if (e != cudaSuccess) return cuda_fail(e, "actions H2D");
+        }
+    }
     // A pinned result block is mapped into the device's address space (unified addressing): the step kernel then stores
     // position / velocity / state of every env into it as the env finishes, and only the observations -- computed from the
     // final state by a second kernel -- are staged and copied.  A pageable block takes the staged path for everything, and
@@ -797,7 +810,7 @@ static int step_host_impl(const nppsim_state_t* st, const uint8_t* actions_host,
             host_state = reinterpret_cast<int32_t*>(reinterpret_cast<uint8_t*>(attr.devicePointer) + N * 32);
         } else cudaGetLastError();                               // (an unregistered pointer is not an error here)
     }
-    rc = launch_step(st, nullptr, nullptr, actions_dev, 1, n_ticks, nullptr, stop_on_terminal, nullptr, stream, nullptr, host_pv, host_state);
+    rc = launch_step(st, nullptr, nullptr, actions_in, 1, n_ticks, nullptr, stop_on_terminal, nullptr, stream, nullptr, host_pv, host_state);
     if (rc) return rc;
     if (!host_pv || with_obs) {
         // one pass over the batch packs what the caller reads every step, in the caller's env order, into one block: one D2H copy

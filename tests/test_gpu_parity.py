@@ -246,9 +246,10 @@ def test_step_host_matches_device_path(golden_replays, golden_generated):
     block5, v5 = s5.host_block(with_obs=True)
     block6, v6 = s6.host_block(with_obs=True)
     terminal = 0
+    a_pinned = torch.from_numpy(a).pin_memory().numpy()           # pinned actions are read in place by the step kernel, pageable ones copied first
     for k in range(20):
         s5.step_host(a[k], block5, 4, True, with_obs=True)
-        s6.step_host(a[k], block6, 4, True, with_obs=True, reset_max_frames=24)
+        s6.step_host(a_pinned[k], block6, 4, True, with_obs=True, reset_max_frames=24)
         assert np.array_equal(block5.numpy(), block6.numpy()), k
         terminal += int(np.isin(v6["state"], (6, 7, 8)).sum())
         s5.reset_terminal(24)
