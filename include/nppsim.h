@@ -237,6 +237,31 @@ int nppsim_step_host_reset(const nppsim_state_t* st, const uint8_t* actions_host
                            int32_t n_ticks, int32_t stop_on_terminal, uint8_t* staging_dev, uint8_t* out_host,
                            int32_t with_obs, int32_t max_frames, int32_t reset_mode, unsigned long long* stats, void* stream);
 
+/* nppsim_step_host_static: nppsim_step_host for a caller that has no way to allocate device memory.  (No counterpart in the
+ * reference -- it has no device memory to manage; this exists for the hosts the library gets embedded in.)
+ * Who that is: a ctypes / cffi stub that loads this library but links no CUDA runtime of its own to call cudaMalloc with; an
+ * actor process next to a trainer or inference server that has claimed the card's memory up front for its own pool, where a
+ * late cudaMalloc fails or is against the deployment's rules; a step loop that must not allocate because cudaMalloc
+ * synchronises the whole device under the other streams' feet.  Such a caller still owns the simulation state it passes in
+ * `st` and the two host buffers; what it cannot supply is nppsim_step_host's pair of scratch buffers (`actions_dev`,
+ * `staging_dev`).  Here they are a fixed array inside the library image instead: NPPSIM_STATIC_MAX_ENVS * 203 bytes
+ * (3.2 MiB) of every GPU that loads the library, held until the process exits whether or not this function is ever called.
+ *   - Same arguments, same block layout, same results bit for bit as nppsim_step_host without `actions_dev` / `staging_dev`;
+ *     host buffers may be pinned or pageable (both are copied; nothing is read or written in place).  st->handoff is ignored:
+ *     every env runs in its home lane (results do not depend on it).
+ *   - n_envs > NPPSIM_STATIC_MAX_ENVS: returns NPPSIM_E_CAPACITY before anything is launched; split the batch into sub-batch
+ *     views (nppsim_state_t.stride) and call once per view, one after the other.
+ *   - The function calls no cudaMalloc / cudaFree and nothing that allocates on the device.  Its FIRST call on each device
+ *     looks up the array's device address and sets the step kernels' launch attributes (under a lock, with that device
+ *     current); make that first call outside any stream capture.
+ *   - All calls on one device share the one array.  It needs no clearing (a call writes every byte it copies out) and it keeps
+ *     the previous call's data.  The function returns only after its stream has drained, so calls made one after the other are
+ *     safe; calls that overlap on the GPU -- which takes two host threads stepping on the same device at once -- overwrite each
+ *     other's actions and results.  Serialise them, or give each thread buffers of its own through nppsim_step_host. */
+#define NPPSIM_STATIC_MAX_ENVS 16384
+int nppsim_step_host_static(const nppsim_state_t* st, const uint8_t* actions_host, int32_t n_ticks, int32_t stop_on_terminal,
+                            uint8_t* out_host, int32_t with_obs, void* stream);
+
 /* nppsim_observe: the two per-step observation primitives the env wrapper calls.
  *   ninja_state_out  optional device float32 [N][40]: NPlayHeadless.get_ninja_state (nplay_headless.py:735-917);
  *   mask_out         optional device uint8 [N][6]: Ninja.get_valid_action_mask (ninja.py:628-839), masking mode

@@ -30,7 +30,7 @@ STREAM_ACTIONS, STREAM_REPLAY_BYTES = 0, 1
 EXPORTS = (
     "nppsim_version", "nppsim_last_error", "nppsim_map_blob_bound", "nppsim_compile_map",
     "nppsim_reset", "nppsim_reset_terminal", "nppsim_step", "nppsim_step_actions", "nppsim_step_stream", "nppsim_replay_rows",
-    "nppsim_step_host", "nppsim_step_host_reset", "nppsim_host_block_bytes", "nppsim_launch_count",
+    "nppsim_step_host", "nppsim_step_host_reset", "nppsim_step_host_static", "nppsim_host_block_bytes", "nppsim_launch_count",
     "nppsim_observe", "nppsim_set_exit_positions", "nppsim_compile_maps_device", "nppsim_debug_sq", "nppsim_debug_div2", "nppsim_sq_mode",
 )
 
@@ -66,6 +66,7 @@ def lib():
     L.nppsim_replay_rows.argtypes = [st, sp, vp, i32, i32, vp, vp, vp, vp, vp]; L.nppsim_replay_rows.restype = C.c_int
     L.nppsim_step_host.argtypes = [st, vp, vp, i32, i32, vp, vp, i32, vp]; L.nppsim_step_host.restype = C.c_int
     L.nppsim_step_host_reset.argtypes = [st, vp, vp, i32, i32, vp, vp, i32, i32, i32, vp, vp]; L.nppsim_step_host_reset.restype = C.c_int
+    L.nppsim_step_host_static.argtypes = [st, vp, i32, i32, vp, i32, vp]; L.nppsim_step_host_static.restype = C.c_int
     L.nppsim_host_block_bytes.argtypes = [i32, i32]; L.nppsim_host_block_bytes.restype = i64
     L.nppsim_launch_count.restype = i64
     L.nppsim_observe.argtypes = [st, vp, vp, vp, vp]; L.nppsim_observe.restype = C.c_int

@@ -514,6 +514,25 @@ class BatchedSimulator:
                                                     {"reset": 0, "fast": 1}[reset_mode], C.c_void_p(self.stats.data_ptr()), self._stream()))
         self._adapt_handoff()
 
+    def step_host_static(self, actions_host, block, frame_skip=4, stop_on_terminal=True, with_obs=False):
+        """step_host through nppsim_step_host_static: same inputs, same block, same results, but the two device scratch
+        buffers of step_host (this object's _actions_dev / _staging) are not used -- the library's built-in array stands in
+        for them, which is what a caller without a device allocator has to rely on (include/nppsim.h).  At most
+        STATIC_MAX_ENVS envs per call; larger batches raise (step their groups() one after the other instead).  The array is
+        shared by every simulator on the device: do not call this from two threads at once."""
+        self._need_maps()
+        a = np.asarray(actions_host)
+        if a.dtype != np.uint8 or a.shape != (self.n_envs,) or not a.flags["C_CONTIGUOUS"]:
+            raise ValueError("actions_host must be a contiguous uint8 array with one action per env")
+        need = int(self.L.nppsim_host_block_bytes(self.n_envs, int(bool(with_obs))))
+        if block.dtype != torch.uint8 or block.device.type != "cpu" or block.numel() < need or not block.is_contiguous():
+            raise ValueError(f"block must be a contiguous CPU uint8 tensor of at least {need} bytes (host_block())")
+        with torch.cuda.device(self.device):
+            check(self.L.nppsim_step_host_static(C.byref(self._state), C.c_void_p(a.ctypes.data), int(frame_skip), int(bool(stop_on_terminal)),
+                                                 C.c_void_p(block.data_ptr()), int(bool(with_obs)), self._stream()))
+
+    STATIC_MAX_ENVS = 16384     # NPPSIM_STATIC_MAX_ENVS
+
     # ------------------------------------------------------------------ NPlayHeadless getters, batched
     def _f(self, name):
         return self._ext(self._nin_f[FD.F[name]])

@@ -849,4 +849,95 @@ int nppsim_step_host_reset(const nppsim_state_t* st, const uint8_t* actions_host
     return step_host_impl(st, actions_host, actions_dev, n_ticks, stop_on_terminal, staging_dev, out_host, with_obs, stream, true, max_frames, reset_mode, stats);
 }
 
+// ---- nppsim_step_host_static: the host-buffer step for callers that cannot give the library device buffers ---------------
+// nppsim_step_host needs two pieces of device memory that are neither input nor output: `actions_dev` (where pageable actions
+// land) and `staging_dev` (where the pack kernel assembles the result block before its one copy to the host).  A caller
+// that has no allocator to get them from -- see include/nppsim.h -- uses this entry point instead: both live in the
+// file-scope array below, which every device that loads the library carries from load to exit.
+//   [0, 202 * MAX)            result block of the current call, laid out for the call's own n_envs (nppsim_host_block_bytes)
+//   [202 * MAX, 203 * MAX)    the call's actions
+// Nothing here is accumulated from call to call: every byte a call copies out it has written itself first, so nothing needs
+// clearing -- but the array keeps the last call's data, and two calls in flight on one device would write over each other.
+#define STATIC_BLOCK_BYTES ((size_t)NPPSIM_STATIC_MAX_ENVS * 202)
+#define STATIC_SCRATCH_BYTES ((size_t)NPPSIM_STATIC_MAX_ENVS * 203)
+static __device__ __align__(256) unsigned char g_static_scratch[STATIC_SCRATCH_BYTES];
+
+// The array's name means something only to device code and to the runtime's symbol calls; the address a kernel argument
+// needs is asked for once per device, with that device current.  The same set-up gives the two step kernels this entry
+// point launches the attributes launch_step gives them (same values: whichever runs first, the kernels end up configured
+// alike) -- without launch_step's probe launch, which allocates.
+static int static_scratch(unsigned char** out) {
+    static std::mutex mu;
+    static unsigned char* ptr_of[64] = {nullptr};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice");
+    std::lock_guard<std::mutex> lock(mu);
+    if (dev >= 0 && dev < 64 && ptr_of[dev]) { *out = ptr_of[dev]; return 0; }
+    unsigned char* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_static_scratch);
+    if (e != cudaSuccess || !p) return cuda_fail(e != cudaSuccess ? e : cudaErrorInvalidSymbol, "address of the static scratch array");
+    const int resident = STEP_BLOCKS_PER_SM > 2 ? STEP_BLOCKS_PER_SM : 2;
+    const int carve = (int)((resident * (STEP_SMEM + 1024) * 100 + 233471) / 233472) + 1;
+    e = cudaFuncSetAttribute(sim_basic::step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(sim_full::step_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(sim_basic::step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)STEP_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(sim_full::step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)STEP_SMEM);
+    if (e != cudaSuccess) return cuda_fail(e, "step kernel attributes");
+    if (dev >= 0 && dev < 64) ptr_of[dev] = p;                  // (a device number past the table is looked up on every call)
+    *out = p;
+    return 0;
+}
+
+int nppsim_step_host_static(const nppsim_state_t* st, const uint8_t* actions_host, int32_t n_ticks, int32_t stop_on_terminal,
+                            uint8_t* out_host, int32_t with_obs, void* stream) {
+    g_err[0] = 0;
+    int rc = check_state(st);
+    if (rc) return rc;
+    if (!actions_host || !out_host) return fail(NPPSIM_E_ARG, "a host buffer is NULL");
+    if (n_ticks <= 0) return fail(NPPSIM_E_ARG, "n_ticks must be positive");
+    if (st->n_envs > NPPSIM_STATIC_MAX_ENVS) {
+        snprintf(g_err, sizeof(g_err), "n_envs %d is more than the built-in scratch holds (NPPSIM_STATIC_MAX_ENVS = %d): split the batch, or "
+                 "give nppsim_step_host buffers of your own", (int)st->n_envs, (int)NPPSIM_STATIC_MAX_ENVS);
+        return NPPSIM_E_CAPACITY;
+    }
+    unsigned char* scratch = nullptr;
+    rc = static_scratch(&scratch);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t N = (size_t)st->n_envs;
+    uint8_t* const actions = scratch + STATIC_BLOCK_BYTES;
+    cudaError_t e = cudaMemcpyAsync(actions, actions_host, N, cudaMemcpyHostToDevice, s);
+    if (e != cudaSuccess) return cuda_fail(e, "actions H2D");
+    // every env in its home lane: the solo-warp queue needs launch_step's per-device SM table (results are the same either way)
+    nppsim_state_t own = *st;
+    own.handoff = nullptr;
+    const bool basic = own.kind_mask != 0 && (own.kind_mask & ~NPP_BASIC_MASK) == 0;
+    nppsim_input_stream_t sp;
+    memset(&sp, 0, sizeof(sp));
+    sp.repeat = 1;
+    const int n_regular = (own.n_envs + STEP_BLOCK - 1) / STEP_BLOCK;
+    auto kernel = basic ? sim_basic::step_kernel : sim_full::step_kernel;
+    kernel<<<n_regular, STEP_BLOCK, STEP_SMEM, s>>>(own, nullptr, nullptr, actions, 1, n_ticks, nullptr, stop_on_terminal, nullptr, sp, 0, 0, n_regular, 0, nullptr, nullptr);
+    g_launches++;
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "step_kernel launch");
+    if (own.warp_order && own.warp_cost) {                      // keep the caller's longest-first order current, as nppsim_step_host does
+        sched_kernel<<<1, 1024, 0, s>>>(own.warp_order, own.warp_cost, (own.n_envs + 31) / 32, nullptr, nullptr, 0, 0, 256);
+        g_launches++;
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return cuda_fail(e, "sched_kernel launch");
+    }
+    obs_kernel<<<(own.n_envs + 127) / 128, 128, 0, s>>>(own, nullptr, with_obs ? scratch + N * 196 : nullptr, with_obs ? reinterpret_cast<float*>(scratch + N * 36) : nullptr,
+                                                         reinterpret_cast<double*>(scratch), reinterpret_cast<int32_t*>(scratch + N * 32));
+    g_launches++;
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "obs_kernel launch");
+    e = cudaMemcpyAsync(out_host, scratch, (size_t)nppsim_host_block_bytes(own.n_envs, with_obs), cudaMemcpyDeviceToHost, s);
+    if (e != cudaSuccess) return cuda_fail(e, "result D2H");
+    e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) return cuda_fail(e, "stream sync");
+    return 0;
+}
+
 }  // extern "C"
