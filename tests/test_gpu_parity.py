@@ -409,7 +409,8 @@ def test_wedged_ninja_handoff_to_solo_warps_vs_oracle(solo_sm, monkeypatch):
     first wedged tick and finishes the agent step on a solo warp; envs wedged when the previous launch ended start there.
     Same scenario as above with the queue switched on (it is on by default from 1,024 envs): full ninja record and
     frames_executed against the oracle after every agent step, handoffs must have happened, no solo warp may have timed out.
-    Second half: per-tick input rows and per-env action streams (the two other input forms) through the handoff.
+    Second half: per-tick input rows, per-env action streams and one held hor / jump value per env (the three other input
+    forms) through the handoff -- an env that changes hands at tick >= 1 must keep the inputs it was given.
     solo_sm = "2": the same with the solo blocks dealt by SM (whole SMs reserved for solo warps, regular blocks taking their envs
     from a counter) -- what launches of a full wave and more do by themselves -- forced onto this small grid."""
     import torch
@@ -428,7 +429,7 @@ def test_wedged_ninja_handoff_to_solo_warps_vs_oracle(solo_sm, monkeypatch):
         actions[:len(p), e] = p
         actions[len(p):, e] = e % 6
     ref = _oracle_rollout(maps, env_to_map, actions, 4, 2000, 1)
-    for mode in ("actions", "rows", "stream"):
+    for mode in ("actions", "rows", "stream", "held"):
         sim = BatchedSimulator(N, handoff=True)
         sim.load_maps(maps, env_to_map)
         hj = np.array(ACTION_TO_INPUTS, dtype=np.int8)
@@ -444,6 +445,8 @@ def test_wedged_ninja_handoff_to_solo_warps_vs_oracle(solo_sm, monkeypatch):
             elif mode == "rows":
                 hor = np.repeat(hj[actions[st], 0][None, :], 4, 0); jump = np.repeat(hj[actions[st], 1][None, :], 4, 0)
                 fe = sim.tick(hor, jump, n_ticks=4, stop_on_terminal=True)
+            elif mode == "held":
+                fe = sim.tick(hj[actions[st], 0].copy(), hj[actions[st], 1].copy(), n_ticks=4, stop_on_terminal=True)
             else:
                 fe = sim.step_stream(sp, 4, start_tick=4 * st, stop_on_terminal=True)
             _, nf, ni = ref[st]
