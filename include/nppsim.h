@@ -215,11 +215,15 @@ int nppsim_replay_rows(const nppsim_state_t* st, const nppsim_input_stream_t* in
 
 /* nppsim_step_host: the call a host-resident caller makes (one NppEnvironment.step worth of physics -- and, with
  * with_obs != 0, of the observations the wrapper pulls every step, base_environment.py:2822, 3107 -- for the batch):
- * copies `actions_host` [N] to `actions_dev`, runs nppsim_step_actions, packs the results in the CALLER's env order into
- * `staging_dev` and copies that block to `out_host` with ONE device-to-host copy, then synchronises the stream.
- * Pinned `actions_host` is read in place by the step kernel (mapped host memory, no copy operation; `actions_dev` is then unused).
- * When `out_host` is pinned (page-locked) memory and the state is not permuted (ext_of == NULL), the step kernel stores
- * position / velocity / state into it directly as each env finishes (mapped host memory; no pack, no copy for that part).
+ * runs nppsim_step_actions on `actions_host` [N] and delivers the results in the CALLER's env order in `out_host`, then
+ * synchronises the stream.  How the bytes travel depends on the host buffers:
+ *   - pinned `actions_host` is read in place by the step kernel (mapped host memory, no copy operation; `actions_dev` is then
+ *     unused); pageable actions are copied to `actions_dev` first;
+ *   - when `out_host` is pinned (page-locked, 8-byte aligned) and the state is not permuted (ext_of == NULL), the step kernel
+ *     stores position / velocity / state into it directly as each env finishes (no pack, no copy for that part), and only the
+ *     observations (with_obs) are packed into `staging_dev` and copied;
+ *   - otherwise a pack kernel assembles the whole block in `staging_dev` and ONE device-to-host copy moves it.
+ * All arguments are checked before anything is queued.
  * Block layout (nppsim_host_block_bytes(N, with_obs) bytes; staging_dev 8-byte aligned, out_host pinned for speed):
  *   [0, 32N)      f64 [4][N]   ninja xpos, ypos, xspeed, yspeed
  *   [32N, 36N)    i32 [N]      ninja state

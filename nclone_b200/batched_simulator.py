@@ -260,10 +260,12 @@ class BatchedSimulator:
         return 1024 <= n_envs
 
     def _adapt_handoff(self):
-        """Called after every step: every 16th launch, read the queue's saturation counters (asynchronously -- the copy is
-        looked at once its event has completed) and, under the automatic policy, stop using the queue when more than half of
-        the launches overflowed it, or when no env has used it in 128 launches.  The kernels without a queue run every env in its home lane; results are identical."""
-        if self.handoff is None or self._handoff_arg is not None:
+        """Called after every step: every 16th launch, read the queue's error word and saturation counters (asynchronously --
+        the copy is looked at once its event has completed).  A set error word (a solo warp gave up waiting for an entry, so an
+        env may have missed ticks: csrc/sim_variant.inc) raises -- such a batch is no longer the reference's.  Under the
+        automatic policy the queue is then dropped when more than half of the launches overflowed it, or when no env has used
+        it in 128 launches.  The kernels without a queue run every env in its home lane; results are identical."""
+        if self.handoff is None:
             return
         self._adapt_calls = getattr(self, "_adapt_calls", 0) + 1
         pending = getattr(self, "_adapt_pending", None)
@@ -272,7 +274,12 @@ class BatchedSimulator:
             if not ev.query():
                 return
             self._adapt_pending = None
-            used, clipped, total = int(buf[0]) + int(buf[3]), int(buf[8]), int(buf[9])      # words 4 + 7 | 12 | 13
+            if int(buf[0]) != 0:                                       # word 3, sticky
+                raise RuntimeError(f"handoff queue error bits {int(buf[0])}: a solo warp timed out waiting for an env; "
+                                   "the batch may have lost ticks (reload, or step with handoff=False)")
+            if self._handoff_arg is not None:                          # queue forced on or off by the caller: no policy
+                return
+            used, clipped, total = int(buf[1]) + int(buf[4]), int(buf[9]), int(buf[10])      # words 4 + 7 | 12 | 13
             seen = getattr(self, "_adapt_seen", (0, 0))
             drop = False
             if total - seen[1] >= 16:
@@ -290,9 +297,9 @@ class BatchedSimulator:
         if self._adapt_calls % 16 == 0:
             buf = getattr(self, "_adapt_buf", None)
             if buf is None:
-                buf = self._adapt_buf = torch.zeros(10, dtype=torch.int32).pin_memory()
+                buf = self._adapt_buf = torch.zeros(11, dtype=torch.int32).pin_memory()
             with torch.cuda.device(self.device):
-                buf.copy_(self.handoff[4:14], non_blocking=True)
+                buf.copy_(self.handoff[3:14], non_blocking=True)
                 ev = torch.cuda.Event()
                 ev.record()
             self._adapt_pending = (ev, buf)
@@ -411,6 +418,7 @@ class BatchedSimulator:
             check(self.L.nppsim_step(C.byref(self._state), C.c_void_p(hor.data_ptr()), C.c_void_p(jump.data_ptr()),
                                      input_ticks, int(n_ticks), lim, int(bool(stop_on_terminal)),
                                      C.c_void_p(self._frames_executed.data_ptr()), self._stream()))
+        self._adapt_handoff()
         return self.frames_executed
 
     def step(self, actions, frame_skip=4, stop_on_terminal=True):
@@ -457,6 +465,7 @@ class BatchedSimulator:
         with torch.cuda.device(self.device):
             check(self.L.nppsim_step_stream(C.byref(self._state), C.byref(stream), int(n_ticks), int(bool(stop_on_terminal)),
                                             C.c_void_p(self._frames_executed.data_ptr()), self._stream()))
+        self._adapt_handoff()
         return self.frames_executed
 
     def replay_to_checkpoint(self, action_sequences, frame_skip=1, mask=None):

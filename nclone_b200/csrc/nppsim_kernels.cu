@@ -777,6 +777,9 @@ static int step_host_impl(const nppsim_state_t* st, const uint8_t* actions_host,
     if (rc) return rc;
     if (!actions_host || !actions_dev || !staging_dev || !out_host) return fail(NPPSIM_E_ARG, "a host/device buffer is NULL");
     if (((uintptr_t)staging_dev & 7) != 0) return fail(NPPSIM_E_ARG, "staging_dev must be 8-byte aligned");
+    if (n_ticks <= 0) return fail(NPPSIM_E_ARG, "n_ticks must be positive");
+    // (everything is checked before anything is queued: an error return leaves the state as it was)
+    if (turnover && reset_mode != 0 && reset_mode != 1) return fail(NPPSIM_E_ARG, "mode must be 0 (load/reset) or 1 (fast_reset)");
     cudaStream_t s = (cudaStream_t)stream;
     const size_t N = (size_t)st->n_envs;
     // Pinned actions are read by the step kernel where they are (one byte per env as the env is loaded: mapped host memory)
@@ -805,7 +808,8 @@ static int step_host_impl(const nppsim_state_t* st, const uint8_t* actions_host,
         const char* const ev_zc = getenv("NPPSIM_ZEROCOPY");
         const int zc = ev_zc ? atoi(ev_zc) : 1;
         cudaPointerAttributes attr;
-        if (zc && (!st->ext_of || zc == 2) && cudaPointerGetAttributes(&attr, out_host) == cudaSuccess && attr.type == cudaMemoryTypeHost && attr.devicePointer) {
+        if (zc && (!st->ext_of || zc == 2) && cudaPointerGetAttributes(&attr, out_host) == cudaSuccess && attr.type == cudaMemoryTypeHost && attr.devicePointer &&
+            ((uintptr_t)attr.devicePointer & 7) == 0) {          // (f64 stores: an unaligned slice of a pinned buffer takes the staged path)
             host_pv = reinterpret_cast<double*>(attr.devicePointer);
             host_state = reinterpret_cast<int32_t*>(reinterpret_cast<uint8_t*>(attr.devicePointer) + N * 32);
         } else cudaGetLastError();                               // (an unregistered pointer is not an error here)
@@ -827,7 +831,6 @@ static int step_host_impl(const nppsim_state_t* st, const uint8_t* actions_host,
         if (e != cudaSuccess) return cuda_fail(e, "result D2H");
     }
     if (turnover) {                                              // the block holds the step's results; the episode turnover queues behind them
-        if (reset_mode != 0 && reset_mode != 1) return fail(NPPSIM_E_ARG, "mode must be 0 (load/reset) or 1 (fast_reset)");
         reset_kernel<<<(st->n_envs + 127) / 128, 128, 0, s>>>(*st, nullptr, reset_mode, 1, max_frames, stats);
         g_launches++;
         e = cudaGetLastError();
