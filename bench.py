@@ -125,6 +125,11 @@ def config_dict(workload, n_envs, n_levels, placement, flush):
             "arithmetic": "IEEE double, x**2 == glibc pow(x, 2) (GPU arm: exact emulation)"}
 
 
+def headline_config(args, n_levels):
+    """`config` of the headline workload from the parsed command line -- the ONE place both arms get it from."""
+    return config_dict(args.workload, args.envs or WORKLOADS[args.workload][1], n_levels, args.placement, not args.no_flush)
+
+
 # ---------------------------------------------------------------------------------------------------- CPU baselines
 def cpu_baseline_port(arr, lens, threads, target_seconds, seed=99):
     """Oracle port (oracle/nsim_oracle.c) on the host cores: same level set, same action distribution, same frame-skip /
@@ -230,7 +235,7 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": "env-steps/sec", "value": value, "unit": "env-steps/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * wall / n_slices,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": config_dict(args.workload, n_envs, len(arr), args.placement, not args.no_flush),
+        "config": headline_config(args, len(arr)),
         "cpu_baseline": info,
         "e2e": {"value": value, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "host_threads": threads,
@@ -386,7 +391,7 @@ def secondary_block(tag, m, r, n_envs, steps):
     return b
 
 
-def main():
+def build_parser():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
@@ -403,7 +408,11 @@ def main():
     ap.add_argument("--engine-order", default="auto", choices=["level", "caller", "auto"], help="BatchedSimulator placement: envs of a level in consecutive state columns, the caller's order, or (default) by replicas per level")
     ap.add_argument("--handoff", default="auto", choices=["auto", "on", "off"], help="solo-warp handoff of wedged envs")
     ap.add_argument("--spread", type=int, default=300, help="untimed agent steps run first so envs sit at mixed episode phases")
-    args = ap.parse_args()
+    return ap
+
+
+def main():
+    args = build_parser().parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -506,7 +515,7 @@ def main():
         "metric": "env-steps/sec", "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": config_dict(args.workload, n_envs, M, args.placement, flush is not None),
+        "config": headline_config(args, M),
         "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": int(n_envs), "d2h_bytes_per_step": int(m["e2e_d2h"]),
                 "ms_per_step": r["e2e_ms_per_step"]},
         "gpu_launches": int(m["launches"]),

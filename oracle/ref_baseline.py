@@ -23,12 +23,38 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ACTION_TO_INPUTS = ((0, 0), (-1, 0), (1, 0), (0, 1), (-1, 1), (1, 1))
 
 
+def _stale(compiled, src):
+    """True when `src` holds the reference and some module listed in the compiled copy's MANIFEST is missing from it or
+    newer there than its compiled image."""
+    if not os.path.isfile(os.path.join(src, "nclone", "nsim.py")):
+        return False
+    try:
+        with open(os.path.join(compiled, "MANIFEST.txt")) as f:
+            mods = [ln.strip() for ln in f.read().splitlines()[1:] if ln.strip()]
+    except OSError:
+        return True
+    for name in mods:
+        rel = name.replace(".", os.sep)
+        for cand in (rel + ".py", os.path.join(rel, "__init__.py")):
+            if os.path.isfile(os.path.join(src, cand)):
+                img = os.path.join(compiled, cand[:-3] + ".refc")
+                if not os.path.isfile(img) or os.path.getmtime(img) < os.path.getmtime(os.path.join(src, cand)):
+                    return True
+                break
+        else:
+            return True
+    return False
+
+
 def ref_path():
     """Where the reference's `nclone` package can be imported from, or None."""
     compiled = os.path.join(HERE, "_ref")
-    if os.path.isfile(os.path.join(compiled, "nclone", "nsim.refc")):
-        return compiled
     src = os.environ.get("NCLONE_REF", "/root/reference")
+    if os.path.isfile(os.path.join(compiled, "nclone", "nsim.refc")):
+        # where the reference tree is present too (the build container) a compiled copy older than any of its sources
+        # would be timed silently in its place: refuse it and import the tree itself (python -m oracle.make_ref rebuilds)
+        if not _stale(compiled, src):
+            return compiled
     if os.path.isfile(os.path.join(src, "nclone", "nsim.py")):
         return src
     return None

@@ -31,10 +31,23 @@ def test_reference_pool_counts_ticks_of_the_workload_policy():
 
 
 def test_both_arms_describe_the_workload_identically():
-    a = bench.config_dict("c3", 65536, 4096, "scattered", True)
-    b = bench.config_dict("c3", 65536, 4096, "scattered", True)
-    assert a == b and set(a) >= {"workload", "envs_per_gpu", "frame_skip", "max_frames", "distinct_levels"}
-    assert "model" not in a
+    """The driver compares the two arms' `config` objects.  Both arms must build theirs from the command line through the same
+    function (and through nothing else), and that function must not depend on --impl or on anything only one arm knows."""
+    import inspect
+    import json
+    for fn in (bench.run_reference, bench.main):
+        src = inspect.getsource(fn)
+        assert src.count('"config": headline_config(args, ') == 1, fn.__name__
+        assert "config_dict(" not in src.replace("headline_config(", ""), fn.__name__
+    n_levels = len(bench.load_maps(bench.WORKLOADS["c3"][0])[0])
+    for flags in ([], ["--envs", "131072", "--workload", "c4"], ["--no-flush", "--placement", "adjacent"]):
+        ours = bench.build_parser().parse_args(flags + ["--gpus", "1", "--steps", "20", "--warmup", "5"])
+        ref = bench.build_parser().parse_args(flags + ["--impl", "reference", "--gpus", "1", "--steps", "20", "--warmup", "5"])
+        a, b = json.dumps(bench.headline_config(ours, n_levels)), json.dumps(bench.headline_config(ref, n_levels))
+        assert a == b
+        cfg = json.loads(a)
+        assert set(cfg) >= {"workload", "envs_per_gpu", "frame_skip", "max_frames", "distinct_levels"} and "model" not in cfg
+    assert json.loads(a)["l2"] == "not flushed" and json.loads(a)["caller_env_order"] == "adjacent"
 
 
 def test_reference_modules_are_compiler_output_only():
