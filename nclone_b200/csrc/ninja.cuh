@@ -139,7 +139,6 @@ DEV bool ninja_collide_vs_tiles(Nin& n, Ctx& c, WarpPool& wp, bool alive) {
     }
     }
     unsigned todo;
-#ifndef NPP_COOP_LEGACY
     // Cooperative service, uniform: every lane parks its own loop state in shared memory and takes over the served
     // owner's, so the whole iteration (query + push) runs redundantly on all 32 lanes without a divergent section;
     // a lone wedged ninja -- the kernel's critical path -- pays per iteration for one broadcast of (a, b, result) only.
@@ -239,135 +238,9 @@ DEV bool ninja_collide_vs_tiles(Nin& n, Ctx& c, WarpPool& wp, bool alive) {
         COOP_T(cacc, 5, ct)
         int w1 = -1, w2 = -1;                                // winning lanes of the last two calls (-1: unknown)
         int it;
-#if NPP_COOP_BATCH
-        // Batched speculation.  The chain of a wedged ninja is evaluate -> (select) -> push, 30 times per substep; with the
-        // winner predicted the selection is off the chain, but the evaluation still has the warp run every lane's segment
-        // -- the arc lanes' branch (sqrt, two divisions), then the line lanes' -- before the predicted lane's point is
-        // there.  Here FOUR iterations run back to back on the predicted segments alone (winners alternate: w2, w1, w2,
-        // w1), evaluated uniformly on every lane from a decoded copy in shared memory -- closest point and push only, no
-        // distance, no vote -- and ONE divergent pass then checks all four votes at once: lane l evaluates segment l % 8
-        // at the position of iteration l / 8.  Every vote is the one of the predicted path below (same / loses, guard
-        // band for flagged squares); if any fails, or a predicted segment's bounds test does, the state of before the
-        // batch comes back from shared memory and the next four iterations run one at a time.  A committed batch is
-        // therefore four iterations of the reference's loop: same query results, same pushes, in the same order.
-        const bool batch_ok = ns >= 1 && ns <= 16;
-        const int bshift = ns <= 8 ? 3 : 4, bK = 32 >> bshift;   // lanes per iteration in the verification pass: 8 / 16; iterations per batch: 4 / 2
-        int batch_from = 0;
-        if (batch_ok) { if (lane < ns) seg_tab_put(wp, lane, g); __syncwarp(); }
-#endif
         #pragma unroll 1
         for (it = it_first; it < 32; it++) {
             ncoop++;
-#if NPP_COOP_BATCH
-            if (batch_ok && w1 >= 0 && w2 >= 0 && it >= batch_from && it + bK <= 32) {
-                if (lane == 0) {
-                    double* sn = wp.rb + COOP_SNAP;
-                    sn[0] = xpos; sn[1] = ypos; sn[2] = xspeed; sn[3] = yspeed; sn[4] = n.f[F_XCRUSH]; sn[5] = n.f[F_YCRUSH]; sn[6] = n.f[F_CRUSH_LEN];
-                    sn[7] = n.f[F_CEIL_NX]; sn[8] = n.f[F_CEIL_NY]; sn[9] = n.f[F_FLOOR_NX]; sn[10] = n.f[F_FLOOR_NY];
-                    sn[11] = __hiloint2double(n.i[I_CEILING_COUNT], n.i[I_FLOOR_COUNT]);
-                }
-                const bool pushed_before = pushed;
-                int nk = 0;
-                bool stop = false, inb_all = true;
-                #pragma unroll 1
-                for (int k = 0; k < bK; k++) {
-                    const SegC gs = seg_tab_get(wp, (k & 1) ? w1 : w2);
-                    if (lane == 0) { wp.rb[COOP_POS + k] = xpos; wp.rb[COOP_POS + 4 + k] = ypos; }
-                    double pa, pb; bool pback;
-                    const bool inb = closest_ab(gs, xpos, ypos, pa, pb, pback);
-                    nk = k + 1;
-                    if (!inb) { inb_all = false; break; }
-                    const Push t = push_eval(pback ? -1 : 1, pa, pb);
-                    if (!t.go) { stop = true; break; }
-                    push_commit(t);
-                }
-                __syncwarp();
-                // the batch's votes in one pass
-                const double inf = __longlong_as_double(0x7ff0000000000000LL);
-                const int vk = lane >> bshift, vj = lane & ((1 << bshift) - 1);
-                const bool act = vk < nk && vj < ns;
-                double d2 = inf, ea = 0, eb = 0; int er = 0; bool ix = false, ok = false;
-                if (inb_all && act) ok = closest_eval(seg_tab_get(wp, vj), wp.rb[COOP_POS + vk], wp.rb[COOP_POS + 4 + vk], d2, ea, eb, er, ix);
-                if (!ok) { d2 = inf; er = 0; ix = false; }
-                const int pj = (vk & 1) ? w1 : w2, pl = (vk << bshift) + pj;
-                const double sd = __shfl_sync(FULL_MASK, d2, pl), sa = __shfl_sync(FULL_MASK, ea, pl), sb = __shfl_sync(FULL_MASK, eb, pl);
-                const int scode = __shfl_sync(FULL_MASK, (er & 3) | (ix ? 4 : 0) | (ok ? 8 : 0), pl);
-                const int sr = (scode & 3) == 3 ? -1 : (scode & 3);
-                const bool same = er == sr && __double_as_longlong(ea) == __double_as_longlong(sa) && __double_as_longlong(eb) == __double_as_longlong(sb);
-                const bool loses = (ix || (scode & 4)) ? (d2 > sd + 1e-10) : (d2 > sd || (d2 == sd && vj > pj));
-                const unsigned bad = __ballot_sync(FULL_MASK, act && (vj == pj ? !ok : (ok && !same && !loses)));
-#ifdef NPP_PROFILE
-                if (lane == 0) { atomicAdd(&g_coop_cycles[6], 1ULL); if (!(inb_all && bad == 0)) atomicAdd(&g_coop_cycles[7], 1ULL + ((unsigned long long)(inb_all ? __ffs(bad) - 1 : 63) << 32)); }
-#endif
-                if (inb_all && bad == 0) {                    // all votes confirm the predictions: the batch stands
-                    ncoop += nk - 1;
-                    if (nk & 1) { const int t_ = w1; w1 = w2; w2 = t_; }
-                    if (stop) { it += nk - 1; break; }         // the loop ends at the iteration whose push did not go
-                    it += nk - 1;
-                    continue;
-                }
-                // a vote failed: back to the state of before the batch, the next four iterations one at a time
-                {
-                    const double* sn = wp.rb + COOP_SNAP;
-                    xpos = sn[0]; ypos = sn[1]; xspeed = sn[2]; yspeed = sn[3]; n.f[F_XCRUSH] = sn[4]; n.f[F_YCRUSH] = sn[5]; n.f[F_CRUSH_LEN] = sn[6];
-                    n.f[F_CEIL_NX] = sn[7]; n.f[F_CEIL_NY] = sn[8]; n.f[F_FLOOR_NX] = sn[9]; n.f[F_FLOOR_NY] = sn[10];
-                    n.i[I_CEILING_COUNT] = __double2hiint(sn[11]); n.i[I_FLOOR_COUNT] = __double2loint(sn[11]);
-                    pushed = pushed_before;
-                }
-                __syncwarp();
-                batch_from = it + bK;
-            }
-#endif
-#ifdef NPP_COOP_SPEC   // measured slower than the plain uniform loop (the broadcast of the push costs what the select saved); kept for A/B
-            // Speculative push: every lane pushes from ITS segment's closest point while the warp minimum is being
-            // found, then the winner's push is broadcast -- selection (two collectives and a vote) leaves the chain
-            // evaluate -> sqrt -> reciprocal -> position.  Same expressions on the same inputs as depen() above.
-            if (ns >= 0) {
-                const double inf = __longlong_as_double(0x7ff0000000000000LL);
-                double d2 = inf, ca = 0, cb = 0; int r = 1; bool ix = false, ok = false;
-                if (lane < ns) ok = closest_eval_nb(g, xpos, ypos, d2, ca, cb, r);
-                COOP_T(cacc, 0, ct)
-                if (__ballot_sync(FULL_MASK, ok && ix) == 0) {
-                    const unsigned cand = warp_first_min(d2, ok);
-                    double sdx = xpos - ca, sdy = ypos - cb;
-                    if (fabs(sdx) <= 0.0000001) {                  // ninja.py:312-318 band-aid
-                        sdx = 0;
-                        if (xpos == 50.51197510492316 || xpos == 49.23232124849253) sdx = -0x1p-47;
-                        if (xpos == 49.153536108584795) sdx = 0x1p-47;
-                    }
-                    const double dist_sq = sdx * sdx + sdy * sdy;
-                    const double dist = SQRT(dist_sq);
-                    double depen_len = NINJA_RADIUS - (r < 0 ? -dist : dist);
-                    const bool go_own = !(dist_sq < 1e-16) && !(depen_len < 0.0000001);
-                    const double inv_dist = DIV(1.0, dist);
-                    double norm_dx = sdx * inv_dist, norm_dy = sdy * inv_dist;
-                    double nvx = xspeed, nvy = yspeed;
-                    if (xspeed * sdx + yspeed * sdy < 0) {
-                        const double cross_product = xspeed * sdy - yspeed * sdx;
-                        const double inv_dist_sq = inv_dist * inv_dist;
-                        nvx = cross_product * inv_dist_sq * sdy;
-                        nvy = cross_product * inv_dist_sq * (sdx == 0 ? 0.0 : -sdx);
-                    }
-                    int pack = (go_own ? 1 : 0) | (sdy >= -0.0001 ? 2 : 0);
-                    COOP_T(cacc, 2, ct)
-                    if (!cand) break;                              // result == 0: nothing within reach
-                    const int w = __ffs(cand) - 1;
-                    pack = __shfl_sync(FULL_MASK, pack, w);
-                    if (!(pack & 1)) break;
-                    norm_dx = __shfl_sync(FULL_MASK, norm_dx, w); norm_dy = __shfl_sync(FULL_MASK, norm_dy, w);
-                    depen_len = __shfl_sync(FULL_MASK, depen_len, w);
-                    xspeed = __shfl_sync(FULL_MASK, nvx, w); yspeed = __shfl_sync(FULL_MASK, nvy, w);
-                    const double depen_x = norm_dx * depen_len, depen_y = norm_dy * depen_len;
-                    pushed = true;
-                    xpos += depen_x; ypos += depen_y;
-                    n.f[F_XCRUSH] += depen_x; n.f[F_YCRUSH] += depen_y; n.f[F_CRUSH_LEN] += depen_len;
-                    if (pack & 2) { n.i[I_CEILING_COUNT] += 1; n.f[F_CEIL_NX] += norm_dx; n.f[F_CEIL_NY] += norm_dy; }
-                    else { n.i[I_FLOOR_COUNT] += 1; n.f[F_FLOOR_NX] += norm_dx; n.f[F_FLOOR_NY] += norm_dy; }
-                    COOP_T(cacc, 1, ct)
-                    continue;
-                }
-            }
-#endif
             double a = 0, b = 0; int result = 0, w = -1;
             if (ns < 0) {                                    // list overflow: the owner's literal walk, then broadcast
                 double ea = 0, eb = 0;
@@ -456,39 +329,6 @@ DEV bool ninja_collide_vs_tiles(Nin& n, Ctx& c, WarpPool& wp, bool alive) {
 #undef COOP_PARK
 #undef COOP_TAKE
 #undef COOP_BACK
-#else
-    #pragma unroll 1
-    while ((todo = __ballot_sync(FULL_MASK, need)) != 0) {
-        const int lane = threadIdx.x & 31;
-        const int o = __ffs(todo) - 1;
-        const int ns = __shfl_sync(FULL_MASK, nseg, o);
-        const SegC g = seg_decode(lane < ns ? wp.lseg[o][lane] : 0u);
-        #pragma unroll 1
-        for (int it = 2; it < 32; it++) {
-            if (lane == o) wp.coop++;
-            double a = 0, b = 0; int result = 0;
-#ifdef NPP_PROFILE
-            long long _c0 = clock64();
-#endif
-            if (ns < 0) {
-                if (lane == o) result = closest_point_exact(c.cell_hdr, c.segs, gx1, gy1, gx2, gy2, xpos, ypos, a, b);
-            } else {
-                result = warp_closest_point(wp, c, o, ns, g, gx1, gy1, gx2, gy2, xpos, ypos, a, b);
-            }
-#ifdef NPP_PROFILE
-            long long _c1 = clock64();
-#endif
-            bool cont = false;
-            if (lane == o) cont = depen(result, a, b);
-            const bool go = __shfl_sync(FULL_MASK, (int)cont, o);
-#ifdef NPP_PROFILE
-            (void)_c0; (void)_c1;
-#endif
-            if (!go) break;
-        }
-        if (lane == o) need = false;
-    }
-#endif
     PH_MARK(6)
     if (alive) { n.f[F_XPOS] = xpos; n.f[F_YPOS] = ypos; n.f[F_XSPEED] = xspeed; n.f[F_YSPEED] = yspeed; }
     return !pushed && __double_as_longlong(xpos) == __double_as_longlong(xin) && __double_as_longlong(ypos) == __double_as_longlong(yin);

@@ -378,54 +378,6 @@ DEV bool closest_eval(const SegC& g, double x, double y, double& d2, double& a, 
     r = back ? -1 : 1;
     return true;
 }
-// The closest point alone -- closest_eval's first half, same expressions -- for the speculative chain of the batched
-// cooperative loop (ninja.cuh): the push needs (a, b, side), not the distance.  Returns the bounds test.
-DEV bool closest_ab(const SegC& g, double x, double y, double& a, double& b, bool& back) {
-    const bool inb = !(g.bx1 < x - NINJA_RADIUS || g.bx0 > x + NINJA_RADIUS || g.by1 < y - NINJA_RADIUS || g.by0 > y + NINJA_RADIUS);
-    const double dx = x - g.x1, dy = y - g.y1;
-    if (!g.arc) {                                                            // entities.py:43-59
-        double u = div_seglen(dx * g.px + dy * g.py, g.lensq);
-        if (0 > u) u = 0;
-        if (1 < u) u = 1;
-        a = g.x1 + u * g.px; b = g.y1 + u * g.py;
-        back = (dy * g.px - dx * g.py < 0);
-    } else {                                                                 // entities.py:127-157
-        back = false;
-        if (dx * g.px > 0 && dy * g.py > 0) {
-            double dist = SQRT(SQ(dx) + SQ(dy));
-            double qa, qb;
-            div2(24.0 * dx, 24.0 * dy, dist, qa, qb);
-            a = g.x1 + qa; b = g.y1 + qb;
-            back = (g.lensq != 0) ? (dist < 24.0) : (dist > 24.0);
-        } else if (dx * g.px > dy * g.py) { a = g.x1 + 24.0 * g.px; b = g.y1; }
-        else { a = g.x1; b = g.y1 + 24.0 * g.py; }
-    }
-    return inb;
-}
-// Decoded segments of the served owner's list in shared memory (the first 16 entries; rows of 16 in the idle part of
-// wp.rb): the batched loop evaluates the PREDICTED segment on every lane, and its verification pass gives lane l segment
-// l % 8 (lists of up to 8: four iterations per batch) or l % 16 (up to 16: two).
-// Measured (tools/r02_call34.sh, profiles/r02_handoff_ab.md section 15): every batch verified (0 failures on the three wedge
-// fixtures), yet a batch costs what it saves -- lists of up to 8 (four iterations per batch) 1,273 against 1,372 cycles per
-// iteration on the line wedge, lists of 9-16 (two per batch) 2,217 against 2,101 (arc) and 1,532 against 1,380 (lines);
-// config 3 at 65,536 envs 358 against 377 M.  The predicted path had taken the selection off the chain already; what the
-// batch removes (the other lanes' evaluations) is less than its table reads, snapshot and verification pass.  Off.
-#ifndef NPP_COOP_BATCH
-#define NPP_COOP_BATCH 0
-#endif
-#define COOP_TAB 32                     // wp.rb[32 .. 192): 10 rows x 16 segments
-#define COOP_POS 192                    // wp.rb[192 .. 200): positions of the batch's iterations, x then y
-#define COOP_SNAP 200                   // wp.rb[200 .. 212): the state before the batch
-DEV void seg_tab_put(WarpPool& wp, int j, const SegC& g) {
-    double* t = wp.rb + COOP_TAB + j;
-    t[0] = g.bx0; t[16] = g.by0; t[32] = g.bx1; t[48] = g.by1; t[64] = g.x1; t[80] = g.y1; t[96] = g.px; t[112] = g.py; t[128] = g.lensq; t[144] = g.arc ? 1.0 : 0.0;
-}
-DEV SegC seg_tab_get(const WarpPool& wp, int j) {
-    const double* t = wp.rb + COOP_TAB + j;
-    SegC g;
-    g.bx0 = t[0]; g.by0 = t[16]; g.bx1 = t[32]; g.by1 = t[48]; g.x1 = t[64]; g.y1 = t[80]; g.px = t[96]; g.py = t[112]; g.lensq = t[128]; g.arc = t[144] != 0.0;
-    return g;
-}
 DEV bool closest_item(uint32_t s, double x, double y, double& d2, double& a, double& b, int& r, bool& ix) {
     return closest_eval(seg_decode(s), x, y, d2, a, b, r, ix);
 }
@@ -625,11 +577,7 @@ DEV int warp_closest_uniform(WarpPool& wp, const Ctx& c, int o, int ns, const Se
     win = -1;
     const double inf = __longlong_as_double(0x7ff0000000000000LL);
     double d2 = inf, a = 0, b = 0; int r = 0; bool ix = false, ok = false;
-#ifdef NPP_COOP_EVAL_EXACT   // bounds test off the chain + exact squares instead of the flagged ones: measured 1-2 % slower
-    if (lane < ns) ok = closest_eval_nb(g, x, y, d2, a, b, r);
-#else
     if (lane < ns) ok = closest_eval(g, x, y, d2, a, b, r, ix);
-#endif
     if (!ok) d2 = inf;
     COOP_T(cacc, 0, ct)
     return warp_select_uniform(wp, c, o, ns, ok, d2, a, b, r, ix, gx1, gy1, gx2, gy2, x, y, pa, pb, win);
