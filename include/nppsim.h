@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define NPPSIM_VERSION 101
+#define NPPSIM_VERSION 102
 
 #define NPPSIM_E_ARG      (-1)
 #define NPPSIM_E_MAP      (-2)   /* malformed map_data (the reference raises KeyError/IndexError/ValueError) */
@@ -47,7 +47,11 @@ extern "C" {
 #define NPPSIM_ENV_TICKS   5   /* ticks executed since load_maps (wraps at 2^31), for throughput accounting */
 #define NPPSIM_ENV_WEDGE   6   /* == the tag of a handoff queue (nppsim_state_t.handoff): the env is among that queue's initial
                                   entries and starts the next launch on a solo warp; written only between launches */
-#define NPPSIM_NENV 7
+#define NPPSIM_ENV_RELOADS 7   /* Simulator.reset() calls since the level was loaded on a fresh Simulator: the reference numbers entities
+                                  from counters that live as long as the Simulator (entities.py:213-216), so an entity's `index` is
+                                  its index in the level + RELOADS * (entities of its type in the level); death balls stop repelling
+                                  each other once it is non-zero (entity_death_ball.py:153-166) */
+#define NPPSIM_NENV 8
 
 #define NPPSIM_EV_EXIT_SWITCH 1  /* entity_exit_switch.py:128-129 -> gym_env.invalidate_switch_cache() */
 #define NPPSIM_EV_LOCKED_DOOR 2  /* entity_door_locked.py:66-67 */
@@ -149,9 +153,14 @@ int nppsim_compile_maps_device(const double* map_data, int64_t row_stride, const
                                int32_t* summary, void* stream);
 
 /* ---- device side ------------------------------------------------------------------------
- * nppsim_reset: Simulator.load()'s dynamic part / reset() (mode 0, nsim.py:62-76) or
- * fast_reset() (mode 1, nsim.py:78-140) for every env whose mask byte is non-zero
- * (mask == NULL: all envs).  mask is a device pointer. */
+ * nppsim_reset, for every env whose mask byte is non-zero (mask == NULL: all envs; mask is a device pointer):
+ *   mode 0  Simulator.reset() (nsim.py:62-76) on the Simulator that already holds the level -- the call NPlayHeadless.reset
+ *           (nplay_headless.py:272-276) and ActionReplayer.replay_to_checkpoint (action_replayer.py:99) make.  The reference
+ *           never clears sim.entity_counts, so the re-created entities' `index` keeps counting (NPPSIM_ENV_RELOADS), and
+ *           with it death balls stop repelling each other from the second episode on.
+ *   mode 1  fast_reset() (nsim.py:78-140).
+ *   mode 2  Simulator() + load() (nsim.py:51-56): the dynamic part of a load on a fresh Simulator, indices from 0.  Use it
+ *           once after the state arrays are allocated (zero-filled state + mode 0 would leave RELOADS at 1). */
 int nppsim_reset(const nppsim_state_t* st, const uint8_t* mask, int32_t mode, void* stream);
 
 /* nppsim_reset_terminal: the env wrapper's episode turnover for a whole batch -- reset (mode as above)

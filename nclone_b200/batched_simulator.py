@@ -81,7 +81,7 @@ class BatchedSimulator:
         for t in self.maps:
             kind_mask |= t.kind_mask           # entity-kind census of the level set -> step-kernel variant
         self._alloc_state(len(blobs), max(t.n_ent for t in self.maps), max(t.n_dyn for t in self.maps), kind_mask)
-        self.reset()
+        self.reset(mode="load")
 
     def load_maps_device(self, map_data, map_len=None, env_to_map=None):
         """Simulator.load for levels that are already in HBM: map_data is a CUDA float64 tensor
@@ -126,7 +126,7 @@ class BatchedSimulator:
         self.env_map_host = env_map.cpu().numpy()
         self._place(self.env_map_host)
         self._alloc_state(M, ent_cap, dyn_cap, kind_mask)
-        self.reset()
+        self.reset(mode="load")
 
     def _place(self, env_map_host):
         """State-column order (placement='level'): envs sorted by level, stable, unless that is the caller's order anyway
@@ -339,10 +339,15 @@ class BatchedSimulator:
             raise RuntimeError("load_maps() first")
 
     # ------------------------------------------------------------------ Simulator.reset / fast_reset (nsim.py:62-140)
+    RESET_MODES = {"reset": 0, "fast": 1, "load": 2}
+
     def reset(self, mask=None, mode="reset"):
-        """mode 'reset' = Simulator.load/reset on a fresh Simulator; 'fast' = Simulator.fast_reset."""
+        """mode 'reset' = Simulator.reset() as the reference's callers issue it, on the Simulator that has held the level since
+        load_maps (NPlayHeadless.reset, ActionReplayer): entities are re-created and their `index` keeps counting
+        (entities.py:213-216), so death balls no longer repel each other afterwards (entity_death_ball.py:153-166);
+        'fast' = Simulator.fast_reset; 'load' = a fresh Simulator loading the level (what load_maps does)."""
         self._need_maps()
-        m = {"reset": 0, "fast": 1}[mode]
+        m = self.RESET_MODES[mode]
         ptr = None
         if mask is not None:
             mask = torch.as_tensor(mask, device=self.device).to(torch.uint8).contiguous()
@@ -358,7 +363,7 @@ class BatchedSimulator:
         Episode statistics accumulate in self.stats (device uint64[4]: episodes, wins, deaths, truncations)."""
         self._need_maps()
         with torch.cuda.device(self.device):
-            check(self.L.nppsim_reset_terminal(C.byref(self._state), int(max_frames), {"reset": 0, "fast": 1}[mode],
+            check(self.L.nppsim_reset_terminal(C.byref(self._state), int(max_frames), self.RESET_MODES[mode],
                                                C.c_void_p(self.stats.data_ptr()), self._stream()))
 
     # ------------------------------------------------------------------ curriculum mutation from outside tick
@@ -520,7 +525,7 @@ class BatchedSimulator:
                 check(self.L.nppsim_step_host_reset(C.byref(self._state), C.c_void_p(a.ctypes.data), C.c_void_p(self._actions_dev.data_ptr()),
                                                     int(frame_skip), int(bool(stop_on_terminal)), C.c_void_p(stg),
                                                     C.c_void_p(block.data_ptr()), int(bool(with_obs)), int(reset_max_frames),
-                                                    {"reset": 0, "fast": 1}[reset_mode], C.c_void_p(self.stats.data_ptr()), self._stream()))
+                                                    self.RESET_MODES[reset_mode], C.c_void_p(self.stats.data_ptr()), self._stream()))
         self._adapt_handoff()
 
     def step_host_static(self, actions_host, block, frame_skip=4, stop_on_terminal=True, with_obs=False):
@@ -683,10 +688,11 @@ class BatchedSimulator:
         df = self._dyn_f[:, tid].cpu().numpy()
         di = self._dyn_i[:, tid].cpu().numpy()
         order = self._env_i[FD.ENV_ORDER][tid].cpu().numpy()
+        reloads = self._env_i[FD.ENV_RELOADS][tid].cpu().numpy()
         out = []
         for k, env in enumerate(ids):
             t = self.maps[self.env_map_host[env]]
-            out.append((nf[k], ni[k]) + _entity_rows(t, fl[:, k], df[:, k], di[:, k], int(order[k])))
+            out.append((nf[k], ni[k]) + _entity_rows(t, fl[:, k], df[:, k], di[:, k], int(order[k]), int(reloads[k])))
         return out
 
     def _queue(self):
@@ -777,9 +783,11 @@ class _DeviceMaps:
         return sw_id[em], sw_slot[em], dr_slot[em]
 
 
-def _entity_rows(t, fl, df, di, order_mode):
-    """Rebuild the reference's per-entity attributes from one env's flag / slot arrays."""
+def _entity_rows(t, fl, df, di, order_mode, reloads=0):
+    """Rebuild the reference's per-entity attributes from one env's flag / slot arrays.  `index` is the entity's index in the
+    level plus, per Simulator.reset() since the load, the number of entities of its type (entities.py:213-216)."""
     E = t.n_ent
+    per_type = np.bincount(np.asarray(t.ents["type"][:E], dtype=np.int64), minlength=40) if E else np.zeros(40, dtype=np.int64)
     ef = np.zeros((E, 4)); ei = np.zeros((E, 8), dtype=np.int64)
     cell = np.zeros(E, dtype=np.int64); stamp = np.zeros(E, dtype=np.int64); in_grid = np.ones(E, dtype=bool)
     for e in range(E):
@@ -820,7 +828,7 @@ def _entity_rows(t, fl, df, di, order_mode):
             a0, a1 = df[slot * 4 + 2], df[slot * 4 + 3]
         cell[e], stamp[e] = c, st
         ef[e] = (x, y, a0, a1)
-        ei[e, :7] = (int(s["type"]), int(s["index"]), active, c // 25, c % 25, s0, s1)
+        ei[e, :7] = (int(s["type"]), int(s["index"]) + reloads * int(per_type[int(s["type"])]), active, c // 25, c % 25, s0, s1)
     for e in range(E):
         if not in_grid[e]:
             ei[e, 7] = -1

@@ -24,7 +24,10 @@ int cuda_fail(cudaError_t e, const char* what) {
 }
 
 // ---- reset -------------------------------------------------------------------------------------------
-// mode 0: state right after Simulator.load / reset (nsim.py:62-76; Ninja.__init__ ninja.py:80-196; entity ctors)
+// mode 0: state right after Simulator.reset() on the Simulator that has held the level so far (nsim.py:62-76; Ninja.__init__
+//         ninja.py:80-196; entity ctors) -- what NPlayHeadless.reset and ActionReplayer call; the entities are created again and
+//         their `index` goes on counting (entities.py:213-216), which env_i[NPPSIM_ENV_RELOADS] records
+// mode 2: the same state on a FRESH Simulator (Simulator() + load(), nsim.py:51-56): indices start at 0 again
 // mode 1: Simulator.fast_reset (nsim.py:78-140): only classes with reset_state() are restored, every
 //         entity (except exit doors) is re-appended to its cell in entity_dic order.
 // One lane owns one env for the test and the ninja record; the entity tables of the envs that do reset (about 1 % per
@@ -35,6 +38,8 @@ __global__ void __launch_bounds__(128) reset_kernel(nppsim_state_t st, const uin
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
     const size_t N = npp_stride(st);
+    const bool fresh = mode == 2;
+    if (fresh) mode = 0;
     bool need = i < st.n_envs && !(mask && !mask[npp_ext(st, i)]);
     if (need && auto_terminal) {
         int s = st.nin_i[I_STATE * N + i], fr = st.nin_i[I_FRAME * N + i];
@@ -62,6 +67,7 @@ __global__ void __launch_bounds__(128) reset_kernel(nppsim_state_t st, const uin
         envi[NPPSIM_ENV_STAMP * N] = h->n_ent;
         envi[NPPSIM_ENV_EVENTS * N] = 0;
         envi[NPPSIM_ENV_SWFRAME * N] = -1;
+        if (mode == 0) envi[NPPSIM_ENV_RELOADS * N] = fresh ? 0 : envi[NPPSIM_ENV_RELOADS * N] + 1;     // (fast_reset re-creates nothing)
         envi[NPPSIM_ENV_ORDER * N] = mode ? 1 : 0;           // (NPPSIM_ENV_WEDGE stays: it belongs to the handoff queue)
     }
     #pragma unroll 1
@@ -680,7 +686,7 @@ int nppsim_reset(const nppsim_state_t* st, const uint8_t* mask, int32_t mode, vo
     g_err[0] = 0;
     int rc = check_state(st);
     if (rc) return rc;
-    if (mode != 0 && mode != 1) return fail(NPPSIM_E_ARG, "mode must be 0 (load/reset) or 1 (fast_reset)");
+    if (mode < 0 || mode > 2) return fail(NPPSIM_E_ARG, "mode must be 0 (reset), 1 (fast_reset) or 2 (load on a fresh Simulator)");
     const int block = 128;
     reset_kernel<<<(st->n_envs + block - 1) / block, block, 0, (cudaStream_t)stream>>>(*st, mask, mode, 0, 0, nullptr);
     g_launches++;
@@ -693,7 +699,7 @@ int nppsim_reset_terminal(const nppsim_state_t* st, int32_t max_frames, int32_t 
     g_err[0] = 0;
     int rc = check_state(st);
     if (rc) return rc;
-    if (mode != 0 && mode != 1) return fail(NPPSIM_E_ARG, "mode must be 0 (load/reset) or 1 (fast_reset)");
+    if (mode < 0 || mode > 2) return fail(NPPSIM_E_ARG, "mode must be 0 (reset), 1 (fast_reset) or 2 (load on a fresh Simulator)");
     const int block = 128;
     reset_kernel<<<(st->n_envs + block - 1) / block, block, 0, (cudaStream_t)stream>>>(*st, nullptr, mode, 1, max_frames, stats);
     g_launches++;
@@ -779,7 +785,7 @@ static int step_host_impl(const nppsim_state_t* st, const uint8_t* actions_host,
     if (((uintptr_t)staging_dev & 7) != 0) return fail(NPPSIM_E_ARG, "staging_dev must be 8-byte aligned");
     if (n_ticks <= 0) return fail(NPPSIM_E_ARG, "n_ticks must be positive");
     // (everything is checked before anything is queued: an error return leaves the state as it was)
-    if (turnover && reset_mode != 0 && reset_mode != 1) return fail(NPPSIM_E_ARG, "mode must be 0 (load/reset) or 1 (fast_reset)");
+    if (turnover && (reset_mode < 0 || reset_mode > 2)) return fail(NPPSIM_E_ARG, "mode must be 0 (reset), 1 (fast_reset) or 2 (load on a fresh Simulator)");
     cudaStream_t s = (cudaStream_t)stream;
     const size_t N = (size_t)st->n_envs;
     // Pinned actions are read by the step kernel where they are (one byte per env as the env is loaded: mapped host memory)

@@ -29,7 +29,7 @@ I = {n: i for i, n in enumerate(NINJA_I)}
 NF, NI = len(NINJA_F), len(NINJA_I)
 DEATH_CAUSES = (None, "mine", "terminal_impact")
 
-ENV_STAMP, ENV_HOT, ENV_EVENTS, ENV_SWFRAME, ENV_ORDER, ENV_TICKS, ENV_WEDGE, NENV = 0, 1, 2, 3, 4, 5, 6, 7
+ENV_STAMP, ENV_HOT, ENV_EVENTS, ENV_SWFRAME, ENV_ORDER, ENV_TICKS, ENV_WEDGE, ENV_RELOADS, NENV = 0, 1, 2, 3, 4, 5, 6, 7, 8
 HANDOFF_WORDS = 16 + 2 * 4096
 EV_EXIT_SWITCH, EV_LOCKED_DOOR, EV_WIN, EV_DEATH = 1, 2, 4, 8
 

@@ -23,7 +23,7 @@ def test_header_symbols_exported():
     L = lib()
     for name in declared:
         assert getattr(L, name) is not None
-    assert L.nppsim_version() == 101
+    assert L.nppsim_version() == 102
     assert L.nppsim_sq_mode() == 1
 
 

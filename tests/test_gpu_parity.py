@@ -112,7 +112,12 @@ def test_curriculum_repositioning_bit_exact(golden_curriculum, golden_replays):
     two.set_exit_positions(np.array([[m[1]], [m[2]]]), np.array([[m[3]], [m[4]]]))
     assert schema.state_hash(*two.canonical_state()[0]) == first["hash"][0]
     two.reset()
-    assert schema.state_hash(*two.canonical_state()[0]) == schema.state_hash(*before[0])
+    after = two.canonical_state()[0]
+    ref = oracle.OracleSim(); ref.load(first["map_data"]); ref.reset()       # Simulator.reset() re-creates the entities: `index` counts on
+    assert schema.state_hash(*after) == schema.state_hash(*ref.state())
+    (nf0, ni0, ef0, ei0), (nf1, ni1, ef1, ei1) = before[0], after                 # and everything but `index` is as after the load
+    assert np.array_equal(nf0, nf1) and np.array_equal(ni0, ni1) and np.array_equal(ef0, ef1)
+    assert np.array_equal(np.delete(ei0, 1, axis=1), np.delete(ei1, 1, axis=1)) and not np.array_equal(ei0[:, 1], ei1[:, 1])
 
 
 def test_first_replay_known_answer(golden_replays):
@@ -177,12 +182,20 @@ def test_reset_and_fast_reset(golden_replays):
     for _ in range(50):
         sim.step(torch.from_numpy(rng.integers(0, 6, len(idx)).astype(np.uint8)).cuda(), 4, False)
     sim.reset()
-    for a, b in zip(first, sim.canonical_state()):
-        assert schema.state_hash(*a) == schema.state_hash(*b)
-    # fast_reset against the oracle's fast_reset after the same history
+    # Simulator.reset() on the Simulator that loaded the level: the initial state again, entity indices counting on
+    # (entities.py:213-216) -- the oracle's reset() is pinned to the reference's on exactly this (tests/golden/reset_reuse.npz)
     osims = []
     for t in trajs:
-        s = oracle.OracleSim(); s.load(t["map_data"]); osims.append(s)
+        s = oracle.OracleSim(); s.load(t["map_data"]); s.reset(); osims.append(s)
+    for a, b, s in zip(first, sim.canonical_state(), osims):
+        assert schema.state_hash(*b) == schema.state_hash(*s.state())
+        assert np.array_equal(a[0].view(np.int64), b[0].view(np.int64)) and np.array_equal(a[1], b[1])
+        assert np.array_equal(a[2].view(np.int64), b[2].view(np.int64)) and np.array_equal(np.delete(a[3], 1, axis=1), np.delete(b[3], 1, axis=1))
+    sim.reset(mode="load")                                # a fresh Simulator loading the level: indices from 0 again
+    for a, b in zip(first, sim.canonical_state()):
+        assert schema.state_hash(*a) == schema.state_hash(*b)
+    sim.reset()
+    # fast_reset against the oracle's fast_reset after the same history
     acts = rng.integers(0, 6, size=(40, len(idx))).astype(np.uint8)
     from nclone_b200 import ACTION_TO_INPUTS
     for st in range(40):
@@ -202,6 +215,48 @@ def test_reset_and_fast_reset(golden_replays):
             for _ in range(4):
                 s.tick(h, j)
             assert schema.state_hash(*s.state()) == schema.state_hash(*recs[k]), (k, st)
+
+
+def test_reset_on_a_reused_simulator_vs_reference(golden_replays):
+    """nppsim_reset mode 0 is Simulator.reset() the way the reference's callers use it -- on the Simulator that already holds
+    the level (NPlayHeadless.reset, ActionReplayer).  tests/golden/reset_reuse.npz (unmodified reference,
+    oracle/gen_golden_reset.py): load -> 150 ticks -> reset() -> 400 ticks -> reset() -> 400 ticks on every bc_replays level
+    with two or more death balls; entity indices keep counting (entities.py:213-216) and the balls stop repelling each other
+    after the first episode (entity_death_ball.py:153-166) -- 10 of the 19 levels, 41 and 86 among them, then move differently
+    from a fresh Simulator.  Full canonical record, `index` included, after the load, every tick and each reset."""
+    import torch
+    from nclone_b200 import BatchedSimulator
+    d = np.load(os.path.join(ROOT, "tests", "golden", "reset_reuse.npz"))
+    levels = [int(v) for v in d["level"]]
+    starts = list(np.cumsum(d["segments"])[:-1])
+    assert int((d["differs_from_fresh"] >= 0).sum()) >= 8 and {41, 86} <= set(levels)
+    N = len(levels)
+    sim = BatchedSimulator(N)
+    sim.load_maps([golden_replays.traj(i)["map_data"] for i in levels], np.arange(N))
+    assert sim.kernel_variant() == "sim_full"
+    hor_d = torch.from_numpy(np.ascontiguousarray(d["hor"].T)).cuda(); jump_d = torch.from_numpy(np.ascontiguousarray(d["jump"].T)).cuda()
+    bad = [(levels[k], "load") for k, r in enumerate(sim.canonical_state()) if schema.state_hash(*r) != d["hash_init"][k]]
+    alive = np.ones(N, dtype=bool)
+    for t in range(hor_d.shape[0]):
+        if t in starts:
+            sim.reset()
+            for k, r in enumerate(sim.canonical_state()):
+                if alive[k] and schema.state_hash(*r) != d["hash_reset"][k, starts.index(t)]:
+                    bad.append((levels[k], f"reset before tick {t}")); alive[k] = False
+        sim.tick(hor_d[t], jump_d[t], n_ticks=1)
+        ids = np.nonzero(alive)[0]
+        for k, r in zip(ids, sim.canonical_state(ids)):
+            if schema.state_hash(*r) != d["hash_tick"][k, t]:
+                bad.append((levels[k], t)); alive[k] = False       # first differing frame only
+    assert not bad, bad
+    # a batch that is reloaded instead (fresh Simulators) does NOT follow these goldens where balls meet: the distinction is real
+    fresh = BatchedSimulator(N); fresh.load_maps([golden_replays.traj(i)["map_data"] for i in levels], np.arange(N))
+    for t in range(hor_d.shape[0]):
+        if t in starts:
+            fresh.reset(mode="load")
+        fresh.tick(hor_d[t], jump_d[t], n_ticks=1)
+    differ = (fresh.dyn_f.view(torch.int64) != sim.dyn_f.view(torch.int64)).any(0).cpu().numpy()
+    assert differ.sum() >= 5, differ
 
 
 def test_step_host_matches_device_path(golden_replays, golden_generated):
@@ -283,7 +338,7 @@ def _oracle_rollout(maps, env_to_map, actions, frame_skip, max_frames, check_eve
             out.append((st, nf.copy(), ni.copy()))
         for k, s in enumerate(sims):
             if ni[k, 0] in (6, 7, 8) or ni[k, 26] >= max_frames:
-                s.load(maps[env_to_map[k]])           # fresh-Simulator semantics, as nppsim_reset mode 0
+                s.reset()                             # Simulator.reset() on the same Simulator, as nppsim_reset mode 0
     return out
 
 
@@ -668,8 +723,8 @@ def test_replay_dataset_rows_vs_reference():
 
 def test_checkpoint_replay_vs_reference():
     """replay_to_checkpoint (reset + ragged per-env action streams, one launch) against the
-    reference's ActionReplayer(frame_skip=4).replay_to_checkpoint.  Every column bit-exact except entity `index`,
-    which keeps counting across reset() on the reference's re-used Simulator (entities.py:213-216)."""
+    reference's ActionReplayer(frame_skip=4).replay_to_checkpoint.  Every column bit-exact, entity `index` included: it
+    keeps counting across the reset() on the reference's re-used Simulator (entities.py:213-216), and so does the batch's."""
     import torch
     from nclone_b200 import BatchedSimulator
     d, G = _replay_rows_fixture()
@@ -688,15 +743,17 @@ def test_checkpoint_replay_vs_reference():
         e0, e1 = d["ck_ent_off"][k], d["ck_ent_off"][k + 1]
         assert np.array_equal(nf.view(np.int64), d["ck_nin_f"][k].view(np.int64)) and np.array_equal(ni, d["ck_nin_i"][k]), k
         assert np.array_equal(ef.view(np.int64), d["ck_ent_f"][e0:e1].view(np.int64)), k
-        keep = [c for c in range(ei.shape[1]) if c != 1]
-        assert np.array_equal(ei[:, keep], d["ck_ent_i"][e0:e1][:, keep]), k
+        assert np.array_equal(ei, d["ck_ent_i"][e0:e1]), k
     # masked restore: only env 0 is touched
     before = sim.canonical_state()
     mask = np.zeros(N, dtype=np.uint8); mask[0] = 1
     sim.replay_to_checkpoint(seqs, frame_skip=4, mask=mask)
     after = sim.canonical_state()
-    for k in range(N):
+    for k in range(1, N):
         assert schema.state_hash(*before[k]) == schema.state_hash(*after[k]), k
+    # env 0 went through one more reset(): the same state again, its entities' indices one level's worth further on
+    assert all(np.array_equal(a, b) for a, b in zip(before[0][:3], after[0][:3]))
+    assert np.array_equal(np.delete(before[0][3], 1, axis=1), np.delete(after[0][3], 1, axis=1)) and (after[0][3][:, 1] > before[0][3][:, 1]).all()
 
 
 def test_env_view_mirrors_single_env_interface(golden_replays):

@@ -225,3 +225,26 @@ def test_threaded_rollout_records_match_the_per_tick_loop():
             if ni[0] in (6, 7, 8) or ni[26] >= 300:
                 s.load(md)
     assert total == ticks
+
+
+def test_reset_on_a_reused_simulator_vs_reference(golden_replays):
+    """tests/golden/reset_reuse.npz (oracle/gen_golden_reset.py, unmodified reference): load -> 150 ticks -> reset() -> 400 ticks
+    -> reset() -> 400 ticks on ONE Simulator, every bc_replays level with two or more death balls.  entity_counts outlives
+    reset() (entities.py:213-216), so entity indices keep counting and death balls stop repelling each other after the first
+    episode (entity_death_ball.py:153-166): 10 of the 19 levels then move differently from a fresh Simulator.  The oracle's
+    reset() must follow the reference's, every frame, full record (entity `index` included)."""
+    import os
+    from conftest import GOLDEN
+    d = np.load(os.path.join(GOLDEN, "reset_reuse.npz"))
+    starts = list(np.cumsum(d["segments"])[:-1])
+    assert int((d["differs_from_fresh"] >= 0).sum()) >= 8 and {41, 86} <= set(int(v) for v in d["level"])
+    for k, lvl in enumerate(d["level"]):
+        s = oracle.OracleSim(); s.load(golden_replays.traj(int(lvl))["map_data"])
+        assert schema.state_hash(*s.state()) == d["hash_init"][k], lvl
+        for t in range(d["hor"].shape[1]):
+            if t in starts:
+                s.reset()
+                assert schema.state_hash(*s.state()) == d["hash_reset"][k, starts.index(t)], (lvl, t)
+            s.tick(int(d["hor"][k, t]), int(d["jump"][k, t]))
+            assert schema.state_hash(*s.state()) == d["hash_tick"][k, t], (lvl, t)
+
